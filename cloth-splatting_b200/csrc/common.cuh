@@ -1,0 +1,135 @@
+// Shared helpers for the sm_100a kernels of the cloth-splatting hot path.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/cloth_splatting_b200.h"
+
+#define CSB_TILE_X 16  // RAST/cuda_rasterizer/config.h:16-17 (results depend on it through getRect)
+#define CSB_TILE_Y 16
+#define CSB_TILE_PIX (CSB_TILE_X * CSB_TILE_Y)
+
+#define CSB_CUDA_TRY(expr)                         \
+    do {                                           \
+        cudaError_t _e = (expr);                   \
+        if (_e != cudaSuccess) return (int)_e;     \
+    } while (0)
+
+#define CSB_LAUNCH_CHECK()                         \
+    do {                                           \
+        cudaError_t _e = cudaGetLastError();       \
+        if (_e != cudaSuccess) return (int)_e;     \
+    } while (0)
+
+namespace csb {
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Bump allocator over a caller-provided workspace (256-byte aligned slices).
+struct Carver {
+    char* base;
+    size_t off;
+    explicit Carver(void* p) : base((char*)p), off(0) {}
+    template <typename T>
+    T* take(size_t count) {
+        off = align_up(off, 256);
+        T* r = (T*)(base ? base + off : nullptr);
+        off += count * sizeof(T);
+        return r;
+    }
+    size_t total() const { return align_up(off, 256); }
+};
+
+// Per-launch constants of up to CSB_MAX_VIEWS views, passed by value as a kernel parameter.
+struct ViewBatch {
+    int V, P, W, H, gx, gy, tiles;
+    float focal_x[CSB_MAX_VIEWS], focal_y[CSB_MAX_VIEWS];
+    float tan_fovx[CSB_MAX_VIEWS], tan_fovy[CSB_MAX_VIEWS];
+    const float* viewmatrix[CSB_MAX_VIEWS];
+    const float* projmatrix[CSB_MAX_VIEWS];
+    const float* campos[CSB_MAX_VIEWS];
+    const float* background[CSB_MAX_VIEWS];
+};
+
+// Number of bits needed to tell n tile ids apart the way the reference does
+// (rasterizer_impl.cu:35-50: the bit above the MSB of n).
+static inline int higher_msb(uint32_t n) {
+    int b = 0;
+    while (b < 32 && (n >> b)) ++b;
+    return b < 1 ? 1 : b;
+}
+
+// ---- workspaces ---------------------------------------------------------------
+struct GeomState {
+    float2* means2D;         // [V*P]
+    float4* conic_opacity;   // [V*P]
+    float4* rgb_depth;       // [V*P]  r,g,b, view-space z
+    float* cov3D;            // [P*6]  (view independent)
+    uint8_t* clamped;        // [V*P]  bit c set = channel c clamped at 0
+    uint32_t* tiles_touched; // [V*P]
+    uint4* rects;            // [V*P]  (min.x, min.y, width, depth bits) of the touched tile rectangle
+    uint32_t* depth_keys;    // [V*P]  sort key of the per-view depth order
+    uint32_t* order_a;       // [V*P]  ping/pong buffers of the depth sort (values = v*P + idx)
+    uint32_t* order_b;       // [V*P]
+    uint32_t* keys_b;        // [V*P]
+    float* grad_acc;         // [V*P*12] backward accumulators: dmean2D.xy, dconic.xyz, dopacity, dcolor.rgb
+    uint32_t* control;       // counters, scan states, histograms (zeroed by one memset per forward)
+    size_t control_words;
+    size_t bytes;
+    static GeomState carve(void* ws, int V, int P);
+};
+
+struct ImageState {
+    float* final_T;      // [V*H*W]
+    uint32_t* n_contrib; // [V*H*W]
+    uint2* ranges;       // [V*tiles]
+    size_t bytes;
+    static ImageState carve(void* ws, int V, int W, int H);
+};
+
+struct BinState {
+    uint32_t* tiles_a; // [cap] tile id (v*tiles + tile) of each instance, ping
+    uint32_t* tiles_b; // [cap] pong
+    uint32_t* vals_a;  // [cap] Gaussian idx
+    uint32_t* vals_b;  // [cap]
+    uint64_t* keys;    // [cap] optional u64 tile|depth keys (flags bit0)
+    uint32_t* lookback; // onesweep status words
+    size_t lookback_words;
+    size_t bytes;
+    static BinState carve(void* ws, int V, int P, int W, int H, size_t cap);
+};
+
+// control-region layout (u32 words)
+enum {
+    CTRL_NUM_RENDERED = 0,  // instances to sort/render (0 when the binning workspace overflowed)
+    CTRL_OVERFLOW = 1,      // set when the instance count exceeds the capacity
+    CTRL_TICKET_SCAN = 2,   // block ticket of the emit kernel
+    CTRL_N_ENTRIES = 3,     // V*P, element count of the depth sort
+    CTRL_TICKET_DEPTH = 4,  // 4 tickets, one per radix pass of the depth sort
+    CTRL_TICKET_TILE = 8,   // 4 tickets of the tile sort
+    CTRL_HIST_DEPTH = 16,   // 4 passes x 256 bins
+    CTRL_HIST_TILE = CTRL_HIST_DEPTH + 4 * 256,
+    CTRL_SCAN_STATE = CTRL_HIST_TILE + 4 * 256,  // u64 per emit block, then the depth sort's look-back words
+    CTRL_FIXED_WORDS = CTRL_SCAN_STATE,
+};
+
+// ---- radix sort (radix_sort.cu) -------------------------------------------------
+// Stable LSD onesweep sort of (u32 key, u32 value) pairs on key bits [0, end_bit).
+// n is read from the device (n_dev), n_max bounds the grid.  Buffers ping-pong; the
+// *side_out tells which side holds the result (0 = *_a, 1 = *_b); returns 0 or an error code.
+#define CSB_SORT_TILE 4096
+static inline size_t sort_lookback_words(size_t n_max, int passes) {
+    return (size_t)passes * ((n_max + CSB_SORT_TILE - 1) / CSB_SORT_TILE + 1) * 256;
+}
+// Which buffer side (0 = *_a, 1 = *_b) holds the tile-sorted instance list.
+static inline int sorted_side(size_t total_tiles) {
+    const int bits = higher_msb((uint32_t)total_tiles);
+    return ((bits + 7) / 8) & 1;
+}
+int fill_view_batch(struct ViewBatch& vb, int num_views, const csb_view* views, int P, int width, int height);
+int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
+                     const uint32_t* n_dev, size_t n_max, int end_bit, uint32_t* hist /*4x256, zeroed*/,
+                     uint32_t* tickets /*4, zeroed*/, uint32_t* lookback /*zeroed*/, int* side_out,
+                     cudaStream_t stream);
+
+}  // namespace csb

@@ -1,0 +1,570 @@
+// Forward pass of the tile rasterizer: preprocess -> depth order -> emit -> tile sort -> ranges -> render.
+//
+// Replaces CudaRasterizer::Rasterizer::forward (RAST/cuda_rasterizer/rasterizer_impl.cu:198-339)
+// and its kernels preprocessCUDA / duplicateWithKeys / identifyTileRanges / renderCUDA
+// (forward.cu:155-256, rasterizer_impl.cu:70-138, forward.cu:261-379).
+#include "rasterize_math.cuh"
+
+namespace csb {
+
+// ----------------------------------------------------------------------------------
+// workspaces
+// ----------------------------------------------------------------------------------
+static inline size_t scan_blocks(int V, int P) { return ((size_t)V * P + 255) / 256; }
+
+GeomState GeomState::carve(void* ws, int V, int P) {
+    GeomState g;
+    Carver c(ws);
+    const size_t n = (size_t)V * P;
+    g.means2D = c.take<float2>(n);
+    g.conic_opacity = c.take<float4>(n);
+    g.rgb_depth = c.take<float4>(n);
+    g.cov3D = c.take<float>((size_t)P * 6);
+    g.clamped = c.take<uint8_t>(n);
+    g.tiles_touched = c.take<uint32_t>(n);
+    g.rects = c.take<uint4>(n);
+    g.depth_keys = c.take<uint32_t>(n);
+    g.order_a = c.take<uint32_t>(n);
+    g.order_b = c.take<uint32_t>(n);
+    g.keys_b = c.take<uint32_t>(n);
+    g.grad_acc = c.take<float>(n * 12);
+    g.control_words = CTRL_FIXED_WORDS + 2 * (scan_blocks(V, P) + 1) + sort_lookback_words(n, 4);
+    g.control = c.take<uint32_t>(g.control_words);
+    g.bytes = c.total();
+    return g;
+}
+
+ImageState ImageState::carve(void* ws, int V, int W, int H) {
+    ImageState s;
+    Carver c(ws);
+    const size_t npix = (size_t)V * W * H;
+    const size_t tiles = (size_t)V * ((W + CSB_TILE_X - 1) / CSB_TILE_X) * ((H + CSB_TILE_Y - 1) / CSB_TILE_Y);
+    s.final_T = c.take<float>(npix);
+    s.n_contrib = c.take<uint32_t>(npix);
+    s.ranges = c.take<uint2>(tiles);
+    s.bytes = c.total();
+    return s;
+}
+
+BinState BinState::carve(void* ws, int V, int P, int W, int H, size_t cap) {
+    (void)V; (void)P; (void)W; (void)H;
+    BinState b;
+    Carver c(ws);
+    b.tiles_a = c.take<uint32_t>(cap);
+    b.tiles_b = c.take<uint32_t>(cap);
+    b.vals_a = c.take<uint32_t>(cap);
+    b.vals_b = c.take<uint32_t>(cap);
+    b.keys = c.take<uint64_t>(cap);
+    b.lookback_words = sort_lookback_words(cap, 4);
+    b.lookback = c.take<uint32_t>(b.lookback_words);
+    b.bytes = c.total();
+    return b;
+}
+
+// ----------------------------------------------------------------------------------
+// preprocess: one thread per (view, Gaussian)
+// ----------------------------------------------------------------------------------
+__device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float* __restrict__ sh, const float3 pos,
+                                            const float3 campos, uint8_t& clamped) {
+    // direction from the camera, normalised by division (forward.cu:27-29)
+    float3 dir = make_float3(pos.x - campos.x, pos.y - campos.y, pos.z - campos.z);
+    const float len = sqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+    dir.x = dir.x / len;
+    dir.y = dir.y / len;
+    dir.z = dir.z / len;
+    const float x = dir.x, y = dir.y, z = dir.z;
+    float res[3];
+    (void)M;
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+#define SHC(k) sh[(k) * 3 + ch]
+        float r = kSH_C0 * SHC(0);
+        if (deg > 0) {
+            r = r - kSH_C1 * y * SHC(1) + kSH_C1 * z * SHC(2) - kSH_C1 * x * SHC(3);
+            if (deg > 1) {
+                const float xx = x * x, yy = y * y, zz = z * z;
+                const float xy = x * y, yz = y * z, xz = x * z;
+                r = r + kSH_C2[0] * xy * SHC(4) + kSH_C2[1] * yz * SHC(5) +
+                    kSH_C2[2] * (2.0f * zz - xx - yy) * SHC(6) + kSH_C2[3] * xz * SHC(7) +
+                    kSH_C2[4] * (xx - yy) * SHC(8);
+                if (deg > 2) {
+                    r = r + kSH_C3[0] * y * (3.0f * xx - yy) * SHC(9) + kSH_C3[1] * xy * z * SHC(10) +
+                        kSH_C3[2] * y * (4.0f * zz - xx - yy) * SHC(11) +
+                        kSH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SHC(12) +
+                        kSH_C3[4] * x * (4.0f * zz - xx - yy) * SHC(13) + kSH_C3[5] * z * (xx - yy) * SHC(14) +
+                        kSH_C3[6] * x * (xx - 3.0f * yy) * SHC(15);
+                }
+            }
+        }
+#undef SHC
+        r += 0.5f;
+        res[ch] = r;
+    }
+    clamped = (uint8_t)((res[0] < 0 ? 1 : 0) | (res[1] < 0 ? 2 : 0) | (res[2] < 0 ? 4 : 0));
+    return make_float3(fmaxf(res[0], 0.0f), fmaxf(res[1], 0.0f), fmaxf(res[2], 0.0f));
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ means3D,
+                  const float* __restrict__ scales, float scale_modifier, const float* __restrict__ rotations,
+                  const float* __restrict__ opacities, const float* __restrict__ shs,
+                  const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
+                  int* __restrict__ radii, GeomState g) {
+    const size_t e = (size_t)blockIdx.x * 256 + threadIdx.x;  // entry = v*P + idx
+    const size_t n = (size_t)vb.V * vb.P;
+    if (e == 0) g.control[CTRL_N_ENTRIES] = (uint32_t)n;  // element count of the depth sort
+    if (e >= n) return;
+    const int v = (int)(e / vb.P);
+    const int idx = (int)(e - (size_t)v * vb.P);
+
+    radii[e] = 0;
+    g.tiles_touched[e] = 0;
+    g.order_a[e] = (uint32_t)e;
+    g.depth_keys[e] = 0xFFFFFFFFu;
+
+    const float* __restrict__ vm = vb.viewmatrix[v];
+    const float* __restrict__ pm = vb.projmatrix[v];
+    const float3 p_orig = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
+
+    // near culling (auxiliary.h:139-164): only view-space z is tested
+    const float3 p_view = xform_point_4x3(p_orig, vm);
+    if (p_view.z <= 0.2f) return;
+
+    const float4 p_hom = xform_point_4x4(p_orig, pm);
+    const float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    const float3 p_proj = make_float3(p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w);
+
+    float cov6[6];
+    if (cov3D_precomp != nullptr) {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) cov6[i] = cov3D_precomp[6 * (size_t)idx + i];
+    } else {
+        const float3 s = make_float3(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]);
+        const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+        cov3d_from_scale_rot(s, scale_modifier, q, cov6);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) g.cov3D[6 * (size_t)idx + i] = cov6[i];  // same bits from every view
+    }
+
+    const EwaProj ep = ewa_project(p_orig, vb.focal_x[v], vb.focal_y[v], vb.tan_fovx[v], vb.tan_fovy[v], vm);
+    const float3 cov = cov2d_from_proj(ep, cov6);
+
+    const float det = (cov.x * cov.z - cov.y * cov.y);
+    if (det == 0.0f) return;
+    const float det_inv = 1.f / det;
+    const float3 conic = make_float3(cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv);
+
+    const float mid = 0.5f * (cov.x + cov.z);
+    const float lambda1 = mid + sqrtf(fmaxf(0.1f, mid * mid - det));
+    const float lambda2 = mid - sqrtf(fmaxf(0.1f, mid * mid - det));
+    const float my_radius = ceilf(3.f * sqrtf(fmaxf(lambda1, lambda2)));
+    const float2 point_image = make_float2(ndc_to_pix(p_proj.x, vb.W), ndc_to_pix(p_proj.y, vb.H));
+    uint2 rect_min, rect_max;
+    tile_rect(point_image, (int)my_radius, vb.gx, vb.gy, rect_min, rect_max);
+    const uint32_t area = (rect_max.x - rect_min.x) * (rect_max.y - rect_min.y);
+    if (area == 0) return;
+
+    float3 rgb;
+    uint8_t clamped = 0;
+    if (colors_precomp == nullptr) {
+        const float3 campos = make_float3(vb.campos[v][0], vb.campos[v][1], vb.campos[v][2]);
+        rgb = sh_to_rgb(D, M, shs + (size_t)idx * M * 3, p_orig, campos, clamped);
+    } else {
+        rgb = make_float3(colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]);
+    }
+
+    radii[e] = (int)my_radius;
+    g.means2D[e] = point_image;
+    g.conic_opacity[e] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
+    g.rgb_depth[e] = make_float4(rgb.x, rgb.y, rgb.z, p_view.z);
+    g.clamped[e] = clamped;
+    g.tiles_touched[e] = area;
+    g.rects[e] = make_uint4(rect_min.x, rect_min.y, rect_max.x - rect_min.x, __float_as_uint(p_view.z));
+    g.depth_keys[e] = __float_as_uint(p_view.z);
+}
+
+// ----------------------------------------------------------------------------------
+// emit: chained scan of tiles_touched in depth order + warp-cooperative instance emission
+// ----------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t ld_volatile_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u64(uint64_t* p, uint64_t v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+constexpr uint64_t SCAN_AGG = 1ull << 62;
+constexpr uint64_t SCAN_INC = 2ull << 62;
+constexpr uint64_t SCAN_VAL = (1ull << 62) - 1;
+
+__global__ void __launch_bounds__(256)
+emit_kernel(const ViewBatch vb, const uint32_t* __restrict__ order, GeomState g, uint64_t* __restrict__ scan_state,
+            uint32_t* __restrict__ out_tiles, uint32_t* __restrict__ out_vals, size_t capacity,
+            uint32_t* __restrict__ num_rendered_out) {
+    __shared__ uint32_t s_block;
+    __shared__ uint32_t s_warp_tot[8];
+    __shared__ uint64_t s_excl;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_block = atomicAdd(&g.control[CTRL_TICKET_SCAN], 1u);
+    __syncthreads();
+    const uint32_t blk = s_block;
+    const size_t n = (size_t)vb.V * vb.P;
+    const size_t j = (size_t)blk * 256 + tid;
+
+    uint32_t e = 0, cnt = 0;
+    uint4 rect = make_uint4(0, 0, 1, 0);
+    if (j < n) {
+        e = order[j];
+        cnt = g.tiles_touched[e];
+        if (cnt) rect = g.rects[e];
+    }
+    // exclusive scan inside the warp, then across the block's warps
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    const uint32_t wexcl = incl - cnt;
+    const uint32_t wtotal = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    if (lane == 31) s_warp_tot[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0, block_tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        if (w < warp) warp_off += s_warp_tot[w];
+        block_tot += s_warp_tot[w];
+    }
+    // decoupled look-back over earlier blocks (warp 0)
+    if (warp == 0) {
+        uint64_t excl = 0;
+        if (blk == 0) {
+            if (lane == 0) st_volatile_u64(&scan_state[0], SCAN_INC | block_tot);
+        } else {
+            if (lane == 0) st_volatile_u64(&scan_state[blk], SCAN_AGG | block_tot);
+            int pos = (int)blk - 1;
+            while (true) {
+                const int q = pos - lane;
+                const uint64_t s = q >= 0 ? ld_volatile_u64(&scan_state[q]) : SCAN_INC;
+                const uint32_t ready = __ballot_sync(0xFFFFFFFFu, (s & ~SCAN_VAL) != 0);
+                const uint32_t inc = __ballot_sync(0xFFFFFFFFu, (s & ~SCAN_VAL) == SCAN_INC);
+                if (inc) {
+                    const int fi = __ffs(inc) - 1;  // nearest predecessor holding an inclusive prefix
+                    const uint32_t need = fi == 31 ? 0xFFFFFFFFu : ((1u << (fi + 1)) - 1);
+                    if ((ready & need) != need) continue;
+                    uint64_t part = lane <= fi ? (s & SCAN_VAL) : 0;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
+                    excl += part;
+                    break;
+                }
+                if (ready != 0xFFFFFFFFu) continue;
+                uint64_t part = s & SCAN_VAL;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
+                excl += part;
+                pos -= 32;
+            }
+            if (lane == 0) st_volatile_u64(&scan_state[blk], SCAN_INC | (excl + block_tot));
+        }
+        if (lane == 0) {
+            s_excl = excl;
+            if (blk == gridDim.x - 1) {  // the last block knows the total
+                const uint64_t total = excl + block_tot;
+                const bool overflow = total > capacity;
+                g.control[CTRL_NUM_RENDERED] = overflow ? 0u : (uint32_t)total;  // n of the later stages
+                g.control[CTRL_OVERFLOW] = overflow ? 1u : 0u;
+                num_rendered_out[0] = (uint32_t)min(total, (uint64_t)0xFFFFFFFFull);
+            }
+        }
+    }
+    __syncthreads();
+    const uint64_t warp_base = s_excl + warp_off;
+    if (warp_base + wtotal > capacity) return;  // overflow: the caller grows the workspace and retries
+
+    // flat emission: item k of the warp belongs to the lane g with wexcl[g] <= k < wexcl[g] + cnt[g]
+    const float inv_w = 1.0f / (float)rect.z;
+    for (uint32_t k = lane; k < ((wtotal + 31) & ~31u); k += 32) {
+        int gl = 0;
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) {
+            const int c = gl + s;
+            const uint32_t v = __shfl_sync(0xFFFFFFFFu, wexcl, c & 31);
+            if (c < 32 && v <= k) gl = c;
+        }
+        // skip over lanes without instances that share the same prefix
+        const uint32_t g_excl = __shfl_sync(0xFFFFFFFFu, wexcl, gl);
+        const uint32_t g_min_x = __shfl_sync(0xFFFFFFFFu, rect.x, gl);
+        const uint32_t g_min_y = __shfl_sync(0xFFFFFFFFu, rect.y, gl);
+        const uint32_t g_w = __shfl_sync(0xFFFFFFFFu, rect.z, gl);
+        const float g_inv_w = __shfl_sync(0xFFFFFFFFu, inv_w, gl);
+        const uint32_t g_e = __shfl_sync(0xFFFFFFFFu, e, gl);
+        if (k < wtotal) {
+            const uint32_t local = k - g_excl;
+            const uint32_t ry = (uint32_t)(((float)local + 0.5f) * g_inv_w);
+            const uint32_t rx = local - ry * g_w;
+            const uint32_t view = g_e / (uint32_t)vb.P;
+            const uint32_t tile = view * (uint32_t)vb.tiles + (g_min_y + ry) * (uint32_t)vb.gx + (g_min_x + rx);
+            out_tiles[warp_base + k] = tile;
+            out_vals[warp_base + k] = g_e;
+        }
+    }
+}
+
+// ----------------------------------------------------------------------------------
+// tile ranges (+ optional u64 keys) from the sorted tile ids
+// ----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(const uint32_t* __restrict__ n_dev, const uint32_t* __restrict__ tiles,
+                   const uint32_t* __restrict__ vals, const float4* __restrict__ rgb_depth,
+                   uint2* __restrict__ ranges, uint64_t* __restrict__ keys_out, uint32_t tiles_per_view) {
+    const uint32_t n = *n_dev;
+    const size_t stride = (size_t)gridDim.x * 256;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
+        const uint32_t cur = tiles[i];
+        if (i == 0) {
+            ranges[cur].x = 0;
+        } else {
+            const uint32_t prev = tiles[i - 1];
+            if (cur != prev) {
+                ranges[prev].y = (uint32_t)i;
+                ranges[cur].x = (uint32_t)i;
+            }
+        }
+        if (i == n - 1) ranges[cur].y = n;
+        if (keys_out) {
+            const uint32_t d = __float_as_uint(rgb_depth[vals[i]].w);
+            keys_out[i] = ((uint64_t)(cur % tiles_per_view) << 32) | d;
+        }
+    }
+}
+
+// ----------------------------------------------------------------------------------
+// render: one 16x16 tile per block, front-to-back alpha compositing
+// ----------------------------------------------------------------------------------
+constexpr int RENDER_BATCH = 256;
+
+__global__ void __launch_bounds__(CSB_TILE_PIX)
+render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+                      const float4* __restrict__ rgb_depth, float* __restrict__ final_T,
+                      uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
+                      float* __restrict__ out_depth) {
+    __shared__ float2 s_xy[RENDER_BATCH];
+    __shared__ float4 s_co[RENDER_BATCH];
+    __shared__ float4 s_cd[RENDER_BATCH];
+
+    const int v = blockIdx.z;
+    const int tid = threadIdx.x;
+    // a warp covers an 8x4 pixel patch of the tile (compact footprint -> coherent early-outs)
+    const int warp = tid >> 5, lane = tid & 31;
+    const int lx = (warp & 1) * 8 + (lane & 7);
+    const int ly = (warp >> 1) * 4 + (lane >> 3);
+    const uint32_t px = blockIdx.x * CSB_TILE_X + lx;
+    const uint32_t py = blockIdx.y * CSB_TILE_Y + ly;
+    const bool inside = px < (uint32_t)vb.W && py < (uint32_t)vb.H;
+    const float pxf = (float)px, pyf = (float)py;
+
+    const uint2 range = ranges[(size_t)v * vb.tiles + blockIdx.y * vb.gx + blockIdx.x];
+    int todo = (int)(range.y - range.x);
+    const int rounds = (todo + RENDER_BATCH - 1) / RENDER_BATCH;
+
+    bool done = !inside;
+    float T = 1.0f;
+    uint32_t contributor = 0, last_contributor = 0;
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dacc = 0.f;
+
+    for (int r = 0; r < rounds; ++r, todo -= RENDER_BATCH) {
+        if (__syncthreads_count(done) == CSB_TILE_PIX) break;
+        const int progress = r * RENDER_BATCH + tid;
+        if (range.x + progress < range.y) {
+            const uint32_t id = point_list[range.x + progress];
+            s_xy[tid] = means2D[id];
+            s_co[tid] = conic_opacity[id];
+            s_cd[tid] = rgb_depth[id];
+        }
+        __syncthreads();
+        const int cnt = min(RENDER_BATCH, todo);
+        for (int j = 0; !done && j < cnt; ++j) {
+            contributor++;
+            const float2 xy = s_xy[j];
+            const float dx = xy.x - pxf, dy = xy.y - pyf;
+            const float4 con_o = s_co[j];
+            const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, con_o.w * expf(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) {
+                done = true;
+                continue;
+            }
+            const float4 cd = s_cd[j];
+            C0 += cd.x * alpha * T;
+            C1 += cd.y * alpha * T;
+            C2 += cd.z * alpha * T;
+            Dacc += cd.w * alpha * T;
+            T = test_T;
+            last_contributor = contributor;
+        }
+    }
+    if (inside) {
+        const size_t hw = (size_t)vb.W * vb.H;
+        const size_t pix = (size_t)py * vb.W + px;
+        const float* __restrict__ bg = vb.background[v];
+        final_T[v * hw + pix] = T;
+        n_contrib[v * hw + pix] = last_contributor;
+        out_color[(v * 3 + 0) * hw + pix] = C0 + T * bg[0];
+        out_color[(v * 3 + 1) * hw + pix] = C1 + T * bg[1];
+        out_color[(v * 3 + 2) * hw + pix] = C2 + T * bg[2];
+        out_depth[v * hw + pix] = Dacc;
+    }
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ vm,
+                                    uint8_t* __restrict__ present) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const float3 p = make_float3(means3D[3 * i], means3D[3 * i + 1], means3D[3 * i + 2]);
+    present[i] = xform_point_4x3(p, vm).z > 0.2f ? 1 : 0;
+}
+
+}  // namespace csb
+
+// ----------------------------------------------------------------------------------
+// host side (C-ABI)
+// ----------------------------------------------------------------------------------
+namespace csb {
+int fill_view_batch(ViewBatch& vb, int num_views, const csb_view* views, int P, int width, int height) {
+    if (num_views < 1 || num_views > CSB_MAX_VIEWS || views == nullptr || P < 0 || width < 1 || height < 1)
+        return CSB_ERR_BAD_ARG;
+    vb.V = num_views;
+    vb.P = P;
+    vb.W = width;
+    vb.H = height;
+    vb.gx = (width + CSB_TILE_X - 1) / CSB_TILE_X;
+    vb.gy = (height + CSB_TILE_Y - 1) / CSB_TILE_Y;
+    vb.tiles = vb.gx * vb.gy;
+    for (int v = 0; v < num_views; ++v) {
+        // rasterizer_impl.cu:226-227
+        vb.focal_y[v] = height / (2.0f * views[v].tan_fovy);
+        vb.focal_x[v] = width / (2.0f * views[v].tan_fovx);
+        vb.tan_fovx[v] = views[v].tan_fovx;
+        vb.tan_fovy[v] = views[v].tan_fovy;
+        vb.viewmatrix[v] = views[v].viewmatrix;
+        vb.projmatrix[v] = views[v].projmatrix;
+        vb.campos[v] = views[v].campos;
+        vb.background[v] = views[v].background;
+    }
+    return 0;
+}
+}  // namespace csb
+
+using namespace csb;
+
+extern "C" {
+
+size_t csb_rasterize_geom_bytes(int num_views, int P) { return GeomState::carve(nullptr, num_views, P).bytes; }
+size_t csb_rasterize_image_bytes(int num_views, int width, int height) {
+    return ImageState::carve(nullptr, num_views, width, height).bytes;
+}
+size_t csb_rasterize_binning_bytes(int num_views, int P, int width, int height, size_t capacity) {
+    return BinState::carve(nullptr, num_views, P, width, height, capacity).bytes;
+}
+
+int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
+                          const float* means3D, const float* shs, const float* colors_precomp,
+                          const float* opacities, const float* scales, float scale_modifier,
+                          const float* rotations, const float* cov3D_precomp, int prefiltered, void* geom_ws,
+                          size_t geom_bytes, void* image_ws, size_t image_bytes, void* binning_ws,
+                          size_t binning_bytes, size_t binning_capacity, float* out_color, float* out_depth,
+                          int* radii, uint32_t* num_rendered_dev, uint32_t* num_rendered_host, int flags,
+                          void* stream_) {
+    (void)prefiltered;  // the reference only uses it to trap on a culled point (auxiliary.h:155-159)
+    cudaStream_t stream = (cudaStream_t)stream_;
+    ViewBatch vb;
+    int rc = fill_view_batch(vb, num_views, views, P, width, height);
+    if (rc) return rc;
+    if (shs == nullptr && colors_precomp == nullptr) return CSB_ERR_BAD_ARG;
+    if (cov3D_precomp == nullptr && (scales == nullptr || rotations == nullptr)) return CSB_ERR_BAD_ARG;
+    if (shs != nullptr && (M < (D + 1) * (D + 1) || D < 0 || D > 3)) return CSB_ERR_BAD_ARG;
+    if (!out_color || !out_depth || !radii || !num_rendered_dev) return CSB_ERR_BAD_ARG;
+    if ((size_t)num_views * (size_t)P >= (1ull << 31) || binning_capacity >= (1ull << 30)) return CSB_ERR_UNSUPPORTED;
+
+    GeomState g = GeomState::carve(geom_ws, num_views, P);
+    ImageState im = ImageState::carve(image_ws, num_views, width, height);
+    BinState b = BinState::carve(binning_ws, num_views, P, width, height, binning_capacity);
+    if (geom_bytes < g.bytes || image_bytes < im.bytes || binning_bytes < b.bytes) return CSB_ERR_WORKSPACE;
+    if (!geom_ws || !image_ws || (!binning_ws && binning_capacity > 0)) return CSB_ERR_BAD_ARG;
+
+    const size_t n = (size_t)num_views * P;
+    const size_t total_tiles = (size_t)num_views * vb.tiles;
+    CSB_CUDA_TRY(cudaMemsetAsync(g.control, 0, g.control_words * sizeof(uint32_t), stream));
+    CSB_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, total_tiles * sizeof(uint2), stream));
+    dim3 tgrid(vb.gx, vb.gy, num_views);
+    if (n > 0) {
+        const unsigned blocks = (unsigned)((n + 255) / 256);
+        preprocess_kernel<<<blocks, 256, 0, stream>>>(vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
+                                                      shs, cov3D_precomp, colors_precomp, radii, g);
+        CSB_LAUNCH_CHECK();
+        // depth order of the (view, Gaussian) entries
+        uint32_t* scan_state = g.control + CTRL_SCAN_STATE;
+        uint32_t* depth_lookback = scan_state + 2 * (blocks + 1);
+        int side = 0;
+        rc = radix_sort_pairs(g.depth_keys, g.keys_b, g.order_a, g.order_b, g.control + CTRL_N_ENTRIES, n, 32,
+                              g.control + CTRL_HIST_DEPTH, g.control + CTRL_TICKET_DEPTH, depth_lookback, &side,
+                              stream);
+        if (rc) return rc;
+        const uint32_t* order = side ? g.order_b : g.order_a;
+        emit_kernel<<<blocks, 256, 0, stream>>>(vb, order, g, (uint64_t*)scan_state, b.tiles_a, b.vals_a,
+                                                binning_capacity, num_rendered_dev);
+        CSB_LAUNCH_CHECK();
+        if (binning_capacity > 0) {
+            CSB_CUDA_TRY(cudaMemsetAsync(b.lookback, 0, b.lookback_words * sizeof(uint32_t), stream));
+            const int tile_bits = higher_msb((uint32_t)total_tiles);
+            int tside = 0;
+            rc = radix_sort_pairs(b.tiles_a, b.tiles_b, b.vals_a, b.vals_b, g.control + CTRL_NUM_RENDERED,
+                                  binning_capacity, tile_bits, g.control + CTRL_HIST_TILE,
+                                  g.control + CTRL_TICKET_TILE, b.lookback, &tside, stream);
+            if (rc) return rc;
+            // the final order always lives in *_a for the consumers: copy back if it ended in *_b
+            const uint32_t* st = tside ? b.tiles_b : b.tiles_a;
+            const uint32_t* sv = tside ? b.vals_b : b.vals_a;
+            int rblocks = (int)((binning_capacity + 255) / 256);
+            if (rblocks > 148 * 16) rblocks = 148 * 16;
+            tile_ranges_kernel<<<rblocks, 256, 0, stream>>>(g.control + CTRL_NUM_RENDERED, st, sv, g.rgb_depth,
+                                                            im.ranges, (flags & 1) ? b.keys : nullptr,
+                                                            (uint32_t)vb.tiles);
+            CSB_LAUNCH_CHECK();
+            render_forward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, sv, g.means2D, g.conic_opacity,
+                                                                     g.rgb_depth, im.final_T, im.n_contrib, out_color,
+                                                                     out_depth);
+            CSB_LAUNCH_CHECK();
+            if (tside != sorted_side(total_tiles)) return CSB_ERR_UNSUPPORTED;  // consumers recompute the side
+        }
+    } else {
+        CSB_CUDA_TRY(cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream));
+        render_forward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity,
+                                                                 g.rgb_depth, im.final_T, im.n_contrib, out_color,
+                                                                 out_depth);
+        CSB_LAUNCH_CHECK();
+    }
+    if (num_rendered_host)
+        CSB_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                     stream));
+    return 0;
+}
+
+int csb_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix, uint8_t* present,
+                     void* stream_) {
+    (void)projmatrix;
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return CSB_ERR_BAD_ARG;
+    if (P == 0) return 0;
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, viewmatrix, present);
+    CSB_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

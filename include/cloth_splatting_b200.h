@@ -1,0 +1,142 @@
+/*
+ * cloth_splatting_b200.h -- C-ABI of the B200-native (sm_100a) hot path of
+ * KTH-RPL/cloth-splatting.
+ *
+ * Every entry point takes raw device pointers, sizes, a CUDA stream (passed as
+ * void* so that no CUDA header is needed to bind it) and caller-provided
+ * workspaces.  The library allocates nothing, keeps no state between calls and
+ * is re-entrant per stream.  Return value: 0 = ok, CSB_ERR_* (<0) = usage error,
+ * >0 = cudaError_t of the failing launch.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo,
+ * RAST = submodules/depth-diff-gaussian-rasterization, KNN = submodules/simple-knn):
+ *   csb_rasterize_forward   <- CudaRasterizer::Rasterizer::forward   RAST/cuda_rasterizer/rasterizer.h:31-54
+ *                              (pybind: rasterize_gaussians          RAST/ext.cpp:16, rasterize_points.cu:35-117)
+ *   csb_rasterize_backward  <- CudaRasterizer::Rasterizer::backward  RAST/cuda_rasterizer/rasterizer.h:56-85
+ *                              (pybind: rasterize_gaussians_backward RAST/ext.cpp:17, rasterize_points.cu:119-198)
+ *   csb_mark_visible        <- CudaRasterizer::Rasterizer::markVisible RAST/cuda_rasterizer/rasterizer.h:24-29
+ *                              (pybind: mark_visible                 RAST/ext.cpp:18, rasterize_points.cu:200-219)
+ *   csb_dist_cuda2          <- SimpleKNN::knn                        KNN/simple_knn.h:15-19
+ *                              (pybind: distCUDA2                    KNN/ext.cpp:15-17, spatial.cu:15-26)
+ *   csb_gnn_*               <- EncodeProcessDecode.forward           meshnet/graph_network.py:387-408
+ *                              (PyG MessagePassing.propagate + torch addmm/layer_norm/scatter_add_)
+ *   csb_mesh_xyz_*          <- MultiGaussianMesh.get_xyz             scene_reconstruction/gaussian_mesh.py:151-169
+ */
+#ifndef CLOTH_SPLATTING_B200_H
+#define CLOTH_SPLATTING_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CSB_OK 0
+#define CSB_ERR_BAD_ARG (-1)
+#define CSB_ERR_WORKSPACE (-2) /* a caller-provided workspace is too small */
+#define CSB_ERR_UNSUPPORTED (-3)
+
+#define CSB_MAX_VIEWS 16 /* views rendered by one launch set */
+
+/* ABI version; bumped whenever a signature changes. */
+int csb_abi_version(void);
+/* Human readable string for a return code of this library. */
+const char* csb_error_string(int code);
+
+/* ------------------------------------------------------------------------- *
+ * Rasterizer
+ * ------------------------------------------------------------------------- */
+
+/* One camera view.  The four pointers are DEVICE pointers, exactly the tensors
+ * GaussianRasterizationSettings carries (RAST/diff_gaussian_rasterization/__init__.py:157-169):
+ * viewmatrix / projmatrix are the 16 floats of the transposed 4x4 matrices, consumed as
+ * out_k = m[k] x + m[4+k] y + m[8+k] z + m[12+k]  (RAST/cuda_rasterizer/auxiliary.h:58-77). */
+typedef struct csb_view {
+    const float* viewmatrix; /* f32[16] device */
+    const float* projmatrix; /* f32[16] device */
+    const float* campos;     /* f32[3]  device */
+    const float* background; /* f32[3]  device */
+    float tan_fovx, tan_fovy;
+} csb_view;
+
+/* Sizes of the three caller-owned byte workspaces (the reference's geomBuffer,
+ * imgBuffer and binningBuffer, rasterize_points.cu:74-79).  `capacity` is the number
+ * of (Gaussian, tile) instances the binning workspace can hold. */
+size_t csb_rasterize_geom_bytes(int num_views, int P);
+size_t csb_rasterize_image_bytes(int num_views, int width, int height);
+size_t csb_rasterize_binning_bytes(int num_views, int P, int width, int height, size_t capacity);
+/* Inverse of the above: the largest capacity whose binning workspace fits in `bytes` (the backward
+ * pass derives the layout from the size of the buffer the forward pass was given). */
+size_t csb_rasterize_binning_capacity(int num_views, int P, int width, int height, size_t bytes);
+
+/* Forward for `num_views` (1..CSB_MAX_VIEWS) views of the same P Gaussians and the same
+ * image size.  With num_views == 1 this is a drop-in for Rasterizer::forward.
+ *
+ *   means3D f32[P,3]; shs f32[P,M,3] or NULL; colors_precomp f32[P,3] or NULL;
+ *   opacities f32[P]; scales f32[P,3] + rotations f32[P,4] (r,x,y,z; NOT normalised,
+ *   forward.cu:127) or cov3D_precomp f32[P,6].
+ *   out_color f32[V,3,H,W]; out_depth f32[V,1,H,W]; radii i32[V,P].
+ *
+ * The number of instances is only known on the device.  It is written to
+ * num_rendered_dev[0] (u32, device) and, if num_rendered_host is not NULL, copied
+ * asynchronously on `stream` to that (pinned) host word.  If it exceeds
+ * `binning_capacity` nothing is rendered and the caller must grow the binning
+ * workspace to csb_rasterize_binning_bytes(..., num_rendered) and call again
+ * (the reference does the same resize after its blocking cudaMemcpy,
+ * rasterizer_impl.cu:280-286).  flags: bit0 = also write the sorted u64
+ * tile|depth keys (rasterizer_impl.cu:70-111 layout) for inspection. */
+int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
+                          const float* means3D, const float* shs, const float* colors_precomp,
+                          const float* opacities, const float* scales, float scale_modifier,
+                          const float* rotations, const float* cov3D_precomp, int prefiltered,
+                          void* geom_ws, size_t geom_bytes, void* image_ws, size_t image_bytes,
+                          void* binning_ws, size_t binning_bytes, size_t binning_capacity,
+                          float* out_color, float* out_depth, int* radii, uint32_t* num_rendered_dev,
+                          uint32_t* num_rendered_host, int flags, void* stream);
+
+/* Backward of the colour output (the depth output has no backward in the reference,
+ * RAST/diff_gaussian_rasterization/__init__.py:101-129).  Needs the three workspaces of
+ * the matching forward call untouched.  Gradients are summed over the views, except
+ * dL_dmeans2D f32[V,P,3] which the caller consumes per view
+ * (scene_reconstruction/train_utils.py:290-292).
+ *   dL_dpix f32[V,3,H,W];
+ *   outputs (all overwritten, no pre-zeroing needed): dL_dmeans3D f32[P,3],
+ *   dL_dcolors f32[P,3] (only meaningful with colors_precomp), dL_dopacity f32[P],
+ *   dL_dcov3D f32[P,6], dL_dsh f32[P,M,3] (may be NULL when shs is NULL),
+ *   dL_dscales f32[P,3], dL_drotations f32[P,4]. */
+int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
+                           const float* means3D, const float* shs, const float* colors_precomp,
+                           const float* scales, float scale_modifier, const float* rotations,
+                           const float* cov3D_precomp, const int* radii, const void* geom_ws,
+                           const void* image_ws, const void* binning_ws, size_t binning_capacity,
+                           const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                           float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                           float* dL_drotations, void* stream);
+
+/* present[i] = (viewmatrix * means3D[i]).z > 0.2   (auxiliary.h:139-164) */
+int csb_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/* Device pointers of the arrays carved out of the workspaces, for parity tests
+ * (counterpart of GeometryState/ImageState/BinningState::fromChunk, rasterizer_impl.h:21-73).
+ * names: "means2D" f32x2[V,P]; "conic_opacity" f32x4[V,P]; "rgb_depth" f32x4[V,P] (r,g,b,view z);
+ *        "cov3D" f32[P,6]; "clamped" u8[V,P] (bit c = channel c clamped); "tiles_touched" u32[V,P];
+ *        "final_T" f32[V,H*W]; "n_contrib" u32[V,H*W]; "ranges" u32x2[V*tiles];
+ *        "point_list" u32[R]; "point_tiles" u32[R]; "keys" u64[R] (flags bit0 only).
+ * Returns NULL for an unknown name. */
+void* csb_rasterize_state_ptr(const char* name, int num_views, int P, int width, int height,
+                              size_t binning_capacity, void* geom_ws, void* image_ws, void* binning_ws);
+
+/* ------------------------------------------------------------------------- *
+ * simple-knn
+ * ------------------------------------------------------------------------- */
+size_t csb_dist_cuda2_bytes(int P);
+/* mean_dists[i] = mean of the 3 smallest squared distances from points[i] to the
+ * other points (KNN/simple_knn.cu:147-183).  points f32[P,3], mean_dists f32[P]. */
+int csb_dist_cuda2(int P, const float* points, float* mean_dists, void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CLOTH_SPLATTING_B200_H */

@@ -135,6 +135,14 @@ void* ref_state_ptr(void* h, const char* name) {
     return nullptr;
 }
 
+// Device-to-device copy of one carved sub-array into a caller buffer (synchronous).
+int ref_copy_state(void* h, const char* name, void* dst, size_t nbytes) {
+    void* src = ref_state_ptr(h, name);
+    if (!src) return -1;
+    cudaError_t e = cudaMemcpy(dst, src, nbytes, cudaMemcpyDeviceToDevice);
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
 // simple-knn: KNN/spatial.cu:15-26 minus torch.
 int ref_dist_cuda2(int P, float* points, float* mean_dists) {
     SimpleKNN::knn(P, (float3*)points, mean_dists);
