@@ -1,0 +1,472 @@
+"""Headline benchmark: rasterizer fwd+bwd Mpix/s on BASELINE.json configs[1] (C2).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c2|c3|c4]
+
+One "step" = forward + backward of every view of this rank's view batch (C2: 4 views at 800x800 of the
+10 108 mesh-anchored Gaussians of the 20x20 cloth).  With N > 1 (torchrun) every rank renders its own 4
+ring views of the replicated Gaussians and the parameter gradients are summed with ONE flat NCCL
+all-reduce per step ("scaling": "weak").
+
+  value   device-resident inputs, C-ABI calls back to back, CUDA events, L2 flushed between steps
+  e2e     the package's public API (rasterize_views + autograd) with pinned HOST buffers: H2D of the
+          Gaussian parameters and dL/dpixel, D2H of the parameter gradients inside the timed region
+  --impl reference: the reference's own CUDA rasterizer (oracle/_ref/libref_cuda.so, compiled unmodified
+          from /root/reference) driven view by view the way its Python loop does, on the same inputs.
+          The reference has no CPU implementation of the rasterizer; if the .so is absent the CPU
+          oracle port is timed instead on a bounded sample.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "cloth-splatting_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+import csb_synth as S  # noqa: E402
+
+PARAM_NAMES = ("means3D", "scales", "rotations", "opacities", "shs")
+
+
+# ------------------------------------------------------------------------------------------
+# workloads
+# ------------------------------------------------------------------------------------------
+def make_workload(name, rank, world):
+    if name == "c2":
+        g = S.mesh_gaussians(20, 14, 1)
+        center = g["verts"].mean(0)
+        cams = S.ring_cameras(4 * world, 800, 800, 0.6911, center)[rank::world]
+        desc = "C2: 20x20 cloth, 10108 mesh-anchored Gaussians, SH deg 3, 4 ring views 800x800 per GPU, fwd+bwd"
+    elif name == "c3":
+        g, cams = S.config_c3(1_000_000, 1920, 1080)
+        desc = "C3: 1M random Gaussians, SH deg 3, one 1920x1080 view per GPU, fwd+bwd"
+    elif name == "c4":
+        g, cams = S.config_c4(100_000, 64, 800)
+        per = max(1, 64 // world)
+        cams = cams[rank * per:(rank + 1) * per]
+        desc = "C4: 100k Gaussians x 64 views 800x800 split over the GPUs, fwd+bwd + gradient all-reduce"
+    else:
+        raise SystemExit(f"unknown workload {name}")
+    g = {k: g[k] for k in PARAM_NAMES}
+    H, W = cams[0].image_height, cams[0].image_width
+    dl = S.pixel_grad(len(cams), H, W, seed=5 + rank)
+    return g, cams, dl, desc
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def l2_flusher(dev):
+    buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def flush():
+        buf.fill_(1)
+    return flush
+
+
+def settings_list(cams, dev, sh_degree=3):
+    from diff_gaussian_rasterization import GaussianRasterizationSettings
+
+    out = []
+    for c in cams:
+        out.append(GaussianRasterizationSettings(
+            image_height=c.image_height, image_width=c.image_width, tanfovx=c.tanfovx, tanfovy=c.tanfovy,
+            bg=torch.ones(3, device=dev), scale_modifier=1.0,
+            viewmatrix=torch.from_numpy(c.world_view_transform).to(dev),
+            projmatrix=torch.from_numpy(c.full_proj_transform).to(dev), sh_degree=sh_degree,
+            campos=torch.from_numpy(c.camera_center).to(dev), prefiltered=False, debug=False))
+    return out
+
+
+def batches(n, size=16):
+    return [list(range(i, min(n, i + size))) for i in range(0, n, size)]
+
+
+# ------------------------------------------------------------------------------------------
+# product arm
+# ------------------------------------------------------------------------------------------
+def run_b200(args, rank, world, dev):
+    import csb_cabi
+    import diff_gaussian_rasterization as dgr
+    import torch.distributed as dist
+
+    lib = csb_cabi.lib()
+    g_np, cams, dl_np, desc = make_workload(args.workload, rank, world)
+    V, H, W = len(cams), cams[0].image_height, cams[0].image_width
+    P = g_np["means3D"].shape[0]
+    gd = {k: torch.from_numpy(v).to(dev) for k, v in g_np.items()}
+    dl = torch.from_numpy(dl_np).to(dev)
+    sl = settings_list(cams, dev)
+    view_batches = batches(V)
+    flush = l2_flusher(dev)
+    e = torch.Tensor([])
+    stream = torch.cuda.current_stream()
+
+    def views_of(b):
+        return [(sl[v].viewmatrix, sl[v].projmatrix, sl[v].campos, sl[v].bg, sl[v].tanfovx, sl[v].tanfovy) for v in b]
+
+    grad_flat = torch.zeros(P * 59, dtype=torch.float32, device=dev)  # 3+3+4+1+48 floats per Gaussian
+
+    def pack(grads):
+        o = 0
+        for t in grads:
+            n = t.numel()
+            grad_flat[o:o + n].copy_(t.reshape(-1)) if len(view_batches) == 1 else grad_flat[o:o + n].add_(t.reshape(-1))
+            o += n
+
+    def device_step():
+        """Device-resident step through the C-ABI wrapper layer (no autograd)."""
+        if len(view_batches) > 1:
+            grad_flat.zero_()
+        R_total = 0
+        for b in view_batches:
+            vs = views_of(b)
+            fwd = dgr._forward_views(vs, gd["means3D"], e, gd["opacities"], gd["scales"], gd["rotations"], 1.0, e, H, W,
+                                     gd["shs"], 3, False)
+            R, color, depth, radii, geom, binning, img = fwd
+            R_total += R
+            gb = dgr._backward_views(vs, gd["means3D"], radii, e, gd["scales"], gd["rotations"], 1.0, e, H, W,
+                                     dl[b[0]:b[-1] + 1], gd["shs"], 3, geom, binning, img)
+            dm2, dcol, dop, dm3, dcov, dsh, dsc, drot = gb
+            pack((dm3, dsc, drot, dop, dsh))
+        if world > 1:
+            dist.all_reduce(grad_flat)
+        return R_total
+
+    def timed(step_fn, steps, warmup):
+        for _ in range(warmup):
+            step_fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = []
+        for _ in range(steps):
+            flush()
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            step_fn()
+            b_.record(stream)
+            b_.synchronize()
+            ms.append(a.elapsed_time(b_))
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        total = torch.tensor([sum(ms)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(total, op=dist.ReduceOp.MAX)
+        return float(total.item()) / steps, ms
+
+    sampler = ClockSampler(dev.index) if rank == 0 else None
+    launches0 = lib.csb_launch_count()
+    ms_step, ms_all = timed(device_step, args.steps, args.warmup)
+    launches = (lib.csb_launch_count() - launches0) // (args.steps + args.warmup) * args.steps
+    R_step = device_step()
+    torch.cuda.synchronize()
+    mpix = V * H * W / 1e6
+
+    # ---- end to end through the public API with host buffers --------------------------------------
+    host = {k: torch.from_numpy(g_np[k]).pin_memory() for k in PARAM_NAMES}
+    dl_host = torch.from_numpy(dl_np).pin_memory()
+    leaves = {k: torch.empty_like(gd[k]).requires_grad_(True) for k in PARAM_NAMES}
+    dl_dev = torch.empty_like(dl)
+    grads_host = {k: torch.empty(g_np[k].shape, dtype=torch.float32).pin_memory() for k in PARAM_NAMES}
+    h2d = sum(t.numel() * 4 for t in host.values()) + dl_host.numel() * 4
+    d2h = sum(t.numel() * 4 for t in grads_host.values())
+
+    def e2e_step():
+        with torch.no_grad():
+            for k in PARAM_NAMES:
+                leaves[k].copy_(host[k], non_blocking=True)
+                leaves[k].grad = None
+            dl_dev.copy_(dl_host, non_blocking=True)
+        for b in view_batches:
+            color, radii, depth = dgr.rasterize_views([sl[v] for v in b], leaves["means3D"], leaves["opacities"],
+                                                      shs=leaves["shs"], scales=leaves["scales"],
+                                                      rotations=leaves["rotations"])
+            color.backward(dl_dev[b[0]:b[-1] + 1])
+        if world > 1:
+            flat = torch.cat([leaves[k].grad.reshape(-1) for k in PARAM_NAMES])
+            dist.all_reduce(flat)
+            o = 0
+            for k in PARAM_NAMES:
+                n = leaves[k].grad.numel()
+                grads_host[k].copy_(flat[o:o + n].view_as(leaves[k].grad), non_blocking=True)
+                o += n
+        else:
+            for k in PARAM_NAMES:
+                grads_host[k].copy_(leaves[k].grad, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    ms_e2e, _ = timed(e2e_step, args.steps, args.warmup)
+    clocks = sampler.stop() if sampler else None
+
+    # ---- per-kernel device time of the same step (library CUDA events) -> roofline -----------------
+    lib.csb_profile_enable(1)
+    for _ in range(max(3, min(args.steps, 10))):
+        flush()
+        device_step()
+    torch.cuda.synchronize()
+    prof = csb_cabi.profile_read()
+    lib.csb_profile_enable(0)
+    kernels = {k: {"ms_per_launch": ms / n, "launches_per_step": n / max(3, min(args.steps, 10)),
+                   "ms_per_step": ms / max(3, min(args.steps, 10))} for k, (ms, n) in prof.items()}
+    top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    R_launch = R_step / max(1, len(view_batches))
+    Vb = len(view_batches[0])
+    alg = {  # algorithmic bytes per launch (DESIGN.md "roofline")
+        "preprocess": 311.0 * P * Vb,
+        "emit": 20.0 * P * Vb + 12.0 * R_launch,
+        "sort_onesweep": 16.0 * R_launch,
+        "sort_histogram": 4.0 * R_launch,
+        "tile_ranges": 16.0 * R_launch + 8.0 * tiles * Vb,
+        "render_forward": 44.0 * R_launch + 24.0 * Vb * H * W,
+        "render_backward": 40.0 * R_launch + 20.0 * Vb * H * W + 36.0 * R_launch,
+        "gaussian_backward": (236.0 + 24 + 40 * Vb + 256) * P,
+    }
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    ach = alg.get(top, 0.0) / (kernels[top]["ms_per_launch"] * 1e-3) / 1e9
+    roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                "note": "compositing kernels are FP32/SFU-issue bound, not HBM bound; see kernels{} and DESIGN.md"}
+
+    line = {
+        "metric": "rasterizer fwd+bwd Mpix/s", "value": world * mpix / (ms_step * 1e-3), "unit": "Mpix/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "gaussians": P, "views_per_gpu": V, "width": W, "height": H,
+                   "instances_per_step": int(R_step), "l2": "flushed between steps (256 MB write)",
+                   "parallelism": f"views x{world}" + (" + 1 flat NCCL all-reduce of gradients" if world > 1 else "")},
+        "e2e": {"value": world * mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "api": "diff_gaussian_rasterization.rasterize_views + autograd backward"},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
+        "impl": "b200",
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(g_np, cams, dl_np)
+        print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+# CPU baseline (oracle port on the host cores) and reference arm
+# ------------------------------------------------------------------------------------------
+def cpu_baseline(g_np, cams, dl_np, budget_s=12.0):
+    import oracle
+
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cam = cams[0]
+    H, W = cam.image_height, cam.image_width
+    n, t0 = 0, time.perf_counter()
+    while True:
+        s = oracle.rasterize_forward(g_np["means3D"], g_np["opacities"], cam.world_view_transform,
+                                     cam.full_proj_transform, cam.camera_center, np.ones(3, np.float32), cam.tanfovx,
+                                     cam.tanfovy, H, W, shs=g_np["shs"], scales=g_np["scales"],
+                                     rotations=g_np["rotations"], sh_degree=3)
+        oracle.rasterize_backward(s, dl_np[0])
+        n += 1
+        if time.perf_counter() - t0 > budget_s or n >= 20:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": n * H * W / 1e6 / dt, "unit": "Mpix/s", "cores": cores, "kind": "port",
+            "sample": f"{n} x (view 0 of the workload, {W}x{H}, fwd+bwd) with the OpenMP C oracle (oracle/rast_oracle*.c)"}
+
+
+def run_reference(args, rank, world, dev):
+    from oracle import ref_cuda
+
+    if rank != 0:
+        return
+    g_np, cams, dl_np, desc = make_workload(args.workload, 0, 1)
+    V, H, W = len(cams), cams[0].image_height, cams[0].image_width
+    P = g_np["means3D"].shape[0]
+    mpix = V * H * W / 1e6
+    base = {"metric": "rasterizer fwd+bwd Mpix/s", "unit": "Mpix/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "impl": "reference",
+            "config": {"workload": desc, "gaussians": P, "views_per_gpu": V, "width": W, "height": H}}
+    if not (ref_cuda.available() and torch.cuda.is_available()):
+        cb = cpu_baseline(g_np, cams, dl_np, budget_s=20.0)
+        base.update(value=cb["value"], ms_per_step=mpix / cb["value"] * 1e3, cpu_baseline=cb,
+                    e2e={"value": cb["value"], "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                    gpu_launches=0)
+        print(json.dumps(base), flush=True)
+        return
+    # The reference's rasterizer exists only as CUDA: time its own kernels (compiled unmodified for
+    # sm_100a) on this B200, view by view like train_utils.py:259 does.
+    host = {k: torch.from_numpy(g_np[k]).pin_memory() for k in PARAM_NAMES}
+    dl_host = torch.from_numpy(dl_np).pin_memory()
+    gd = {k: torch.empty(g_np[k].shape, dtype=torch.float32, device=dev) for k in PARAM_NAMES}
+    dl = torch.empty(dl_np.shape, dtype=torch.float32, device=dev)
+    grads_host = {k: torch.empty(g_np[k].shape, dtype=torch.float32).pin_memory() for k in PARAM_NAMES}
+    cam_t = [dict(viewmatrix=torch.from_numpy(c.world_view_transform).to(dev),
+                  projmatrix=torch.from_numpy(c.full_proj_transform).to(dev),
+                  campos=torch.from_numpy(c.camera_center).to(dev), bg=torch.ones(3, device=dev)) for c in cams]
+    ref = ref_cuda.RefRasterizer()
+    flush = l2_flusher(dev)
+    stream = torch.cuda.current_stream()
+
+    def render_all():
+        tot = None
+        for v, c in enumerate(cams):
+            t = cam_t[v]
+            ref.forward(gd["means3D"], gd["opacities"], t["viewmatrix"], t["projmatrix"], t["campos"], t["bg"],
+                        c.tanfovx, c.tanfovy, H, W, shs=gd["shs"], scales=gd["scales"], rotations=gd["rotations"],
+                        sh_degree=3)
+            g = ref.backward(dl[v])
+            if tot is None:
+                tot = {k: g[k] for k in PARAM_NAMES}
+            else:
+                for k in PARAM_NAMES:
+                    tot[k] += g[k]
+        return tot
+
+    def device_step():
+        render_all()
+
+    def e2e_step():
+        for k in PARAM_NAMES:
+            gd[k].copy_(host[k], non_blocking=True)
+        dl.copy_(dl_host, non_blocking=True)
+        tot = render_all()
+        for k in PARAM_NAMES:
+            grads_host[k].copy_(tot[k].view(grads_host[k].shape), non_blocking=True)
+        torch.cuda.synchronize()
+
+    def timed(fn):
+        for _ in range(args.warmup):
+            fn()
+        torch.cuda.synchronize()
+        ms = []
+        for _ in range(args.steps):
+            flush()
+            torch.cuda.synchronize()
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            fn()
+            torch.cuda.synchronize()  # the reference launches on the legacy default stream
+            b_.record(stream)
+            b_.synchronize()
+            ms.append(a.elapsed_time(b_))
+        return sum(ms) / len(ms)
+
+    for k in PARAM_NAMES:
+        gd[k].copy_(host[k])
+    dl.copy_(dl_host)
+    sampler = ClockSampler(dev.index)
+    ms_dev = timed(device_step)
+    ms_e2e = timed(e2e_step)
+    clocks = sampler.stop()
+    h2d = sum(t.numel() * 4 for t in host.values()) + dl_host.numel() * 4
+    d2h = sum(t.numel() * 4 for t in grads_host.values())
+    base.update(
+        value=mpix / (ms_dev * 1e-3), ms_per_step=ms_dev, clocks=clocks,
+        e2e={"value": mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
+             "d2h_bytes_per_step": d2h},
+        cpu_baseline={"value": mpix / (ms_dev * 1e-3), "unit": "Mpix/s", "cores": 0, "kind": "reference",
+                      "sample": "the reference has no CPU rasterizer: its own CUDA kernels (forward.cu, backward.cu, "
+                                "rasterizer_impl.cu recompiled for sm_100a, CUB onesweep sort) on this B200, "
+                                f"{V} views sequentially per step"},
+        gpu_launches=0)
+    base["config"]["l2"] = "flushed between steps (256 MB write)"
+    print(json.dumps(base), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference" and rank != 0:
+        return
+    if not torch.cuda.is_available():
+        if args.impl == "reference":
+            run_reference(args, rank, world, None)
+            return
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if args.impl == "reference":
+        run_reference(args, rank, world, dev)
+        return
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    try:
+        run_b200(args, rank, world, dev)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -80,6 +80,10 @@ def _load():
 _OPTIONAL = [
     ("csb_dist_cuda2_bytes", c_size_t, [c_int]),
     ("csb_dist_cuda2", c_int, [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    ("csb_launch_count", ctypes.c_ulonglong, []),
+    ("csb_profile_enable", None, [c_int]),
+    ("csb_profile_read", c_int, [c_char_p, POINTER(ctypes.c_double), POINTER(ctypes.c_ulonglong)]),
+    ("csb_profile_names", c_int, [c_char_p, c_size_t]),
 ]
 
 _lib = None
@@ -109,3 +113,16 @@ def current_stream_ptr():
     import torch
 
     return torch.cuda.current_stream().cuda_stream
+
+
+def profile_read():
+    """{kernel name: (total device ms, launches)} of the launches recorded since csb_profile_enable(1)."""
+    L = lib()
+    buf = ctypes.create_string_buffer(4096)
+    L.csb_profile_names(buf, 4096)
+    out = {}
+    for name in [n for n in buf.value.decode().split(",") if n]:
+        ms, n = ctypes.c_double(0), ctypes.c_ulonglong(0)
+        check(L.csb_profile_read(name.encode(), ctypes.byref(ms), ctypes.byref(n)), "csb_profile_read")
+        out[name] = (ms.value, n.value)
+    return out

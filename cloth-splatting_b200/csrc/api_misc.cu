@@ -1,8 +1,56 @@
 // Small C-ABI entry points: version, error strings, workspace introspection for parity tests.
 #include <string.h>
+#include <atomic>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
 #include "common.cuh"
 
 using namespace csb;
+
+// ---- launch accounting (always) and per-kernel CUDA-event timing (opt-in) ------------------
+namespace {
+std::atomic<unsigned long long> g_launches{0};
+std::atomic<int> g_profile{0};
+struct Span {
+    const char* name;
+    cudaEvent_t a, b;
+};
+std::mutex g_mu;
+std::vector<Span> g_spans;
+std::vector<cudaEvent_t> g_free_events;
+
+cudaEvent_t take_event() {
+    if (!g_free_events.empty()) {
+        cudaEvent_t e = g_free_events.back();
+        g_free_events.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+}  // namespace
+
+namespace csb {
+LaunchScope::LaunchScope(const char* name_, cudaStream_t stream_) : name(name_), stream(stream_), slot(-1) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (g_profile.load(std::memory_order_relaxed)) {
+        std::lock_guard<std::mutex> lk(g_mu);
+        Span sp{name, take_event(), take_event()};
+        cudaEventRecord(sp.a, stream);
+        slot = (int)g_spans.size();
+        g_spans.push_back(sp);
+    }
+}
+LaunchScope::~LaunchScope() {
+    if (slot >= 0) {
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (slot < (int)g_spans.size()) cudaEventRecord(g_spans[slot].b, stream);
+    }
+}
+}  // namespace csb
 
 extern "C" {
 
@@ -16,6 +64,49 @@ const char* csb_error_string(int code) {
         case CSB_ERR_UNSUPPORTED: return "unsupported configuration";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
     }
+}
+
+unsigned long long csb_launch_count(void) { return g_launches.load(); }
+
+void csb_profile_enable(int on) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (auto& sp : g_spans) {
+        g_free_events.push_back(sp.a);
+        g_free_events.push_back(sp.b);
+    }
+    g_spans.clear();
+    g_profile.store(on ? 1 : 0);
+}
+
+int csb_profile_read(const char* name, double* total_ms, unsigned long long* launches) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    double ms = 0.0;
+    unsigned long long n = 0;
+    for (auto& sp : g_spans) {
+        if (name && strcmp(name, sp.name) != 0) continue;
+        cudaError_t e = cudaEventSynchronize(sp.b);
+        if (e != cudaSuccess) return (int)e;
+        float t = 0.f;
+        e = cudaEventElapsedTime(&t, sp.a, sp.b);
+        if (e != cudaSuccess) return (int)e;
+        ms += t;
+        ++n;
+    }
+    if (total_ms) *total_ms = ms;
+    if (launches) *launches = n;
+    return 0;
+}
+
+int csb_profile_names(char* out, size_t out_bytes) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    std::map<std::string, int> seen;
+    std::string all;
+    for (auto& sp : g_spans)
+        if (!seen[sp.name]++) { all += sp.name; all += ","; }
+    if (!out || out_bytes == 0) return (int)all.size() + 1;
+    strncpy(out, all.c_str(), out_bytes - 1);
+    out[out_bytes - 1] = 0;
+    return (int)all.size() + 1;
 }
 
 size_t csb_rasterize_binning_capacity(int num_views, int P, int width, int height, size_t bytes) {

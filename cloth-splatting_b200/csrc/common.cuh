@@ -23,6 +23,24 @@
 
 namespace csb {
 
+// Counts every kernel launch of the library and, while csb_profile_enable(1) is in effect, brackets
+// it with CUDA events on the launching stream (api_misc.cu).
+struct LaunchScope {
+    const char* name;
+    cudaStream_t stream;
+    int slot;
+    LaunchScope(const char* name, cudaStream_t stream);
+    ~LaunchScope();
+};
+#define CSB_LAUNCH(name, stream, ...)              \
+    do {                                           \
+        {                                          \
+            csb::LaunchScope _ls(name, stream);    \
+            __VA_ARGS__;                           \
+        }                                          \
+        CSB_LAUNCH_CHECK();                        \
+    } while (0)
+
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Bump allocator over a caller-provided workspace (256-byte aligned slices).

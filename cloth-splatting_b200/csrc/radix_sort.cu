@@ -208,14 +208,12 @@ int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint3
     int hist_blocks = (int)((n_max + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
     if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
     if (hist_blocks < 1) hist_blocks = 1;
-    sort_histogram_kernel<<<hist_blocks, SORT_THREADS, 0, stream>>>(keys_a, n_dev, passes, hist);
-    CSB_LAUNCH_CHECK();
+    CSB_LAUNCH("sort_histogram", stream, sort_histogram_kernel<<<hist_blocks, SORT_THREADS, 0, stream>>>(keys_a, n_dev, passes, hist));
     uint32_t *kin = keys_a, *kout = keys_b, *vin = vals_a, *vout = vals_b;
     for (int p = 0; p < passes; ++p) {
-        sort_onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, 0, stream>>>(
+        CSB_LAUNCH("sort_onesweep", stream, sort_onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, 0, stream>>>(
             kin, kout, vin, vout, n_dev, p * RADIX_BITS, hist + p * RADIX, tickets + p,
-            lookback + (size_t)p * (tiles + 1) * RADIX);
-        CSB_LAUNCH_CHECK();
+            lookback + (size_t)p * (tiles + 1) * RADIX));
         uint32_t* t = kin; kin = kout; kout = t;
         t = vin; vin = vout; vout = t;
     }

@@ -488,16 +488,14 @@ int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, i
     if (binning_capacity > 0 && binning_ws) {
         const uint32_t* point_list = sorted_side(total_tiles) ? b.vals_b : b.vals_a;
         dim3 tgrid(vb.gx, vb.gy, num_views);
-        render_backward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, point_list, g.means2D,
+        CSB_LAUNCH("render_backward", stream, render_backward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, point_list, g.means2D,
                                                                   g.conic_opacity, g.rgb_depth, im.final_T,
-                                                                  im.n_contrib, dL_dpix, g.grad_acc);
-        CSB_LAUNCH_CHECK();
+                                                                  im.n_contrib, dL_dpix, g.grad_acc));
     }
     const float* cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
-    gaussian_backward_kernel<<<(P + 127) / 128, 128, 0, stream>>>(
+    CSB_LAUNCH("gaussian_backward", stream, gaussian_backward_kernel<<<(P + 127) / 128, 128, 0, stream>>>(
         vb, D, M, means3D, shs, cov3D_precomp ? nullptr : scales, scale_modifier, rotations, cov3D, radii, g.clamped,
-        g.grad_acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
-    CSB_LAUNCH_CHECK();
+        g.grad_acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations));
     return 0;
 }
 

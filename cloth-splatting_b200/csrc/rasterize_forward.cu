@@ -506,9 +506,8 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
     dim3 tgrid(vb.gx, vb.gy, num_views);
     if (n > 0) {
         const unsigned blocks = (unsigned)((n + 255) / 256);
-        preprocess_kernel<<<blocks, 256, 0, stream>>>(vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
-                                                      shs, cov3D_precomp, colors_precomp, radii, g);
-        CSB_LAUNCH_CHECK();
+        CSB_LAUNCH("preprocess", stream, preprocess_kernel<<<blocks, 256, 0, stream>>>(vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
+                                                      shs, cov3D_precomp, colors_precomp, radii, g));
         // depth order of the (view, Gaussian) entries
         uint32_t* scan_state = g.control + CTRL_SCAN_STATE;
         uint32_t* depth_lookback = scan_state + 2 * (blocks + 1);
@@ -518,9 +517,8 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
                               stream);
         if (rc) return rc;
         const uint32_t* order = side ? g.order_b : g.order_a;
-        emit_kernel<<<blocks, 256, 0, stream>>>(vb, order, g, (uint64_t*)scan_state, b.tiles_a, b.vals_a,
-                                                binning_capacity, num_rendered_dev);
-        CSB_LAUNCH_CHECK();
+        CSB_LAUNCH("emit", stream, emit_kernel<<<blocks, 256, 0, stream>>>(vb, order, g, (uint64_t*)scan_state, b.tiles_a, b.vals_a,
+                                                binning_capacity, num_rendered_dev));
         if (binning_capacity > 0) {
             CSB_CUDA_TRY(cudaMemsetAsync(b.lookback, 0, b.lookback_words * sizeof(uint32_t), stream));
             const int tile_bits = higher_msb((uint32_t)total_tiles);
@@ -534,22 +532,19 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             const uint32_t* sv = tside ? b.vals_b : b.vals_a;
             int rblocks = (int)((binning_capacity + 255) / 256);
             if (rblocks > 148 * 16) rblocks = 148 * 16;
-            tile_ranges_kernel<<<rblocks, 256, 0, stream>>>(g.control + CTRL_NUM_RENDERED, st, sv, g.rgb_depth,
+            CSB_LAUNCH("tile_ranges", stream, tile_ranges_kernel<<<rblocks, 256, 0, stream>>>(g.control + CTRL_NUM_RENDERED, st, sv, g.rgb_depth,
                                                             im.ranges, (flags & 1) ? b.keys : nullptr,
-                                                            (uint32_t)vb.tiles);
-            CSB_LAUNCH_CHECK();
-            render_forward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, sv, g.means2D, g.conic_opacity,
+                                                            (uint32_t)vb.tiles));
+            CSB_LAUNCH("render_forward", stream, render_forward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, sv, g.means2D, g.conic_opacity,
                                                                      g.rgb_depth, im.final_T, im.n_contrib, out_color,
-                                                                     out_depth);
-            CSB_LAUNCH_CHECK();
+                                                                     out_depth));
             if (tside != sorted_side(total_tiles)) return CSB_ERR_UNSUPPORTED;  // consumers recompute the side
         }
     } else {
         CSB_CUDA_TRY(cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream));
-        render_forward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity,
+        CSB_LAUNCH("render_forward", stream, render_forward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity,
                                                                  g.rgb_depth, im.final_T, im.n_contrib, out_color,
-                                                                 out_depth);
-        CSB_LAUNCH_CHECK();
+                                                                 out_depth));
     }
     if (num_rendered_host)
         CSB_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost,
@@ -562,8 +557,7 @@ int csb_mark_visible(int P, const float* means3D, const float* viewmatrix, const
     (void)projmatrix;
     if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return CSB_ERR_BAD_ARG;
     if (P == 0) return 0;
-    mark_visible_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, viewmatrix, present);
-    CSB_LAUNCH_CHECK();
+    CSB_LAUNCH("mark_visible", (cudaStream_t)stream_, mark_visible_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, means3D, viewmatrix, present));
     return 0;
 }
 

@@ -29,6 +29,8 @@ def cpu_deep_copy_tuple(input_tuple):
 # `_C` level: same signatures and return tuples as the reference's pybind module
 # --------------------------------------------------------------------------------------
 _capacity_hint = {}  # (device, V, P, W, H) -> instances seen last time
+_MIN_CAPACITY = 1 << 16  # first guess of the instance capacity: max(this, _PER_GAUSSIAN * V * P)
+_PER_GAUSSIAN = 8
 _pinned_counter = {}
 
 
@@ -95,7 +97,7 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
 
     key = (dev, V, P, W, H)
     hint = _capacity_hint.get(key, 0)
-    capacity = max(int(hint * 1.25) + 4096, 8 * V * P, 1 << 16) if P else 0
+    capacity = max(int(hint * 1.25) + 4096 if hint else 0, _PER_GAUSSIAN * V * P, _MIN_CAPACITY) if P else 0
     stream = _abi.current_stream_ptr()
     while True:
         nbytes = lib.csb_rasterize_binning_bytes(V, P, W, H, capacity)

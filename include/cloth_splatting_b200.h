@@ -44,6 +44,16 @@ int csb_abi_version(void);
 /* Human readable string for a return code of this library. */
 const char* csb_error_string(int code);
 
+/* Kernel launches issued by this library since it was loaded (all entry points). */
+unsigned long long csb_launch_count(void);
+/* Per-kernel device timing for bench.py's roofline: while enabled, every launch is bracketed by CUDA
+ * events on its stream.  csb_profile_enable clears earlier records.  csb_profile_read sums the
+ * device time (ms) and the launch count of the kernel `name` (NULL = all kernels) recorded so far,
+ * waiting for them to finish.  csb_profile_names writes the comma-separated kernel names seen. */
+void csb_profile_enable(int on);
+int csb_profile_read(const char* name, double* total_ms, unsigned long long* launches);
+int csb_profile_names(char* out, size_t out_bytes);
+
 /* ------------------------------------------------------------------------- *
  * Rasterizer
  * ------------------------------------------------------------------------- */

@@ -1,0 +1,82 @@
+"""Pins the CPU oracle against golden outputs of the reference's own CUDA code (tests/golden/*.npz,
+generated on a B200 by tests/make_golden.py from oracle/_ref/libref_cuda.so).  Runs without a GPU.
+
+gcc and nvcc agree on almost every rounding (the oracle writes out nvcc's FMA contraction), but libm's
+expf and CUDA's differ in the last ulp, so float comparisons use the north_star tolerances and integer
+comparisons allow the handful of Gaussians that sit exactly on a rounding boundary."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import conftest
+import csb_synth as S
+import helpers as Hh
+
+GOLDEN = os.path.join(conftest.ROOT, "tests", "golden")
+
+
+def _scenes():
+    import make_golden
+
+    return make_golden.scenes()
+
+
+def _fixture(name):
+    path = os.path.join(GOLDEN, name + ".npz")
+    if not os.path.exists(path):
+        pytest.fail(f"{path} missing: run tests/make_golden.py on the GPU box and commit its output")
+    return np.load(path)
+
+
+@pytest.mark.parametrize("name", ["cloud_3000_160x112_deg3", "cloud_1500_149x83_deg1", "cloth_10108_208x208_deg3"])
+def test_oracle_matches_reference_cuda_golden(name):
+    import oracle
+
+    g, cam, deg, bg = _scenes()[name]
+    fx = _fixture(name)
+    s = Hh.oracle_forward(g, cam, bg, deg)
+    P = g["means3D"].shape[0]
+    bad = int((s.radii != fx["radii"]).sum())
+    assert bad <= max(1, P // 1000), f"{bad} radii differ"
+    vis = (fx["radii"] > 0) & (s.radii > 0)
+    assert np.array_equal(s.depths.view(np.uint32)[vis], fx["depths"].view(np.uint32)[vis])  # sort-key bits
+    assert np.abs(s.means2D[vis] - fx["means2D"][vis]).max() < 1e-3
+    assert Hh.rel_err(s.conic_opacity[vis], fx["conic_opacity"][vis]) < 1e-5
+    assert np.abs(s.rgb[vis] - fx["rgb"][vis]).max() < 1e-5
+    assert Hh.rel_err(s.cov3D[vis], fx["cov3D"][vis]) < 1e-6
+    if bad == 0 and s.num_rendered == int(fx["num_rendered"]):
+        assert np.array_equal(s.keys, fx["keys"])
+        assert np.array_equal(s.point_list, fx["point_list"])
+        assert np.array_equal(s.ranges, fx["ranges"])
+        assert (s.n_contrib != fx["n_contrib"]).mean() < 1e-3
+        assert np.abs(s.color - fx["color"]).max() <= 1e-5
+        assert np.abs(s.depth - fx["depth"]).max() <= 1e-5 * max(1.0, float(fx["depths"].max()))
+        tol = 1e-4
+    else:
+        assert (np.abs(s.color - fx["color"]) > 1e-5).mean() < 2e-3
+        tol = 5e-3
+    H, W = cam.image_height, cam.image_width
+    dl = S.pixel_grad(1, H, W)[0]
+    og = oracle.rasterize_backward(s, dl)
+    for k in ("means2D", "opacities", "means3D", "cov3D", "shs", "scales", "rotations"):
+        rel = Hh.rel_err(og[k], fx["grad_" + k])
+        assert rel < tol, f"grad {k}: rel {rel}"
+
+
+def test_dist2_oracle_matches_reference_cuda_golden():
+    import oracle
+
+    fx = _fixture("dist2")
+    g = S.mesh_gaussians(20, 14, 1)
+    rng = np.random.default_rng(77)
+    clouds = {"cloth_10108": g["means3D"], "normal_4096": rng.standard_normal((4096, 3)).astype(np.float32),
+              "tiny_3": rng.standard_normal((3, 3)).astype(np.float32)}
+    for k, pts in clouds.items():
+        assert np.array_equal(oracle.dist2(pts).view(np.uint32), fx[k].view(np.uint32)), k
+
+
+def test_golden_files_record_their_reference_commit():
+    for path in glob.glob(os.path.join(GOLDEN, "*.npz")):
+        assert "f7acc90" in str(np.load(path)["ref_commit"])
