@@ -212,7 +212,8 @@ knn_query_kernel(int P, int L, const uint32_t* __restrict__ control, const float
                         const float4 o = sorted[j];
                         const float dx = o.x - me.x, dy = o.y - me.y, dz = o.z - me.z;
                         // d.x*d.x + d.y*d.y + d.z*d.z as nvcc contracts it in the reference
-                        const float dist = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+                        // (SASS of boxMeanDist: FMUL dy*dy; FFMA dx*dx + .; FFMA dz*dz + .)
+                        const float dist = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
                         update3(dist, best);
                     }
                 }

@@ -487,10 +487,13 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
     ViewBatch vb;
     int rc = fill_view_batch(vb, num_views, views, P, width, height);
     if (rc) return rc;
-    if (shs == nullptr && colors_precomp == nullptr) return CSB_ERR_BAD_ARG;
-    if (cov3D_precomp == nullptr && (scales == nullptr || rotations == nullptr)) return CSB_ERR_BAD_ARG;
-    if (shs != nullptr && (M < (D + 1) * (D + 1) || D < 0 || D > 3)) return CSB_ERR_BAD_ARG;
-    if (!out_color || !out_depth || !radii || !num_rendered_dev) return CSB_ERR_BAD_ARG;
+    if (P > 0) {  // P == 0 renders the background only (rasterize_points.cu:82)
+        if (means3D == nullptr || opacities == nullptr || radii == nullptr) return CSB_ERR_BAD_ARG;
+        if (shs == nullptr && colors_precomp == nullptr) return CSB_ERR_BAD_ARG;
+        if (cov3D_precomp == nullptr && (scales == nullptr || rotations == nullptr)) return CSB_ERR_BAD_ARG;
+        if (shs != nullptr && (M < (D + 1) * (D + 1) || D < 0 || D > 3)) return CSB_ERR_BAD_ARG;
+    }
+    if (!out_color || !out_depth || !num_rendered_dev) return CSB_ERR_BAD_ARG;
     if ((size_t)num_views * (size_t)P >= (1ull << 31) || binning_capacity >= (1ull << 30)) return CSB_ERR_UNSUPPORTED;
 
     GeomState g = GeomState::carve(geom_ws, num_views, P);

@@ -19,7 +19,7 @@ void oracle_dist2(int P, const float* pts, float* out) {
         for (int j = 0; j < P; ++j) {
             if (j == i) continue;
             const float dx = pts[3 * j] - rx, dy = pts[3 * j + 1] - ry, dz = pts[3 * j + 2] - rz;
-            float dist = fmaf(dz, dz, fmaf(dy, dy, dx * dx)); /* nvcc's contraction of dx*dx + dy*dy + dz*dz */
+            float dist = fmaf(dz, dz, fmaf(dx, dx, dy * dy)); /* nvcc's contraction of dx*dx + dy*dy + dz*dz (reference SASS) */
             for (int k = 0; k < 3; ++k)
                 if (best[k] > dist) { const float t = best[k]; best[k] = dist; dist = t; }
         }

@@ -16,7 +16,9 @@
  *
  * Floating point: fp32 throughout (ndc2Pix in fp64, auxiliary.h:41-44).  The GPU code is compiled
  * with FMA contraction; to stay as close to it as possible the sums of products below are written
- * with explicit fmaf() in the order nvcc contracts them (first product rounded, later ones fused)
+ * with explicit fmaf() the way nvcc contracts them: in A*B + C*D the LEFT product is fused and the
+ * right one rounded (read off the reference's SASS: FMUL dy*dy; FFMA dx*dx+.; FFMA dz*dz+. for
+ * dx*dx + dy*dy + dz*dz), a product added to a non-product is fused into it,
  * and the file is compiled with -ffp-contract=off.  Integer results can still differ from the GPU
  * for inputs that sit exactly on a rounding boundary; the tests bound how often.
  */
@@ -39,7 +41,7 @@ static const float SH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570
 
 /* a*b + c*d + e*f the way nvcc contracts it */
 static inline float dot3(float a, float b, float c, float d, float e, float f) {
-    return fmaf(e, f, fmaf(c, d, a * b));
+    return fmaf(e, f, fmaf(a, b, c * d));
 }
 /* m0*x + m1*y + m2*z + m3 */
 static inline float affine(float m0, float x, float m1, float y, float m2, float z, float m3) {
@@ -65,15 +67,15 @@ static mat3 mat3_t(const mat3* A) {
 static mat3 quat_to_mat3(const float* q) {
     const float r = q[0], x = q[1], y = q[2], z = q[3];
     mat3 R;
-    R.c[0][0] = fmaf(-2.f, fmaf(z, z, y * y), 1.f);
+    R.c[0][0] = fmaf(-2.f, fmaf(y, y, z * z), 1.f);
     R.c[0][1] = 2.f * fmaf(x, y, -(r * z));
-    R.c[0][2] = 2.f * fmaf(r, y, x * z);
-    R.c[1][0] = 2.f * fmaf(r, z, x * y);
-    R.c[1][1] = fmaf(-2.f, fmaf(z, z, x * x), 1.f);
+    R.c[0][2] = 2.f * fmaf(x, z, r * y);
+    R.c[1][0] = 2.f * fmaf(x, y, r * z);
+    R.c[1][1] = fmaf(-2.f, fmaf(x, x, z * z), 1.f);
     R.c[1][2] = 2.f * fmaf(y, z, -(r * x));
     R.c[2][0] = 2.f * fmaf(x, z, -(r * y));
-    R.c[2][1] = 2.f * fmaf(r, x, y * z);
-    R.c[2][2] = fmaf(-2.f, fmaf(y, y, x * x), 1.f);
+    R.c[2][1] = 2.f * fmaf(y, z, r * x);
+    R.c[2][2] = fmaf(-2.f, fmaf(x, x, y * y), 1.f);
     return R;
 }
 
@@ -150,7 +152,7 @@ static void tile_rect(float px, float py, int r, int gx, int gy, int* mn, int* m
 
 static void sh_to_rgb(int deg, const float* sh, const float* pos, const float* campos, float* rgb, uint8_t* clamped) {
     float d[3] = {pos[0] - campos[0], pos[1] - campos[1], pos[2] - campos[2]};
-    const float len = sqrtf(fmaf(d[2], d[2], fmaf(d[1], d[1], d[0] * d[0])));
+    const float len = sqrtf(fmaf(d[2], d[2], fmaf(d[0], d[0], d[1] * d[1])));
     const float x = d[0] / len, y = d[1] / len, z = d[2] / len;
     for (int ch = 0; ch < 3; ++ch) {
 #define S(k) sh[(k) * 3 + ch]
@@ -323,7 +325,7 @@ int oracle_bin(int P, int W, int H, const int* radii, const float* means2D, cons
 
 static inline float pair_power(const float* co, float dx, float dy) {
     /* -0.5f*(a*dx*dx + c*dy*dy) - b*dx*dy with nvcc's contraction */
-    const float s = fmaf(co[2] * dy, dy, co[0] * dx * dx);
+    const float s = fmaf(co[0] * dx, dx, co[2] * dy * dy);
     return fmaf(s, -0.5f, -(co[1] * dx * dy));
 }
 

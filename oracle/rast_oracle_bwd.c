@@ -62,7 +62,7 @@ void oracle_render_backward(int P, int W, int H, const uint32_t* ranges, const u
                     const uint32_t id = point_list[k];
                     const float dx = means2D[2 * id] - pxf, dy = means2D[2 * id + 1] - pyf;
                     const float* co = conic_opacity + 4 * (size_t)id;
-                    const float s = fmaf(co[2] * dy, dy, co[0] * dx * dx);
+                    const float s = fmaf(co[0] * dx, dx, co[2] * dy * dy);
                     const float power = fmaf(s, -0.5f, -(co[1] * dx * dy));
                     if (power > 0.0f) continue;
                     const float G = expf(power);
