@@ -77,7 +77,13 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
     P = means3D.size(0)
     H, W = int(image_height), int(image_width)
     dev = means3D.device
-    means3D = _f32c(means3D, "means3D") if P else means3D
+    if P == 0:
+        # rasterize_points.cu:68-82: nothing is launched, the zero-filled outputs are returned as they are
+        z = torch.zeros((0,), dtype=torch.uint8, device=dev)
+        return (0, torch.zeros((V, 3, H, W), dtype=torch.float32, device=dev),
+                torch.zeros((V, 1, H, W), dtype=torch.float32, device=dev),
+                torch.zeros((V, 0), dtype=torch.int32, device=dev), z, z.clone(), z.clone())
+    means3D = _f32c(means3D, "means3D")
     colors = _f32c(colors, "colors_precomp")
     opacity = _f32c(opacity, "opacities")
     scales = _f32c(scales, "scales")
