@@ -1,0 +1,766 @@
+// meshnet GNN forward (encode - process - decode) for sm_100a: bf16 tcgen05 MLPs with TMEM accumulators.
+//
+// Replaces EncodeProcessDecode.forward (meshnet/graph_network.py:387-408) and what it runs per call:
+// Encoder (:98-111), 15 x InteractionNetwork (message :178-199 = edge MLP over cat[x[dst], x[src], e];
+// aggregate = sum at dst :136; update :201-222 = node MLP over cat[agg, x]; residuals :176) and the
+// Decoder (:323-332), i.e. ~300 cuBLAS / index_select / scatter_add_ / layer_norm launches of PyTorch.
+//
+// One kernel template, four roles.  A CTA owns tiles of 128 rows (edges or nodes).  The role's weights
+// (a "unit" image: bf16, already laid out in the 128-byte-swizzled K-major form tcgen05.mma reads)
+// are bulk-copied (cp.async.bulk, TMA engine) into shared memory once per CTA and stay resident while
+// the CTA walks its tiles.  Per tile:
+//     stage A operand (gather) -> tcgen05.mma chain -> TMEM -> registers (+bias, ReLU) -> bf16 A operand
+//     of the next layer -> ... -> LayerNorm in registers -> role specific output.
+//   ENC   first Linear (K = 8 / 4) on the CUDA cores in fp32, two tensor-core Linears, LN
+//   EDGE  gather x[dst] | x[src] | e0 (K = 384), three Linears, LN, segmented sum over the dst-sorted rows
+//         of the tile, one red.add per (segment, column) into agg
+//   NODE  agg | x (K = 256), three Linears, LN, x += .  (fp32 master copy + bf16 copy for the gathers)
+//   DEC   two tensor-core Linears, last Linear (N = 3) on the CUDA cores in fp32
+// The reference never replaces the edge latents by the edge MLP output: e_m = 2^m e_0 (SURVEY.md fact
+// 0.3).  e_0 is therefore stored once (bf16, in dst-sorted edge order) and the factor 2^m is folded into
+// the edge block of the first edge Linear when the weights are packed (exact in bf16).
+#include <cuda_bf16.h>
+#include "common.cuh"
+
+namespace csb {
+namespace gnn {
+
+constexpr int LAT = 128;  // latent width == hidden width (only configuration supported)
+constexpr int TILE_M = 128;
+constexpr int CHUNK_BYTES = 128 * 128;  // 128 rows x 64 bf16, one swizzle-128B K block
+constexpr int THREADS = 256;
+constexpr int TMEM_COLS = 128;
+
+enum Mode { ENC = 0, EDGE = 1, NODE = 2, DEC = 3 };
+
+// ---- unit images ------------------------------------------------------------------------------
+// bf16 chunks first, then an fp32 block.
+//   EDGE: chunks W0(6) W1(2) W2(2); f32 b0 b1 b2 ln_g ln_b
+//   NODE: chunks W0(4) W1(2) W2(2); f32 b0 b1 b2 ln_g ln_b
+//   ENC : chunks W1(2) W2(2);       f32 b0 b1 b2 ln_g ln_b W0[128 x kin]
+//   DEC : chunks W0(2) W1(2);       f32 b0 b1 W2[nout x 128] b2[nout]
+__host__ __device__ inline int unit_chunks(int mode) { return mode == EDGE ? 10 : mode == NODE ? 8 : 4; }
+__host__ __device__ inline int unit_f32(int mode, int kin, int nout) {
+    if (mode == ENC) return 5 * LAT + LAT * kin;
+    if (mode == DEC) return 2 * LAT + nout * LAT + ((nout + 3) & ~3);
+    return 5 * LAT;
+}
+__host__ __device__ inline size_t unit_bytes(int mode, int kin, int nout) {
+    const size_t b = (size_t)unit_chunks(mode) * CHUNK_BYTES + (size_t)unit_f32(mode, kin, nout) * 4;
+    return (b + 127) / 128 * 128;
+}
+// floats of one MLP (+LN) in the flat parameter buffer: W0[128,k0] b0 W1[128,128] b1 W2[n2,128] b2 (g, beta)
+__host__ __device__ inline size_t mlp_floats(int k0, int n2, bool ln) {
+    return (size_t)LAT * k0 + LAT + (size_t)LAT * LAT + LAT + (size_t)n2 * LAT + n2 + (ln ? 2 * LAT : 0);
+}
+
+struct UnitDesc {
+    unsigned long long src;  // float offset in the flat parameter buffer
+    unsigned long long dst;  // byte offset in the packed buffer
+    int mode, k0, n2;
+    float e_scale;           // EDGE: factor of the columns >= 256 of W0 (2^m)
+};
+constexpr int MAX_UNITS = 2 + 2 * 30 + 1;
+struct PackTable {
+    int n;
+    UnitDesc u[MAX_UNITS];
+};
+
+__device__ __forceinline__ uint32_t swz_off(int row, int c16) {
+    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((c16 ^ (row & 7)) << 4));
+}
+
+// W [128, K] row-major fp32 -> chunks of [128 rows x 64 k] bf16, swizzle-128B K-major
+__device__ void pack_linear(const float* __restrict__ W, int K, int col_scale_from, float scale, uint8_t* dst) {
+    for (int i = threadIdx.x; i < LAT * K; i += blockDim.x) {
+        const int n = i / K, k = i - n * K;
+        float w = W[i];
+        if (k >= col_scale_from) w *= scale;
+        const uint32_t off = (uint32_t)(k >> 6) * CHUNK_BYTES + swz_off(n, (k & 63) >> 3) + (k & 7) * 2;
+        *reinterpret_cast<__nv_bfloat16*>(dst + off) = __float2bfloat16_rn(w);
+    }
+}
+__device__ void copy_f32(const float* __restrict__ s, float* d, int n) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) d[i] = s[i];
+}
+
+__global__ void __launch_bounds__(256) gnn_pack_kernel(const float* __restrict__ flat, uint8_t* __restrict__ packed,
+                                                        const __grid_constant__ PackTable tab) {
+    const UnitDesc& u = tab.u[blockIdx.x];
+    const float* W0 = flat + u.src;
+    const float* b0 = W0 + (size_t)LAT * u.k0;
+    const float* W1 = b0 + LAT;
+    const float* b1 = W1 + LAT * LAT;
+    const float* W2 = b1 + LAT;
+    const float* b2 = W2 + (size_t)u.n2 * LAT;
+    const float* lng = b2 + u.n2;
+    const float* lnb = lng + LAT;
+    uint8_t* d = packed + u.dst;
+    float* f = reinterpret_cast<float*>(d + (size_t)unit_chunks(u.mode) * CHUNK_BYTES);
+    if (u.mode == EDGE || u.mode == NODE) {
+        const int c0 = u.k0 / 64;
+        pack_linear(W0, u.k0, u.mode == EDGE ? 2 * LAT : u.k0, u.e_scale, d);
+        pack_linear(W1, LAT, LAT, 1.f, d + (size_t)c0 * CHUNK_BYTES);
+        pack_linear(W2, LAT, LAT, 1.f, d + (size_t)(c0 + 2) * CHUNK_BYTES);
+        copy_f32(b0, f, LAT); copy_f32(b1, f + LAT, LAT); copy_f32(b2, f + 2 * LAT, LAT);
+        copy_f32(lng, f + 3 * LAT, LAT); copy_f32(lnb, f + 4 * LAT, LAT);
+    } else if (u.mode == ENC) {
+        pack_linear(W1, LAT, LAT, 1.f, d);
+        pack_linear(W2, LAT, LAT, 1.f, d + 2 * CHUNK_BYTES);
+        copy_f32(b0, f, LAT); copy_f32(b1, f + LAT, LAT); copy_f32(b2, f + 2 * LAT, LAT);
+        copy_f32(lng, f + 3 * LAT, LAT); copy_f32(lnb, f + 4 * LAT, LAT);
+        copy_f32(W0, f + 5 * LAT, LAT * u.k0);
+    } else {
+        pack_linear(W0, LAT, LAT, 1.f, d);
+        pack_linear(W1, LAT, LAT, 1.f, d + 2 * CHUNK_BYTES);
+        copy_f32(b0, f, LAT); copy_f32(b1, f + LAT, LAT);
+        copy_f32(W2, f + 2 * LAT, u.n2 * LAT);
+        copy_f32(b2, f + 2 * LAT + u.n2 * LAT, u.n2);
+    }
+}
+
+// ---- PTX wrappers -------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    const long long t0 = clock64();
+    while (true) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) return;
+        if (clock64() - t0 > 4000000000ll) __trap();  // ~2 s: never hang the device on a protocol bug
+    }
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// K-major, swizzle-128B shared-memory matrix descriptor (LBO = 1, SBO = 1024 B, version 1)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) |
+           (2ull << 61);
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32, M = 128, N = 128, K = 16
+constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(IDESC), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 lanes x 32 columns of fp32: thread l of the warp gets row (lane base + l), columns [col, col+32)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+
+// ---- kernel arguments ---------------------------------------------------------------------------
+struct Args {
+    const uint8_t* unit;  // packed unit image
+    int rows;             // E (ENC edges, EDGE) or N
+    int kin, nout;        // ENC: input features; DEC: output features
+    int N;
+    const int* dst_sorted;           // EDGE [E]
+    const int* src_sorted;           // EDGE [E]
+    const __nv_bfloat16* x_bf16;     // EDGE / DEC gathers, NODE input  [N,128]
+    const __nv_bfloat16* e0;         // EDGE [E,128] (dst-sorted order)
+    float* agg;                      // EDGE out (atomic), NODE in (then zeroed)  [N,128]
+    float* x_f32;                    // NODE in/out, ENC(node) out  [N,128]
+    __nv_bfloat16* out_bf16;         // NODE / ENC out  [rows,128]
+    const float* in;                 // ENC input [rows_src, kin]
+    const int* perm;                 // ENC: source row of output row i (NULL = identity)
+    float* y;                        // DEC out [N, nout]
+};
+
+template <int MODE> struct Cfg {
+    static constexpr int K1_CHUNKS = MODE == EDGE ? 6 : MODE == NODE ? 4 : 2;  // K blocks of the first TC layer
+    static constexpr int A_SLOTS = MODE == EDGE ? 3 : MODE == NODE ? 4 : 2;    // resident A chunks
+    static constexpr int TC_LAYERS = (MODE == EDGE || MODE == NODE) ? 3 : 2;
+    static constexpr int W_CHUNKS = MODE == EDGE ? 10 : MODE == NODE ? 8 : 4;
+};
+
+constexpr int SCRATCH_FLOATS = 2048;  // LayerNorm / decoder partials
+static size_t smem_bytes(int mode, int kin, int nout) {
+    const int a_slots = mode == EDGE ? 3 : mode == NODE ? 4 : 2;
+    size_t b = 1024;  // alignment slack
+    b += (size_t)unit_chunks(mode) * CHUNK_BYTES;
+    b += (size_t)a_slots * CHUNK_BYTES;
+    b += ((size_t)unit_f32(mode, kin, nout) * 4 + 127) / 128 * 128;
+    b += SCRATCH_FLOATS * 4 + 2 * TILE_M * 4 + 64;
+    return b;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(THREADS, 1) gnn_mlp_kernel(const __grid_constant__ Args a) {
+    using C = Cfg<MODE>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sW = smem;                                        // weight chunks
+    uint8_t* sA = sW + (size_t)C::W_CHUNKS * CHUNK_BYTES;     // A operand chunks (also scatter staging)
+    float* sF = reinterpret_cast<float*>(sA + (size_t)C::A_SLOTS * CHUNK_BYTES);  // fp32 parameters
+    const int nf32 = unit_f32(MODE, a.kin, a.nout);
+    float* sRed = sF + ((nf32 + 31) & ~31);                    // SCRATCH_FLOATS
+    int* sDst = reinterpret_cast<int*>(sRed + SCRATCH_FLOATS);  // [128]
+    int* sSrc = sDst + TILE_M;                                 // [128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sSrc + TILE_M);  // [0] weights, [1] mma
+    uint32_t* sTmem = reinterpret_cast<uint32_t*>(bars + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int row = (warp & 3) * 32 + lane;  // TMEM lane == tile row owned in the epilogues
+    const int half = warp >> 2;              // columns [64*half, 64*half + 64)
+    const uint32_t bar_w = smem_u32(&bars[0]), bar_mma = smem_u32(&bars[1]);
+
+    if (tid == 0) {
+        mbar_init(bar_w, 1);
+        mbar_init(bar_mma, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(smem_u32(sTmem), TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *sTmem;
+
+    // resident weights: one bulk copy per 16 KB chunk + the fp32 block
+    if (tid == 0) {
+        const uint32_t wbytes = (uint32_t)C::W_CHUNKS * CHUNK_BYTES;
+        const uint32_t fbytes = (uint32_t)nf32 * 4;
+        mbar_expect_tx(bar_w, wbytes + fbytes);
+        for (int c = 0; c < C::W_CHUNKS; ++c)
+            bulk_g2s(smem_u32(sW + (size_t)c * CHUNK_BYTES), a.unit + (size_t)c * CHUNK_BYTES, CHUNK_BYTES, bar_w);
+        bulk_g2s(smem_u32(sF), a.unit + wbytes, fbytes, bar_w);
+    }
+    bool weights_ready = false;
+    uint32_t mma_parity = 0;
+    const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW);
+    const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(half * 64);
+
+    const int num_tiles = (a.rows + TILE_M - 1) / TILE_M;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int row0 = tile * TILE_M;
+        const int grow = row0 + row;  // global row of this thread's epilogue row
+        const bool rvalid = grow < a.rows;
+
+        // ------------------------------------------------------------------ stage the first A operand
+        if (MODE == EDGE) {
+            if (tid < TILE_M) {
+                const int p = row0 + tid;
+                int d = -1, s = -1;
+                if (p < a.rows) {
+                    d = a.dst_sorted[p];
+                    s = a.src_sorted[p];
+                    if ((unsigned)d >= (unsigned)a.N || (unsigned)s >= (unsigned)a.N) d = s = -1;
+                }
+                sDst[tid] = d;
+                sSrc[tid] = s;
+            }
+            __syncthreads();
+        }
+        int wchunk = 0;  // next weight chunk to multiply with
+        if (MODE == ENC) {
+            // first Linear on the CUDA cores (fp32), K = kin
+            if (!weights_ready) { mbar_wait(bar_w, 0); weights_ready = true; }
+            const float* W0 = sF + 5 * LAT;
+            const float* b0 = sF;
+            float xin[16];
+            const int kin = a.kin;
+            const long long srow = rvalid ? (a.perm ? (long long)a.perm[grow] : (long long)grow) : -1;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) xin[k] = (srow >= 0 && k < kin) ? a.in[srow * kin + k] : 0.f;
+#pragma unroll 1
+            for (int c = 0; c < 8; ++c) {
+                float h[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int o = half * 64 + c * 8 + j;
+                    float acc = b0[o];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k)
+                        if (k < kin) acc = fmaf(W0[o * kin + k], xin[k], acc);
+                    h[j] = fmaxf(acc, 0.f);
+                }
+                uint4 pk = make_uint4(pack_bf16(h[0], h[1]), pack_bf16(h[2], h[3]), pack_bf16(h[4], h[5]),
+                                      pack_bf16(h[6], h[7]));
+                *reinterpret_cast<uint4*>(sA + (size_t)half * CHUNK_BYTES + swz_off(row, c)) = pk;
+            }
+        } else if (MODE == DEC) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int idx = it * THREADS + tid;
+                const int c = idx & 7, r = (idx >> 3) & 127, kb = idx >> 10;
+                const int n = row0 + r;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (n < a.rows) v = *reinterpret_cast<const uint4*>(a.x_bf16 + (size_t)n * LAT + kb * 64 + c * 8);
+                *reinterpret_cast<uint4*>(sA + (size_t)kb * CHUNK_BYTES + swz_off(r, c)) = v;
+            }
+        } else if (MODE == NODE) {
+#pragma unroll 4
+            for (int it = 0; it < 16; ++it) {
+                const int idx = it * THREADS + tid;
+                const int c = idx & 7, r = (idx >> 3) & 127, kb = idx >> 10;
+                const int n = row0 + r;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (n < a.rows) {
+                    if (kb < 2) {
+                        float4* p = reinterpret_cast<float4*>(a.agg + (size_t)n * LAT + kb * 64 + c * 8);
+                        const float4 f0 = p[0], f1 = p[1];
+                        v = make_uint4(pack_bf16(f0.x, f0.y), pack_bf16(f0.z, f0.w), pack_bf16(f1.x, f1.y),
+                                       pack_bf16(f1.z, f1.w));
+                        p[0] = make_float4(0.f, 0.f, 0.f, 0.f);  // ready for the next step's scatter
+                        p[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    } else {
+                        v = *reinterpret_cast<const uint4*>(a.x_bf16 + (size_t)n * LAT + (kb - 2) * 64 + c * 8);
+                    }
+                }
+                *reinterpret_cast<uint4*>(sA + (size_t)kb * CHUNK_BYTES + swz_off(r, c)) = v;
+            }
+        }
+
+        // ------------------------------------------------------------------ tensor-core layers
+#pragma unroll 1
+        for (int layer = 0; layer < C::TC_LAYERS; ++layer) {
+            const bool first = layer == 0;
+            const int phases = (MODE == EDGE && first) ? 2 : 1;
+#pragma unroll 1
+            for (int ph = 0; ph < phases; ++ph) {
+                int nchunks = first ? (MODE == EDGE ? 3 : C::K1_CHUNKS) : 2;
+                if (MODE == EDGE && first) {
+                    // gather 3 K blocks of [x[dst] | x[src] | e0] (blocks 3*ph .. 3*ph+2)
+                    uint4 v[12];
+#pragma unroll
+                    for (int it = 0; it < 12; ++it) {
+                        const int idx = it * THREADS + tid;
+                        const int c = idx & 7, r = (idx >> 3) & 127, kb = 3 * ph + (idx >> 10);
+                        const int d = sDst[r];
+                        v[it] = make_uint4(0, 0, 0, 0);
+                        if (d >= 0) {
+                            const __nv_bfloat16* src;
+                            if (kb < 2) src = a.x_bf16 + (size_t)d * LAT + kb * 64;
+                            else if (kb < 4) src = a.x_bf16 + (size_t)sSrc[r] * LAT + (kb - 2) * 64;
+                            else src = a.e0 + (size_t)(row0 + r) * LAT + (kb - 4) * 64;
+                            v[it] = *reinterpret_cast<const uint4*>(src + c * 8);
+                        }
+                    }
+#pragma unroll
+                    for (int it = 0; it < 12; ++it) {
+                        const int idx = it * THREADS + tid;
+                        const int c = idx & 7, r = (idx >> 3) & 127, kl = idx >> 10;
+                        *reinterpret_cast<uint4*>(sA + (size_t)kl * CHUNK_BYTES + swz_off(r, c)) = v[it];
+                    }
+                }
+                // the resident unit image (bulk copy) must have landed before anybody touches it
+                if (!weights_ready) { mbar_wait(bar_w, 0); weights_ready = true; }
+                // generic-proxy writes of the A operand -> visible to the tensor core (async proxy)
+                fence_proxy_async();
+                tc_fence_before();
+                __syncthreads();
+                if (tid == 0) {
+                    tc_fence_after();
+                    for (int s = 0; s < nchunks; ++s) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const uint64_t ad = umma_desc(sA_u32 + (uint32_t)s * CHUNK_BYTES + k * 32);
+                            const uint64_t bd = umma_desc(sW_u32 + (uint32_t)(wchunk + s) * CHUNK_BYTES + k * 32);
+                            umma(tmem, ad, bd, (ph > 0 || s > 0 || k > 0) ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(bar_mma);
+                }
+                wchunk += nchunks;
+                mbar_wait(bar_mma, mma_parity);
+                mma_parity ^= 1;
+                tc_fence_after();
+            }
+            // ---- epilogue of this layer: TMEM -> registers
+            float v[64];
+            tmem_ld32(taddr, v);
+            tmem_ld32(taddr + 32, v + 32);
+            const int bias_idx = (MODE == ENC) ? layer + 1 : layer;
+            const float* bias = sF + bias_idx * LAT + half * 64;
+            const bool last = layer == C::TC_LAYERS - 1;
+            if (!last) {
+                // + bias, ReLU, bf16 -> A operand of the next layer (K block `half`)
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    float h[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) h[j] = fmaxf(v[c * 8 + j] + bias[c * 8 + j], 0.f);
+                    uint4 pk = make_uint4(pack_bf16(h[0], h[1]), pack_bf16(h[2], h[3]), pack_bf16(h[4], h[5]),
+                                          pack_bf16(h[6], h[7]));
+                    *reinterpret_cast<uint4*>(sA + (size_t)half * CHUNK_BYTES + swz_off(row, c)) = pk;
+                }
+                continue;
+            }
+            if (MODE == DEC) {
+                // ReLU(h2) stays fp32; last Linear (nout x 128) on the CUDA cores
+                const float* W2 = sF + 2 * LAT;
+                const float* b2 = W2 + a.nout * LAT;
+#pragma unroll
+                for (int j = 0; j < 64; ++j) v[j] = fmaxf(v[j] + bias[j], 0.f);
+                for (int o = 0; o < a.nout; ++o) {
+                    const float* w = W2 + o * LAT + half * 64;
+                    float acc = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 64; ++j) acc = fmaf(v[j], w[j], acc);
+                    sRed[(row * 2 + half) * 8 + o] = acc;
+                }
+                __syncthreads();
+                if (half == 0 && rvalid)
+                    for (int o = 0; o < a.nout; ++o)
+                        a.y[(size_t)grow * a.nout + o] = sRed[(row * 2) * 8 + o] + sRed[(row * 2 + 1) * 8 + o] + b2[o];
+                tc_fence_before();
+                __syncthreads();
+                continue;
+            }
+            // ---- + bias, LayerNorm (two pass, fp32)
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 64; ++j) { v[j] += bias[j]; s += v[j]; }
+            sRed[row * 2 + half] = s;
+            __syncthreads();
+            const float mean = (sRed[row * 2] + sRed[row * 2 + 1]) * (1.0f / LAT);
+            float q = 0.f;
+#pragma unroll
+            for (int j = 0; j < 64; ++j) { const float dlt = v[j] - mean; q = fmaf(dlt, dlt, q); }
+            sRed[256 + row * 2 + half] = q;
+            __syncthreads();
+            const float var = (sRed[256 + row * 2] + sRed[256 + row * 2 + 1]) * (1.0f / LAT);
+            const float rstd = 1.0f / sqrtf(var + 1e-5f);
+            const float* lg = sF + 3 * LAT + half * 64;
+            const float* lb = sF + 4 * LAT + half * 64;
+#pragma unroll
+            for (int j = 0; j < 64; ++j) v[j] = (v[j] - mean) * rstd * lg[j] + lb[j];
+
+            if (MODE == ENC) {
+                if (rvalid) {
+                    uint4* ob = reinterpret_cast<uint4*>(a.out_bf16 + (size_t)grow * LAT + half * 64);
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        ob[c] = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
+                                           pack_bf16(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16(v[c * 8 + 6], v[c * 8 + 7]));
+                    if (a.x_f32) {
+                        float4* of = reinterpret_cast<float4*>(a.x_f32 + (size_t)grow * LAT + half * 64);
+#pragma unroll
+                        for (int c = 0; c < 16; ++c) of[c] = make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]);
+                    }
+                }
+            } else if (MODE == NODE) {
+                if (rvalid) {
+                    float4* xf = reinterpret_cast<float4*>(a.x_f32 + (size_t)grow * LAT + half * 64);
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) {
+                        float4 o = xf[c];
+                        o.x += v[c * 4]; o.y += v[c * 4 + 1]; o.z += v[c * 4 + 2]; o.w += v[c * 4 + 3];
+                        xf[c] = o;
+                        v[c * 4] = o.x; v[c * 4 + 1] = o.y; v[c * 4 + 2] = o.z; v[c * 4 + 3] = o.w;
+                    }
+                    uint4* ob = reinterpret_cast<uint4*>(a.out_bf16 + (size_t)grow * LAT + half * 64);
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        ob[c] = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
+                                           pack_bf16(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16(v[c * 8 + 6], v[c * 8 + 7]));
+                }
+            } else if (MODE == EDGE) {
+                // segmented sum over the warp's 32 dst-sorted rows, 32 columns per round, staged in the
+                // (now idle) A region; lane j owns one column and adds once per segment.
+                float* st = reinterpret_cast<float*>(sA) + warp * (32 * 33);
+                const int* wd = sDst + (warp & 3) * 32;
+#pragma unroll
+                for (int rd = 0; rd < 2; ++rd) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) st[lane * 33 + j] = v[rd * 32 + j];
+                    __syncwarp();
+                    const int col = half * 64 + rd * 32 + lane;
+                    int cur = wd[0];
+                    float acc = 0.f;
+#pragma unroll 4
+                    for (int i = 0; i < 32; ++i) {
+                        const int d = wd[i];
+                        if (d != cur) {
+                            if (cur >= 0) atomicAdd(a.agg + (size_t)cur * LAT + col, acc);
+                            cur = d;
+                            acc = 0.f;
+                        }
+                        acc += st[i * 33 + lane];
+                    }
+                    if (cur >= 0) atomicAdd(a.agg + (size_t)cur * LAT + col, acc);
+                    __syncwarp();
+                }
+            }
+            // the next tile overwrites sA / TMEM: order this tile's TMEM reads and staging before it
+            tc_fence_before();
+            __syncthreads();
+        }
+    }
+    if (!weights_ready && tid == 0) mbar_wait(bar_w, 0);  // never leave a bulk copy in flight
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, TMEM_COLS);
+}
+
+// ---- graph preparation: dst-sorted edge order ---------------------------------------------------
+__global__ void gnn_edge_keys_kernel(int E, const long long* __restrict__ edge_index, uint32_t* keys, uint32_t* vals,
+                                     uint32_t* n_dev) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *n_dev = (uint32_t)E;
+    if (i >= E) return;
+    keys[i] = (uint32_t)edge_index[(size_t)E + i];  // dst = edge_index[1]
+    vals[i] = (uint32_t)i;
+}
+__global__ void gnn_edge_finish_kernel(int E, const long long* __restrict__ edge_index, const uint32_t* __restrict__ keys,
+                                       const uint32_t* __restrict__ vals, int* dst_sorted, int* src_sorted, int* perm) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= E) return;
+    const uint32_t e = vals[i];
+    dst_sorted[i] = (int)keys[i];
+    src_sorted[i] = (int)edge_index[e];
+    perm[i] = (int)e;
+}
+
+struct Dims {
+    int node_in, edge_in, node_out, steps;
+};
+static int check_dims(const csb_gnn_dims* d) {
+    if (!d) return CSB_ERR_BAD_ARG;
+    if (d->latent_dim != LAT || d->mlp_hidden_dim != LAT || d->nmlp_layers != 2) return CSB_ERR_UNSUPPORTED;
+    if (d->nnode_in < 1 || d->nnode_in > 16 || d->nedge_in < 1 || d->nedge_in > 16) return CSB_ERR_UNSUPPORTED;
+    if (d->nnode_out < 1 || d->nnode_out > 8) return CSB_ERR_UNSUPPORTED;
+    if (d->nmessage_passing_steps < 0 || d->nmessage_passing_steps > 30) return CSB_ERR_UNSUPPORTED;
+    return 0;
+}
+
+static void build_table(const csb_gnn_dims* d, PackTable& t, size_t* total_floats, size_t* total_bytes) {
+    size_t src = 0, dst = 0;
+    int n = 0;
+    auto add = [&](int mode, int k0, int n2, bool ln, float scale) {
+        UnitDesc& u = t.u[n++];
+        u.src = src; u.dst = dst; u.mode = mode; u.k0 = k0; u.n2 = n2; u.e_scale = scale;
+        src += mlp_floats(k0, n2, ln);
+        dst += unit_bytes(mode, k0, n2);
+    };
+    add(ENC, d->nnode_in, LAT, true, 1.f);
+    add(ENC, d->nedge_in, LAT, true, 1.f);
+    float sc = 1.f;
+    for (int m = 0; m < d->nmessage_passing_steps; ++m) {
+        add(EDGE, 3 * LAT, LAT, true, sc);
+        add(NODE, 2 * LAT, LAT, true, 1.f);
+        sc *= 2.f;
+    }
+    add(DEC, LAT, d->nnode_out, false, 1.f);
+    t.n = n;
+    if (total_floats) *total_floats = src;
+    if (total_bytes) *total_bytes = dst;
+}
+
+struct Workspace {
+    float* x_f32;
+    __nv_bfloat16* x_bf16;
+    float* agg;
+    __nv_bfloat16* e0;
+    size_t bytes;
+    static Workspace carve(void* ws, int N, int E) {
+        Workspace w;
+        Carver c(ws);
+        w.x_f32 = c.take<float>((size_t)N * LAT);
+        w.x_bf16 = c.take<__nv_bfloat16>((size_t)N * LAT);
+        w.agg = c.take<float>((size_t)N * LAT);
+        w.e0 = c.take<__nv_bfloat16>((size_t)E * LAT);
+        w.bytes = c.total();
+        return w;
+    }
+};
+
+struct GraphWs {
+    uint32_t *keys_a, *keys_b, *vals_a, *vals_b, *control;
+    size_t control_words, bytes;
+    static GraphWs carve(void* ws, int E) {
+        GraphWs g;
+        Carver c(ws);
+        g.keys_a = c.take<uint32_t>(E);
+        g.keys_b = c.take<uint32_t>(E);
+        g.vals_a = c.take<uint32_t>(E);
+        g.vals_b = c.take<uint32_t>(E);
+        g.control_words = 8 + 4 * 256 + sort_lookback_words((size_t)E, 4);
+        g.control = c.take<uint32_t>(g.control_words);
+        g.bytes = c.total();
+        return g;
+    }
+};
+
+template <int MODE>
+static int launch_role(const Args& a, int kin, int nout, cudaStream_t stream, const char* name) {
+    static bool configured = false;
+    const size_t smem = smem_bytes(MODE, kin, nout);
+    if (!configured) {
+        CSB_CUDA_TRY(cudaFuncSetAttribute(gnn_mlp_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 1024));
+        configured = true;
+    }
+    if (smem > 232448 - 1024) return CSB_ERR_UNSUPPORTED;
+    const int tiles = (a.rows + TILE_M - 1) / TILE_M;
+    if (tiles == 0) return 0;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int grid = tiles < sms ? tiles : sms;
+    CSB_LAUNCH(name, stream, gnn_mlp_kernel<MODE><<<grid, THREADS, smem, stream>>>(a));
+    return 0;
+}
+
+}  // namespace gnn
+}  // namespace csb
+
+using namespace csb;
+using namespace csb::gnn;
+
+extern "C" {
+
+size_t csb_gnn_param_floats(const csb_gnn_dims* d) {
+    if (check_dims(d)) return 0;
+    PackTable t;
+    size_t f = 0;
+    build_table(d, t, &f, nullptr);
+    return f;
+}
+size_t csb_gnn_packed_bytes(const csb_gnn_dims* d) {
+    if (check_dims(d)) return 0;
+    PackTable t;
+    size_t b = 0;
+    build_table(d, t, nullptr, &b);
+    return b;
+}
+int csb_gnn_pack(const csb_gnn_dims* d, const float* flat_params, void* packed, void* stream_) {
+    int rc = check_dims(d);
+    if (rc) return rc;
+    if (!flat_params || !packed) return CSB_ERR_BAD_ARG;
+    PackTable t;
+    build_table(d, t, nullptr, nullptr);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CSB_LAUNCH("gnn_pack", stream, gnn_pack_kernel<<<t.n, 256, 0, stream>>>(flat_params, (uint8_t*)packed, t));
+    return 0;
+}
+
+size_t csb_gnn_graph_workspace_bytes(int E) { return GraphWs::carve(nullptr, E < 0 ? 0 : E).bytes; }
+int csb_gnn_prepare_graph(int N, int E, const int64_t* edge_index, int32_t* dst_sorted, int32_t* src_sorted,
+                          int32_t* perm, void* ws, size_t ws_bytes, void* stream_) {
+    if (N < 0 || E < 0) return CSB_ERR_BAD_ARG;
+    if (E == 0) return 0;
+    if (!edge_index || !dst_sorted || !src_sorted || !perm || !ws) return CSB_ERR_BAD_ARG;
+    GraphWs g = GraphWs::carve(ws, E);
+    if (ws_bytes < g.bytes) return CSB_ERR_WORKSPACE;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CSB_CUDA_TRY(cudaMemsetAsync(g.control, 0, g.control_words * sizeof(uint32_t), stream));
+    const int blocks = (E + 255) / 256;
+    CSB_LAUNCH("gnn_edge_keys", stream, gnn_edge_keys_kernel<<<blocks, 256, 0, stream>>>(
+        E, (const long long*)edge_index, g.keys_a, g.vals_a, g.control));
+    int side = 0;
+    int rc = radix_sort_pairs(g.keys_a, g.keys_b, g.vals_a, g.vals_b, g.control, (size_t)E,
+                              higher_msb((uint32_t)(N > 0 ? N - 1 : 0)), g.control + 8, g.control + 4,
+                              g.control + 8 + 4 * 256, &side, stream);
+    if (rc) return rc;
+    CSB_LAUNCH("gnn_edge_finish", stream, gnn_edge_finish_kernel<<<blocks, 256, 0, stream>>>(
+        E, (const long long*)edge_index, side ? g.keys_b : g.keys_a, side ? g.vals_b : g.vals_a, dst_sorted,
+        src_sorted, perm));
+    return 0;
+}
+
+size_t csb_gnn_workspace_bytes(const csb_gnn_dims* d, int N, int E) {
+    if (check_dims(d) || N < 0 || E < 0) return 0;
+    return Workspace::carve(nullptr, N, E).bytes;
+}
+
+int csb_gnn_forward(const csb_gnn_dims* d, const void* packed, int N, int E, const float* x,
+                    const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
+                    const int32_t* perm, float* y, float* x_latent_out, void* ws, size_t ws_bytes, void* stream_) {
+    int rc = check_dims(d);
+    if (rc) return rc;
+    if (N < 0 || E < 0) return CSB_ERR_BAD_ARG;
+    if (N == 0) return 0;
+    if (!packed || !x || !y || !ws) return CSB_ERR_BAD_ARG;
+    if (E > 0 && (!edge_features || !dst_sorted || !src_sorted || !perm)) return CSB_ERR_BAD_ARG;
+    Workspace w = Workspace::carve(ws, N, E);
+    if (ws_bytes < w.bytes) return CSB_ERR_WORKSPACE;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    PackTable t;
+    build_table(d, t, nullptr, nullptr);
+    const uint8_t* pk = (const uint8_t*)packed;
+
+    CSB_CUDA_TRY(cudaMemsetAsync(w.agg, 0, (size_t)N * LAT * sizeof(float), stream));
+    Args a{};
+    a.N = N;
+    // encoders
+    a.unit = pk + t.u[0].dst; a.rows = N; a.kin = d->nnode_in; a.nout = LAT;
+    a.in = x; a.perm = nullptr; a.out_bf16 = w.x_bf16; a.x_f32 = w.x_f32;
+    rc = launch_role<ENC>(a, a.kin, LAT, stream, "gnn_encode");
+    if (rc) return rc;
+    if (E > 0) {
+        a.unit = pk + t.u[1].dst; a.rows = E; a.kin = d->nedge_in;
+        a.in = edge_features; a.perm = perm; a.out_bf16 = w.e0; a.x_f32 = nullptr;
+        rc = launch_role<ENC>(a, a.kin, LAT, stream, "gnn_encode");
+        if (rc) return rc;
+    }
+    // processor
+    for (int m = 0; m < d->nmessage_passing_steps; ++m) {
+        Args e{};
+        e.N = N; e.kin = 0; e.nout = LAT;
+        e.unit = pk + t.u[2 + 2 * m].dst; e.rows = E;
+        e.dst_sorted = dst_sorted; e.src_sorted = src_sorted; e.x_bf16 = w.x_bf16; e.e0 = w.e0; e.agg = w.agg;
+        rc = launch_role<EDGE>(e, 0, LAT, stream, "gnn_edge");
+        if (rc) return rc;
+        Args n{};
+        n.N = N; n.kin = 0; n.nout = LAT;
+        n.unit = pk + t.u[3 + 2 * m].dst; n.rows = N;
+        n.agg = w.agg; n.x_bf16 = w.x_bf16; n.x_f32 = w.x_f32; n.out_bf16 = w.x_bf16;
+        rc = launch_role<NODE>(n, 0, LAT, stream, "gnn_node");
+        if (rc) return rc;
+    }
+    if (x_latent_out)
+        CSB_CUDA_TRY(cudaMemcpyAsync(x_latent_out, w.x_f32, (size_t)N * LAT * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+    // decoder
+    Args c{};
+    c.N = N; c.kin = 0; c.nout = d->nnode_out;
+    c.unit = pk + t.u[t.n - 1].dst; c.rows = N; c.x_bf16 = w.x_bf16; c.y = y;
+    return launch_role<DEC>(c, 0, d->nnode_out, stream, "gnn_decode");
+}
+
+}  // extern "C"

@@ -1,0 +1,4 @@
+"""Drop-in for the reference's `meshnet` GNN modules (meshnet/graph_network.py), backed by the sm_100a
+kernels of libcloth_splatting_b200.so (csrc/gnn.cu).  No CPU fallback."""
+from .graph_network import (Decoder, EncodeProcessDecode, Encoder, InteractionNetwork, Processor,  # noqa: F401
+                            build_mlp)

@@ -1,0 +1,229 @@
+"""`meshnet.graph_network`: Encode-Process-Decode GNN with the reference's constructor, forward signature
+and state_dict key names (meshnet/graph_network.py of KTH-RPL/cloth-splatting):
+
+  build_mlp :7-45, Encoder :48-111, InteractionNetwork :114-222, Processor :224-292, Decoder :295-332,
+  EncodeProcessDecode :335-408.
+
+The sub-modules only own the parameters (so `state_dict()` / `load_state_dict()` exchange checkpoints
+with the reference: `_encoder.node_fn.0.NN-0.weight`, `_processor.gnn_stacks.3.edge_fn.1.bias`,
+`_decoder.node_fn.NN-2.weight`, ...).  The arithmetic of `EncodeProcessDecode.forward` runs in
+csb_gnn_forward (include/cloth_splatting_b200.h): bf16 tcgen05 MLPs with fp32 accumulation, LayerNorm
+and residuals in fp32.  Semantics follow torch_geometric's MessagePassing as the reference uses it:
+messages are MLP(cat[x[dst], x[src], e]) summed at dst (= edge_index[1]); the edge latents a step returns
+are its *input* latents, so every step doubles them (graph_network.py:173-176,201-222).
+"""
+import ctypes
+from typing import List
+
+import torch
+import torch.nn as nn
+
+import csb_cabi as _abi
+
+
+def build_mlp(input_size: int, hidden_layer_sizes: List[int], output_size: int = None,
+              output_activation: nn.Module = nn.Identity, activation: nn.Module = nn.ReLU) -> nn.Module:
+    """nn.Sequential of Linear layers named NN-k with activations Act-k (graph_network.py:7-45)."""
+    sizes = [input_size] + list(hidden_layer_sizes)
+    if output_size:
+        sizes.append(output_size)
+    n = len(sizes) - 1
+    acts = [activation] * n
+    acts[-1] = output_activation
+    mlp = nn.Sequential()
+    for i in range(n):
+        mlp.add_module("NN-" + str(i), nn.Linear(sizes[i], sizes[i + 1]))
+        mlp.add_module("Act-" + str(i), acts[i]())
+    return mlp
+
+
+class _ParamsOnly(nn.Module):
+    def forward(self, *args, **kwargs):  # pragma: no cover
+        raise RuntimeError(f"{type(self).__name__} only owns parameters here; call EncodeProcessDecode.forward "
+                           "(the fused CUDA path)")
+
+
+class Encoder(_ParamsOnly):
+    def __init__(self, nnode_in_features, nnode_out_features, nedge_in_features, nedge_out_features, nmlp_layers,
+                 mlp_hidden_dim):
+        super().__init__()
+        hidden = [mlp_hidden_dim for _ in range(nmlp_layers)]
+        self.node_fn = nn.Sequential(build_mlp(nnode_in_features, hidden, nnode_out_features),
+                                     nn.LayerNorm(nnode_out_features))
+        self.edge_fn = nn.Sequential(build_mlp(nedge_in_features, hidden, nedge_out_features),
+                                     nn.LayerNorm(nedge_out_features))
+
+
+class InteractionNetwork(_ParamsOnly):
+    def __init__(self, nnode_in, nnode_out, nedge_in, nedge_out, nmlp_layers, mlp_hidden_dim):
+        super().__init__()
+        hidden = [mlp_hidden_dim for _ in range(nmlp_layers)]
+        self.node_fn = nn.Sequential(build_mlp(nnode_in + nedge_out, hidden, nnode_out), nn.LayerNorm(nnode_out))
+        self.edge_fn = nn.Sequential(build_mlp(nnode_in + nnode_in + nedge_in, hidden, nedge_out),
+                                     nn.LayerNorm(nedge_out))
+
+
+class Processor(_ParamsOnly):
+    def __init__(self, nnode_in, nnode_out, nedge_in, nedge_out, nmessage_passing_steps, nmlp_layers, mlp_hidden_dim):
+        super().__init__()
+        self.gnn_stacks = nn.ModuleList([
+            InteractionNetwork(nnode_in, nnode_out, nedge_in, nedge_out, nmlp_layers, mlp_hidden_dim)
+            for _ in range(nmessage_passing_steps)])
+
+
+class Decoder(_ParamsOnly):
+    def __init__(self, nnode_in, nnode_out, nmlp_layers, mlp_hidden_dim):
+        super().__init__()
+        self.node_fn = build_mlp(nnode_in, [mlp_hidden_dim for _ in range(nmlp_layers)], nnode_out)
+
+
+class GnnDims(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int) for n in ("nnode_in", "nnode_out", "nedge_in", "latent_dim",
+                                            "nmessage_passing_steps", "nmlp_layers", "mlp_hidden_dim")]
+
+
+def _bind(lib):
+    if getattr(lib, "_gnn_bound", False):
+        return
+    P, c_int, c_size_t, c_void_p = ctypes.POINTER, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p
+    lib.csb_gnn_param_floats.restype = c_size_t
+    lib.csb_gnn_param_floats.argtypes = [P(GnnDims)]
+    lib.csb_gnn_packed_bytes.restype = c_size_t
+    lib.csb_gnn_packed_bytes.argtypes = [P(GnnDims)]
+    lib.csb_gnn_pack.restype = c_int
+    lib.csb_gnn_pack.argtypes = [P(GnnDims), c_void_p, c_void_p, c_void_p]
+    lib.csb_gnn_graph_workspace_bytes.restype = c_size_t
+    lib.csb_gnn_graph_workspace_bytes.argtypes = [c_int]
+    lib.csb_gnn_prepare_graph.restype = c_int
+    lib.csb_gnn_prepare_graph.argtypes = [c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
+                                          c_void_p]
+    lib.csb_gnn_workspace_bytes.restype = c_size_t
+    lib.csb_gnn_workspace_bytes.argtypes = [P(GnnDims), c_int, c_int]
+    lib.csb_gnn_forward.restype = c_int
+    lib.csb_gnn_forward.argtypes = [P(GnnDims), c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+    lib._gnn_bound = True
+
+
+class PreparedGraph:
+    """dst-sorted edge order of a static topology (csb_gnn_prepare_graph)."""
+
+    def __init__(self, edge_index: torch.Tensor, num_nodes: int):
+        lib = _abi.lib()
+        _bind(lib)
+        if edge_index.dim() != 2 or edge_index.size(0) != 2:
+            raise ValueError("edge_index must have shape [2, E]")
+        if not edge_index.is_cuda:
+            raise ValueError("edge_index must be a CUDA tensor")
+        ei = edge_index.to(torch.int64).contiguous()
+        E = ei.size(1)
+        dev = ei.device
+        self.N, self.E = int(num_nodes), int(E)
+        self.dst = torch.empty(E, dtype=torch.int32, device=dev)
+        self.src = torch.empty(E, dtype=torch.int32, device=dev)
+        self.perm = torch.empty(E, dtype=torch.int32, device=dev)
+        if E:
+            ws = torch.empty(lib.csb_gnn_graph_workspace_bytes(E), dtype=torch.uint8, device=dev)
+            with torch.cuda.device(dev):
+                rc = lib.csb_gnn_prepare_graph(self.N, E, ei.data_ptr(), self.dst.data_ptr(), self.src.data_ptr(),
+                                               self.perm.data_ptr(), ws.data_ptr(), ws.numel(),
+                                               _abi.current_stream_ptr())
+            _abi.check(rc, "csb_gnn_prepare_graph")
+
+
+class EncodeProcessDecode(nn.Module):
+    def __init__(self, nnode_in_features: int, nnode_out_features: int, nedge_in_features: int, latent_dim: int,
+                 nmessage_passing_steps: int, nmlp_layers: int, mlp_hidden_dim: int):
+        super().__init__()
+        self._encoder = Encoder(nnode_in_features, latent_dim, nedge_in_features, latent_dim, nmlp_layers,
+                                mlp_hidden_dim)
+        self._processor = Processor(latent_dim, latent_dim, latent_dim, latent_dim, nmessage_passing_steps,
+                                    nmlp_layers, mlp_hidden_dim)
+        self._decoder = Decoder(latent_dim, nnode_out_features, nmlp_layers, mlp_hidden_dim)
+        self._dims = GnnDims(nnode_in_features, nnode_out_features, nedge_in_features, latent_dim,
+                             nmessage_passing_steps, nmlp_layers, mlp_hidden_dim)
+        self._packed = None
+        self._packed_key = None
+        self._graph = None
+        self._graph_key = None
+        self._ws = None
+        self.last_latent = None  # filled when forward(..., return_latent=True)
+
+    # ---- parameters -> packed image -------------------------------------------------------------
+    def _ordered_params(self):
+        def mlp(seq, ln):
+            out = []
+            for m in seq:
+                if isinstance(m, nn.Linear):
+                    out += [m.weight, m.bias]
+            if ln is not None:
+                out += [ln.weight, ln.bias]
+            return out
+
+        ps = mlp(self._encoder.node_fn[0], self._encoder.node_fn[1]) + mlp(self._encoder.edge_fn[0],
+                                                                            self._encoder.edge_fn[1])
+        for g in self._processor.gnn_stacks:
+            ps += mlp(g.edge_fn[0], g.edge_fn[1]) + mlp(g.node_fn[0], g.node_fn[1])
+        ps += mlp(self._decoder.node_fn, None)
+        return ps
+
+    def _packed_weights(self, dev):
+        lib = _abi.lib()
+        ps = self._ordered_params()
+        key = (str(dev),) + tuple((p.data_ptr(), p._version) for p in ps)
+        if self._packed is not None and key == self._packed_key:
+            return self._packed
+        nfl = lib.csb_gnn_param_floats(ctypes.byref(self._dims))
+        if nfl == 0:
+            raise NotImplementedError(
+                "EncodeProcessDecode (B200): only latent_dim == mlp_hidden_dim == 128 and nmlp_layers == 2 are built "
+                "(the reference defaults); there is no fallback path")
+        flat = torch.cat([p.detach().reshape(-1).to(device=dev, dtype=torch.float32) for p in ps])
+        if flat.numel() != nfl:
+            raise RuntimeError(f"parameter count {flat.numel()} != {nfl} expected by the C-ABI")
+        packed = torch.empty(lib.csb_gnn_packed_bytes(ctypes.byref(self._dims)), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.csb_gnn_pack(ctypes.byref(self._dims), flat.data_ptr(), packed.data_ptr(),
+                                  _abi.current_stream_ptr())
+        _abi.check(rc, "csb_gnn_pack")
+        self._packed, self._packed_key = packed, key
+        return packed
+
+    def prepare_graph(self, edge_index, num_nodes):
+        key = (edge_index.data_ptr(), edge_index._version, tuple(edge_index.shape), int(num_nodes), str(edge_index.device))
+        if self._graph is None or key != self._graph_key:
+            self._graph, self._graph_key = PreparedGraph(edge_index, num_nodes), key
+        return self._graph
+
+    def forward(self, x: torch.Tensor, edge_index: torch.Tensor, edge_features: torch.Tensor, return_latent=False):
+        lib = _abi.lib()
+        _bind(lib)
+        if not x.is_cuda:
+            raise ValueError("EncodeProcessDecode (B200) needs CUDA tensors; there is no CPU path")
+        if torch.is_grad_enabled() and (x.requires_grad or edge_features.requires_grad or
+                                        any(p.requires_grad for p in self.parameters())):
+            raise NotImplementedError("EncodeProcessDecode (B200): the backward pass is not built yet; call under "
+                                      "torch.no_grad() (the reference's rollout does, train_meshnet_sim.py:92-160)")
+        dev = x.device
+        N, E = x.size(0), edge_index.size(1)
+        if x.size(1) != self._dims.nnode_in or edge_features.size(1) != self._dims.nedge_in:
+            raise ValueError("feature widths do not match the constructor arguments")
+        xin = x.detach().to(torch.float32).contiguous()
+        ef = edge_features.detach().to(torch.float32).contiguous()
+        packed = self._packed_weights(dev)
+        g = self.prepare_graph(edge_index, N)
+        y = torch.empty((N, self._dims.nnode_out), dtype=torch.float32, device=dev)
+        lat = torch.empty((N, self._dims.latent_dim), dtype=torch.float32, device=dev) if return_latent else None
+        need = lib.csb_gnn_workspace_bytes(ctypes.byref(self._dims), N, E)
+        if self._ws is None or self._ws.numel() < need or self._ws.device != dev:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.csb_gnn_forward(ctypes.byref(self._dims), packed.data_ptr(), N, E, xin.data_ptr(),
+                                     ef.data_ptr() if E else None, g.dst.data_ptr() if E else None,
+                                     g.src.data_ptr() if E else None, g.perm.data_ptr() if E else None, y.data_ptr(),
+                                     lat.data_ptr() if lat is not None else None, self._ws.data_ptr(),
+                                     self._ws.numel(), _abi.current_stream_ptr())
+        _abi.check(rc, "csb_gnn_forward")
+        if return_latent:
+            self.last_latent = lat
+        return y

@@ -146,6 +146,45 @@ size_t csb_dist_cuda2_bytes(int P);
  * other points (KNN/simple_knn.cu:147-183).  points f32[P,3], mean_dists f32[P]. */
 int csb_dist_cuda2(int P, const float* points, float* mean_dists, void* ws, size_t ws_bytes, void* stream);
 
+/* ------------------------------------------------------------------------- *
+ * meshnet GNN (EncodeProcessDecode.forward, meshnet/graph_network.py:387-408)
+ * ------------------------------------------------------------------------- */
+
+/* Constructor arguments of EncodeProcessDecode (meshnet/graph_network.py:336-345).  Supported:
+ * latent_dim == mlp_hidden_dim == 128, nmlp_layers == 2 (the reference's defaults,
+ * train_meshnet_sim.py:645-650), nnode_in / nedge_in <= 16, nnode_out <= 8, steps <= 30;
+ * anything else returns CSB_ERR_UNSUPPORTED. */
+typedef struct csb_gnn_dims {
+    int nnode_in, nnode_out, nedge_in, latent_dim, nmessage_passing_steps, nmlp_layers, mlp_hidden_dim;
+} csb_gnn_dims;
+
+/* Parameters are handed over as ONE flat fp32 device buffer, MLP after MLP in the order
+ *   _encoder.node_fn, _encoder.edge_fn, then for every step m: _processor.gnn_stacks.m.edge_fn,
+ *   _processor.gnn_stacks.m.node_fn, then _decoder.node_fn;
+ * each MLP as NN-0.weight [128,in] (row major, nn.Linear layout), NN-0.bias, NN-1.weight, NN-1.bias,
+ * NN-2.weight [out,128], NN-2.bias, then (all but the decoder) LayerNorm weight, bias.
+ * csb_gnn_pack converts it into the bf16 / swizzled image the kernels keep resident in shared memory
+ * (also folds the reference's e_m = 2^m e_0 edge-latent doubling, graph_network.py:173-176, into the
+ * edge block of every step's first edge Linear). */
+size_t csb_gnn_param_floats(const csb_gnn_dims* dims);
+size_t csb_gnn_packed_bytes(const csb_gnn_dims* dims);
+int csb_gnn_pack(const csb_gnn_dims* dims, const float* flat_params, void* packed, void* stream);
+
+/* Static topology: edge_index i64[2,E] (row 0 = src, row 1 = dst; torch_geometric flow
+ * source_to_target, messages are summed at dst, graph_network.py:136,197).  Writes the stable
+ * dst-sorted edge order: dst_sorted[i], src_sorted[i] and perm[i] = original edge id of slot i. */
+size_t csb_gnn_graph_workspace_bytes(int E);
+int csb_gnn_prepare_graph(int N, int E, const int64_t* edge_index, int32_t* dst_sorted, int32_t* src_sorted,
+                          int32_t* perm, void* ws, size_t ws_bytes, void* stream);
+
+/* y[N, nnode_out] = EncodeProcessDecode(x[N, nnode_in], edge_index, edge_features[E, nedge_in]).
+ * edge_features are in the ORIGINAL edge order (perm is applied inside).  x_latent_out (optional,
+ * f32[N,128]) receives the node latents after the last message-passing step (for parity tests). */
+size_t csb_gnn_workspace_bytes(const csb_gnn_dims* dims, int N, int E);
+int csb_gnn_forward(const csb_gnn_dims* dims, const void* packed, int N, int E, const float* x,
+                    const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
+                    const int32_t* perm, float* y, float* x_latent_out, void* ws, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

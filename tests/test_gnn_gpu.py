@@ -1,0 +1,129 @@
+"""GPU parity of the meshnet GNN forward (csb_gnn_forward through the drop-in EncodeProcessDecode)
+against the CPU oracle (oracle/gnn_oracle.py, fp32 and bf16-emulating) and the reference goldens.
+
+Tolerances (north_star: "GNN outputs within bf16 tolerance of the reference fp32 path"):
+  vs the bf16-emulating oracle (same roundings, different summation order): 2e-3 of the output scale;
+  vs the fp32 oracle / reference golden: 3e-2 of the output scale (bf16 has 8 mantissa bits and the
+  network is 15 residual steps deep)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import conftest
+import csb_synth as S
+import make_golden_gnn as G
+from oracle import gnn_oracle
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(conftest.ROOT, "tests", "golden")
+TIGHT, LOOSE = 2e-3, 3e-2
+
+
+def _model(seed=0, steps=15):
+    from meshnet import EncodeProcessDecode
+
+    if steps == 15:
+        return G.make_state_dict(seed, EncodeProcessDecode).cuda()
+    torch.manual_seed(seed)
+    return EncodeProcessDecode(8, 3, 4, 128, steps, 2, 128).eval().cuda()
+
+
+def _run(m, x, ei, ef, latent=False):
+    with torch.no_grad():
+        y = m(torch.from_numpy(x).cuda(), torch.from_numpy(ei).cuda(), torch.from_numpy(ef).cuda(), return_latent=latent)
+    torch.cuda.synchronize()
+    return y.cpu()
+
+
+def _scale(t):
+    return max(float(t.abs().max()), 1e-6)
+
+
+@pytest.mark.parametrize("name", list(G.CASES))
+def test_forward_vs_reference_golden_and_oracle(name):
+    fx = np.load(os.path.join(GOLDEN, name + ".npz"))
+    n, seed = int(fx["n"]), int(fx["seed"])
+    m = _model(seed)
+    x, ei, ef, _, _ = S.gnn_inputs(n, seed)
+    y = _run(m, x, ei, ef, latent=True)
+    sd = {k: v.cpu() for k, v in m.state_dict().items()}
+    yb, inter = gnn_oracle.forward(sd, torch.from_numpy(x), torch.from_numpy(ei), torch.from_numpy(ef),
+                                   emulate_bf16=True, return_intermediates=True)
+    lat = m.last_latent.cpu()
+    assert float((lat - inter["x_final"]).abs().max()) < TIGHT * _scale(inter["x_final"]) * 4
+    assert float((y - yb).abs().max()) < TIGHT * _scale(yb) * 4
+    assert float((y - torch.from_numpy(fx["y"])).abs().max()) < LOOSE * _scale(torch.from_numpy(fx["y"]))
+    assert float((lat - torch.from_numpy(fx["x_final"])).abs().max()) < LOOSE * _scale(torch.from_numpy(fx["x_final"]))
+
+
+@pytest.mark.parametrize("steps", [0, 1, 3])
+def test_few_steps_vs_oracle(steps):
+    m = _model(5, steps)
+    x, ei, ef, _, _ = S.gnn_inputs(9, 1)
+    y = _run(m, x, ei, ef)
+    sd = {k: v.cpu() for k, v in m.state_dict().items()}
+    yb = gnn_oracle.forward(sd, torch.from_numpy(x), torch.from_numpy(ei), torch.from_numpy(ef), emulate_bf16=True)
+    assert float((y - yb).abs().max()) < TIGHT * _scale(yb)
+
+
+def test_prepared_graph_is_stable_dst_sort():
+    from meshnet.graph_network import PreparedGraph
+
+    _, ei, _, _, _ = S.gnn_inputs(20, 0)
+    g = PreparedGraph(torch.from_numpy(ei).cuda(), 400)
+    torch.cuda.synchronize()
+    order = np.argsort(ei[1], kind="stable")
+    assert np.array_equal(g.perm.cpu().numpy(), order.astype(np.int32))
+    assert np.array_equal(g.dst.cpu().numpy(), ei[1][order].astype(np.int32))
+    assert np.array_equal(g.src.cpu().numpy(), ei[0][order].astype(np.int32))
+
+
+def test_edge_order_invariance_and_node_relabelling():
+    m = _model(0)
+    x, ei, ef, _, _ = S.gnn_inputs(11, 2)
+    y = _run(m, x, ei, ef)
+    rng = np.random.default_rng(0)
+    pe = rng.permutation(ei.shape[1])
+    y2 = _run(m, x, np.ascontiguousarray(ei[:, pe]), np.ascontiguousarray(ef[pe]))
+    assert float((y - y2).abs().max()) < TIGHT * _scale(y)
+    pn = rng.permutation(x.shape[0])  # new label of node i is inv[i]
+    inv = np.empty_like(pn)
+    inv[pn] = np.arange(len(pn))
+    y3 = _run(m, np.ascontiguousarray(x[pn]), np.ascontiguousarray(inv[ei]), ef)
+    assert float((y3 - y[pn]).abs().max()) < TIGHT * _scale(y)
+
+
+def test_batched_graphs_equal_single_graphs():
+    m = _model(0)
+    parts = [S.gnn_inputs(n, s) for n, s in ((6, 0), (9, 1), (13, 2))]
+    ys = [_run(m, p[0], p[1], p[2]) for p in parts]
+    off, xs, eis, efs = 0, [], [], []
+    for p in parts:
+        xs.append(p[0]); eis.append(p[1] + off); efs.append(p[2])
+        off += p[0].shape[0]
+    yb = _run(m, np.concatenate(xs), np.ascontiguousarray(np.concatenate(eis, 1)), np.concatenate(efs))
+    assert float((yb - torch.cat(ys)).abs().max()) < TIGHT * _scale(yb)
+
+
+def test_ragged_sizes_and_no_edges():
+    m = _model(1, 2)
+    for n in (2, 12):  # N = 4 (one partial tile), 144 (two node tiles), E not a multiple of 128
+        x, ei, ef, _, _ = S.gnn_inputs(n, 4)
+        y = _run(m, x, ei, ef)
+        sd = {k: v.cpu() for k, v in m.state_dict().items()}
+        yb = gnn_oracle.forward(sd, torch.from_numpy(x), torch.from_numpy(ei), torch.from_numpy(ef), emulate_bf16=True)
+        assert float((y - yb).abs().max()) < TIGHT * _scale(yb)
+    x, ei, ef, _, _ = S.gnn_inputs(3, 0)
+    y = _run(m, x, ei[:, :0], ef[:0])
+    sd = {k: v.cpu() for k, v in m.state_dict().items()}
+    yb = gnn_oracle.forward(sd, torch.from_numpy(x), torch.from_numpy(ei[:, :0]), torch.from_numpy(ef[:0]), emulate_bf16=True)
+    assert float((y - yb).abs().max()) < TIGHT * _scale(yb)
+
+
+def test_grad_request_fails_loudly():
+    m = _model(0, 1)
+    x, ei, ef, _, _ = S.gnn_inputs(4, 0)
+    with pytest.raises(NotImplementedError):
+        m(torch.from_numpy(x).cuda(), torch.from_numpy(ei).cuda(), torch.from_numpy(ef).cuda())
