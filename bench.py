@@ -130,6 +130,117 @@ def batches(n, size=16):
     return [list(range(i, min(n, i + size))) for i in range(0, n, size)]
 
 
+
+# ------------------------------------------------------------------------------------------
+# GNN leg (BASELINE.json metric part 2: "GNN graphs/s per GPU")
+# ------------------------------------------------------------------------------------------
+def gnn_flops(N, E, steps=15, nin=8, ein=4, nout=3):
+    return steps * (163840.0 * E + 131072.0 * N) + 2.0 * N * (nin * 128 + 2 * 128 * 128) + \
+        2.0 * E * (ein * 128 + 2 * 128 * 128) + 2.0 * N * (2 * 128 * 128 + nout * 128)
+
+
+def gnn_batch_inputs(n, graphs, seed=4):
+    """`graphs` copies of the n x n cloth as one disjoint-union batch (PyG Batch semantics)."""
+    x, ei, ef, _, _ = S.gnn_inputs(n, seed)
+    N = x.shape[0]
+    xs = np.tile(x, (graphs, 1))
+    efs = np.tile(ef, (graphs, 1))
+    eis = np.concatenate([ei + g * N for g in range(graphs)], 1)
+    return xs, np.ascontiguousarray(eis), efs
+
+
+def _time_cuda(fn, iters, warm, flush=None):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ms = []
+    st = torch.cuda.current_stream()
+    for _ in range(iters):
+        if flush:
+            flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(st)
+        fn()
+        b.record(st)
+        b.synchronize()
+        ms.append(a.elapsed_time(b))
+    return statistics.median(ms), ms
+
+
+def gnn_bench(dev, impl, peaks, flush, with_cpu=True, iters=30):
+    """C1 (one 20x20 graph, one-step prediction = forward) and a 128-graph 40x40 batch, forward only."""
+    from oracle import gnn_oracle
+
+    out = {"metric": "GNN forward graphs/s", "unit": "graphs/s", "dtype": "bf16 (fp32 accumulate, LN, residuals)",
+           "impl": impl}
+    from meshnet import EncodeProcessDecode
+
+    torch.manual_seed(0)
+    model = EncodeProcessDecode(8, 3, 4, 128, 15, 2, 128).eval().to(dev)
+    sd = {k: v.detach() for k, v in model.state_dict().items()}
+    cases = {"c1_20x20": (20, 1), "batch128_40x40": (40, 128)}
+    for name, (n, graphs) in cases.items():
+        x, ei, ef = gnn_batch_inputs(n, graphs)
+        N, E = x.shape[0], ei.shape[1]
+        xt, eit, eft = torch.from_numpy(x).to(dev), torch.from_numpy(ei).to(dev), torch.from_numpy(ef).to(dev)
+        xh, efh = torch.from_numpy(x).pin_memory(), torch.from_numpy(ef).pin_memory()
+        yh = torch.empty((N, 3), dtype=torch.float32).pin_memory()
+        if impl == "b200":
+            def step():
+                with torch.no_grad():
+                    return model(xt, eit, eft)
+
+            def e2e():
+                xt.copy_(xh, non_blocking=True)
+                eft.copy_(efh, non_blocking=True)
+                with torch.no_grad():
+                    y = model(xt, eit, eft)
+                yh.copy_(y, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+        else:
+            def step():
+                with torch.no_grad():
+                    return gnn_oracle.forward(sd, xt, eit, eft, device=dev)
+
+            def e2e():
+                xt.copy_(xh, non_blocking=True)
+                eft.copy_(efh, non_blocking=True)
+                with torch.no_grad():
+                    y = gnn_oracle.forward(sd, xt, eit, eft, device=dev)
+                yh.copy_(y, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+        it = iters if graphs == 1 else max(5, iters // 3)
+        ms, _ = _time_cuda(step, it, 3, flush)
+        ms_warm, _ = _time_cuda(step, it, 3, None)
+        ms_e2e, _ = _time_cuda(e2e, it, 3, flush)
+        fl = gnn_flops(N, E)
+        peak = float(peaks.get("bf16_tflops", 1590.0))
+        out[name] = {"graphs": graphs, "nodes": N, "edges": E, "ms_per_forward": ms, "ms_l2_warm": ms_warm,
+                     "graphs_per_s": graphs / (ms * 1e-3), "e2e_graphs_per_s": graphs / (ms_e2e * 1e-3),
+                     "e2e_ms": ms_e2e, "h2d_bytes": int(xh.numel() * 4 + efh.numel() * 4), "d2h_bytes": int(yh.numel() * 4),
+                     "tflops": fl / (ms * 1e-3) / 1e12,
+                     "roofline": {"bound": "tensor", "achieved": fl / (ms * 1e-3) / 1e12, "peak": peak,
+                                  "unit": "TFLOP/s", "frac": fl / (ms * 1e-3) / 1e12 / peak,
+                                  "peak_source": "measured" if peaks else "fallback"}}
+    if with_cpu:
+        x, ei, ef = gnn_batch_inputs(20, 1)
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        sdc = {k: v.cpu() for k, v in sd.items()}
+        xt, eit, eft = torch.from_numpy(x), torch.from_numpy(ei), torch.from_numpy(ef)
+        n, t0 = 0, time.perf_counter()
+        while True:
+            with torch.no_grad():
+                gnn_oracle.forward(sdc, xt, eit, eft)
+            n += 1
+            if time.perf_counter() - t0 > 8.0 or n >= 100:
+                break
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": n / dt, "unit": "graphs/s", "cores": cores, "kind": "port",
+                               "sample": f"{n} x C1 forward (20x20 graph) with the fp32 torch restatement of "
+                                         "meshnet/graph_network.py (oracle/gnn_oracle.py) on the host cores"}
+    return out
+
 # ------------------------------------------------------------------------------------------
 # product arm
 # ------------------------------------------------------------------------------------------
@@ -300,6 +411,10 @@ def run_b200(args, rank, world, dev):
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(g_np, cams, dl_np)
+        if not args.no_gnn:
+            l0 = lib.csb_launch_count()
+            line["gnn"] = gnn_bench(dev, "b200", peaks, flush, with_cpu=(world == 1 and not args.no_cpu_baseline))
+            line["gnn"]["gpu_launches"] = int(lib.csb_launch_count() - l0)
         print(json.dumps(line), flush=True)
 
 
@@ -425,6 +540,15 @@ def run_reference(args, rank, world, dev):
                                 f"{V} views sequentially per step"},
         gpu_launches=0)
     base["config"]["l2"] = "flushed between steps (256 MB write)"
+    if not args.no_gnn:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        # the reference's GNN = stock PyTorch fp32 ops (index_select, cat, addmm, layer_norm, index_add_); its
+        # op sequence, restated in oracle/gnn_oracle.py (torch_geometric is not installed), timed on this B200
+        base["gnn"] = gnn_bench(dev, "reference", peaks, flush, with_cpu=True)
     print(json.dumps(base), flush=True)
 
 
@@ -436,6 +560,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gnn", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 

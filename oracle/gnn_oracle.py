@@ -50,12 +50,12 @@ def count_layers(sd, prefix):
     return n
 
 
-def forward(sd, x, edge_index, edge_features, emulate_bf16=False, return_intermediates=False):
+def forward(sd, x, edge_index, edge_features, emulate_bf16=False, return_intermediates=False, device="cpu"):
     """EncodeProcessDecode.forward (graph_network.py:387-408) -> f32[N, nnode_out]."""
-    sd = {k: v.detach().to(torch.float32).cpu() for k, v in sd.items()}
-    x = x.detach().float().cpu()
-    ea = edge_features.detach().float().cpu()
-    src, dst = edge_index[0].long().cpu(), edge_index[1].long().cpu()
+    sd = {k: v.detach().to(torch.float32).to(device) for k, v in sd.items()}
+    x = x.detach().float().to(device)
+    ea = edge_features.detach().float().to(device)
+    src, dst = edge_index[0].long().to(device), edge_index[1].long().to(device)
     bf = emulate_bf16
     nl = count_layers(sd, "_encoder.node_fn.0")
     # encoder (the CUDA path runs the tiny first layers, K = 8 / 4, on the CUDA cores in fp32)
@@ -72,7 +72,7 @@ def forward(sd, x, edge_index, edge_features, emulate_bf16=False, return_interme
         e = e0 * float(2 ** m)
         h = torch.cat([_bf(xl, bf)[dst], _bf(xl, bf)[src], e], dim=-1)  # [x_i, x_j, e] = [x[dst], x[src], e]
         msg = _ln(sd, f"{p}.edge_fn.1", _mlp(sd, f"{p}.edge_fn.0", h, nl, bf))
-        agg = torch.zeros((N, L), dtype=torch.float32).index_add_(0, dst, msg)
+        agg = torch.zeros((N, L), dtype=torch.float32, device=msg.device).index_add_(0, dst, msg)
         u = _ln(sd, f"{p}.node_fn.1", _mlp(sd, f"{p}.node_fn.0", torch.cat([agg, xl], dim=-1), nl, bf))
         xl = xl + u
         if m == 0:
