@@ -185,6 +185,20 @@ int csb_gnn_forward(const csb_gnn_dims* dims, const void* packed, int N, int E, 
                     const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
                     const int32_t* perm, float* y, float* x_latent_out, void* ws, size_t ws_bytes, void* stream);
 
+/* ------------------------------------------------------------------------- *
+ * mesh-anchored Gaussians (MultiGaussianMesh.get_xyz, scene_reconstruction/gaussian_mesh.py:151-169)
+ * ------------------------------------------------------------------------- */
+/* xyz[p] = sum_k nb[p,k] * vertices[face[k, face_ids[p]]],  nb = face_bary / sum(face_bary, 1).
+ * vertices f32[Nv,3]; face i64[3,F] (torch_geometric Data.face layout); face_ids i64[P];
+ * face_bary f32[P,3]; xyz f32[P,3]. */
+int csb_mesh_xyz_forward(int P, int Nv, int F, const float* vertices, const int64_t* face, const int64_t* face_ids,
+                         const float* face_bary, float* xyz, void* stream);
+/* Backward of the above.  dL_dvertices f32[Nv,3] (zeroed inside, then accumulated) and dL_dface_bary
+ * f32[P,3] may each be NULL when that gradient is not needed. */
+int csb_mesh_xyz_backward(int P, int Nv, int F, const float* vertices, const int64_t* face, const int64_t* face_ids,
+                          const float* face_bary, const float* dL_dxyz, float* dL_dvertices, float* dL_dface_bary,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif
