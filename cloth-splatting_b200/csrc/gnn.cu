@@ -335,25 +335,71 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_mlp_kernel(const __grid_consta
                 *reinterpret_cast<uint4*>(sA + (size_t)kb * CHUNK_BYTES + swz_off(r, c)) = v;
             }
         } else if (MODE == NODE) {
-#pragma unroll 4
-            for (int it = 0; it < 16; ++it) {
+            // all 24 loads of the thread in flight before the first use (one memory latency per tile)
+            float4 fa[16];
+            uint4 xb[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
                 const int idx = it * THREADS + tid;
                 const int c = idx & 7, r = (idx >> 3) & 127, kb = idx >> 10;
                 const int n = row0 + r;
-                uint4 v = make_uint4(0, 0, 0, 0);
+                fa[2 * it] = fa[2 * it + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                xb[it] = make_uint4(0, 0, 0, 0);
                 if (n < a.rows) {
-                    if (kb < 2) {
-                        float4* p = reinterpret_cast<float4*>(a.agg + (size_t)n * LAT + kb * 64 + c * 8);
-                        const float4 f0 = p[0], f1 = p[1];
-                        v = make_uint4(pack_bf16(f0.x, f0.y), pack_bf16(f0.z, f0.w), pack_bf16(f1.x, f1.y),
-                                       pack_bf16(f1.z, f1.w));
-                        p[0] = make_float4(0.f, 0.f, 0.f, 0.f);  // ready for the next step's scatter
-                        p[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    } else {
-                        v = *reinterpret_cast<const uint4*>(a.x_bf16 + (size_t)n * LAT + (kb - 2) * 64 + c * 8);
+                    const float4* p = reinterpret_cast<const float4*>(a.agg + (size_t)n * LAT + kb * 64 + c * 8);
+                    fa[2 * it] = p[0];
+                    fa[2 * it + 1] = p[1];
+                    xb[it] = *reinterpret_cast<const uint4*>(a.x_bf16 + (size_t)n * LAT + kb * 64 + c * 8);
+                }
+            }
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int idx = it * THREADS + tid;
+                const int c = idx & 7, r = (idx >> 3) & 127, kb = idx >> 10;
+                const int n = row0 + r;
+                const float4 f0 = fa[2 * it], f1 = fa[2 * it + 1];
+                const uint4 v = make_uint4(pack_bf16(f0.x, f0.y), pack_bf16(f0.z, f0.w), pack_bf16(f1.x, f1.y),
+                                           pack_bf16(f1.z, f1.w));
+                *reinterpret_cast<uint4*>(sA + (size_t)kb * CHUNK_BYTES + swz_off(r, c)) = v;
+                *reinterpret_cast<uint4*>(sA + (size_t)(kb + 2) * CHUNK_BYTES + swz_off(r, c)) = xb[it];
+                if (n < a.rows) {  // agg is ready for the next step's scatter
+                    float4* p = reinterpret_cast<float4*>(a.agg + (size_t)n * LAT + kb * 64 + c * 8);
+                    p[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    p[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            // pull the next tile of this CTA towards L2 while this one is multiplied
+            {
+                const int nt = tile + gridDim.x;
+                if (nt < num_tiles) {
+                    const int r = tid >> 1, n = nt * TILE_M + r;
+                    if (n < a.rows) {
+                        const char* pa = reinterpret_cast<const char*>(a.agg + (size_t)n * LAT) + (tid & 1) * 256;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(pa));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(pa + 128));
+                        const char* px = reinterpret_cast<const char*>(a.x_bf16 + (size_t)n * LAT) + (tid & 1) * 128;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(px));
+                        const char* pf = reinterpret_cast<const char*>(a.x_f32 + (size_t)n * LAT) + (tid & 1) * 256;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + 128));
                     }
                 }
-                *reinterpret_cast<uint4*>(sA + (size_t)kb * CHUNK_BYTES + swz_off(r, c)) = v;
+            }
+        }
+        if (MODE == EDGE) {
+            // next tile of this CTA: its rows' x[dst], x[src] and e0 lines towards L2
+            const int nt = tile + gridDim.x;
+            if (nt < num_tiles) {
+                const int r = tid >> 1, p = nt * TILE_M + r;
+                if (p < a.rows) {
+                    const int d = a.dst_sorted[p], sr = a.src_sorted[p];
+                    if ((unsigned)d < (unsigned)a.N && (unsigned)sr < (unsigned)a.N) {
+                        const int hlf = (tid & 1) * 128;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(a.x_bf16 + (size_t)d * LAT) + hlf));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(a.x_bf16 + (size_t)sr * LAT) + hlf));
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(a.e0 + (size_t)p * LAT) + hlf));
+                    }
+                }
             }
         }
 
@@ -486,20 +532,28 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_mlp_kernel(const __grid_consta
                     }
                 }
             } else if (MODE == NODE) {
-                if (rvalid) {
-                    float4* xf = reinterpret_cast<float4*>(a.x_f32 + (size_t)grow * LAT + half * 64);
+                // stage LN(...) row-per-thread (swizzled float4 chunks, conflict free), then update the
+                // fp32 master copy and the bf16 copy with fully coalesced row accesses
+                float* stg = reinterpret_cast<float*>(sA);  // 128 x 128 fp32 = the idle A region
 #pragma unroll
-                    for (int c = 0; c < 16; ++c) {
-                        float4 o = xf[c];
-                        o.x += v[c * 4]; o.y += v[c * 4 + 1]; o.z += v[c * 4 + 2]; o.w += v[c * 4 + 3];
-                        xf[c] = o;
-                        v[c * 4] = o.x; v[c * 4 + 1] = o.y; v[c * 4 + 2] = o.z; v[c * 4 + 3] = o.w;
-                    }
-                    uint4* ob = reinterpret_cast<uint4*>(a.out_bf16 + (size_t)grow * LAT + half * 64);
-#pragma unroll
-                    for (int c = 0; c < 8; ++c)
-                        ob[c] = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
-                                           pack_bf16(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16(v[c * 8 + 6], v[c * 8 + 7]));
+                for (int c = 0; c < 16; ++c) {
+                    const int chunk = (half * 16 + c) ^ (row & 7);
+                    *reinterpret_cast<float4*>(stg + row * LAT + chunk * 4) =
+                        make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]);
+                }
+                __syncthreads();
+#pragma unroll 4
+                for (int i = 0; i < 16; ++i) {
+                    const int r = warp * 16 + i;
+                    const int n = row0 + r;
+                    if (n >= a.rows) break;  // warp-uniform
+                    const float4 u = *reinterpret_cast<const float4*>(stg + r * LAT + ((lane ^ (r & 7)) * 4));
+                    float4* xf = reinterpret_cast<float4*>(a.x_f32 + (size_t)n * LAT) + lane;
+                    float4 o = *xf;
+                    o.x += u.x; o.y += u.y; o.z += u.z; o.w += u.w;
+                    *xf = o;
+                    *(reinterpret_cast<uint2*>(a.out_bf16 + (size_t)n * LAT) + lane) =
+                        make_uint2(pack_bf16(o.x, o.y), pack_bf16(o.z, o.w));
                 }
             } else if (MODE == EDGE) {
                 // segmented sum over the warp's 32 dst-sorted rows, 32 columns per round, staged in the

@@ -146,6 +146,7 @@ class EncodeProcessDecode(nn.Module):
         self._packed_key = None
         self._graph = None
         self._graph_key = None
+        self._graph_src = None
         self._ws = None
         self.last_latent = None  # filled when forward(..., return_latent=True)
 
@@ -170,7 +171,7 @@ class EncodeProcessDecode(nn.Module):
     def _packed_weights(self, dev):
         lib = _abi.lib()
         ps = self._ordered_params()
-        key = (str(dev),) + tuple((p.data_ptr(), p._version) for p in ps)
+        key = (str(dev),) + tuple((id(p), p.data_ptr(), p._version) for p in ps)
         if self._packed is not None and key == self._packed_key:
             return self._packed
         nfl = lib.csb_gnn_param_floats(ctypes.byref(self._dims))
@@ -190,9 +191,11 @@ class EncodeProcessDecode(nn.Module):
         return packed
 
     def prepare_graph(self, edge_index, num_nodes):
-        key = (edge_index.data_ptr(), edge_index._version, tuple(edge_index.shape), int(num_nodes), str(edge_index.device))
-        if self._graph is None or key != self._graph_key:
-            self._graph, self._graph_key = PreparedGraph(edge_index, num_nodes), key
+        # cached per tensor OBJECT (kept alive here, so its storage cannot be recycled under the cache) and
+        # in-place version; a new tensor, even with equal content, is prepared again (6 small launches)
+        key = (edge_index._version, int(num_nodes))
+        if self._graph is None or self._graph_src is not edge_index or key != self._graph_key:
+            self._graph, self._graph_key, self._graph_src = PreparedGraph(edge_index, num_nodes), key, edge_index
         return self._graph
 
     def forward(self, x: torch.Tensor, edge_index: torch.Tensor, edge_features: torch.Tensor, return_latent=False):

@@ -52,10 +52,14 @@ def _check_vs_oracle(g, cam, sh_degree=3, bg=(1.0, 1.0, 1.0), int_slack=2e-3):
         assert np.array_equal(keys, s.keys)
         assert np.array_equal(pl, s.point_list)
         assert np.array_equal(rg, s.ranges)
+    # libm's expf (oracle) and CUDA's expf differ in the last ulp, which can flip an alpha >= 1/255 or a
+    # T < 1e-4 test for a handful of (pixel, Gaussian) pairs; such a pixel is off by up to ~alpha*T.  The
+    # zero-tolerance comparison is the one against the reference's own CUDA code below.
     err = np.abs(color[0].cpu().numpy() - s.color)
-    assert (err > COLOR_ATOL).mean() <= (0 if exact else 2e-3), f"colour max err {err.max()}"
+    assert (err > COLOR_ATOL).mean() <= (2e-4 if exact else 2e-3), f"colour max err {err.max()}"
+    assert err.max() < 5e-3
     derr = np.abs(depth[0].cpu().numpy() - s.depth)
-    assert (derr > COLOR_ATOL * max(1.0, float(s.depths.max()))).mean() <= (0 if exact else 2e-3)
+    assert (derr > COLOR_ATOL * max(1.0, float(s.depths.max()))).mean() <= (2e-4 if exact else 2e-3)
     dl = torch.from_numpy(S.pixel_grad(1, H, W)).cuda()
     got = Hh.product_backward(gc, cam, views, fwd, dl, sh_degree)
     want = __import__("oracle").rasterize_backward(s, dl[0].cpu().numpy())
