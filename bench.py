@@ -264,14 +264,15 @@ def run_b200(args, rank, world, dev):
     def views_of(b):
         return [(sl[v].viewmatrix, sl[v].projmatrix, sl[v].campos, sl[v].bg, sl[v].tanfovx, sl[v].tanfovy) for v in b]
 
-    grad_flat = torch.zeros(P * 59, dtype=torch.float32, device=dev)  # 3+3+4+1+48 floats per Gaussian
+    import csb_dist
+
+    # 3+3+4+1+48 floats per Gaussian, one flat buffer -> one all-reduce per step
+    bucket = csb_dist.FlatGradBucket({k: gd[k].shape for k in PARAM_NAMES}, dev)
+    grad_flat = bucket.flat
 
     def pack(grads):
-        o = 0
-        for t in grads:
-            n = t.numel()
-            grad_flat[o:o + n].copy_(t.reshape(-1)) if len(view_batches) == 1 else grad_flat[o:o + n].add_(t.reshape(-1))
-            o += n
+        d = dict(zip(("means3D", "scales", "rotations", "opacities", "shs"), grads))
+        bucket.copy_(d) if len(view_batches) == 1 else bucket.add_(d)
 
     def device_step():
         """Device-resident step through the C-ABI wrapper layer (no autograd)."""
@@ -288,8 +289,7 @@ def run_b200(args, rank, world, dev):
                                      dl[b[0]:b[-1] + 1], gd["shs"], 3, geom, binning, img)
             dm2, dcol, dop, dm3, dcov, dsh, dsc, drot = gb
             pack((dm3, dsc, drot, dop, dsh))
-        if world > 1:
-            dist.all_reduce(grad_flat)
+        bucket.all_reduce()
         return R_total
 
     def timed(step_fn, steps, warmup):

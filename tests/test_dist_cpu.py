@@ -1,0 +1,67 @@
+"""world_size-2 gloo test of the data-parallel plumbing (view sharding + one flat gradient all-reduce)."""
+import os
+import socket
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import conftest  # noqa: F401
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _fake_view_grads(view, shapes):
+    g = torch.Generator().manual_seed(100 + view)
+    return {k: torch.randn(shp, generator=g) for k, shp in shapes.items()}
+
+
+def _worker(rank, world, port, n_views, out):
+    sys.path.insert(0, conftest.PKG)
+    import csb_dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    shapes = {"means3D": (37, 3), "scales": (37, 3), "rotations": (37, 4), "opacities": (37, 1), "shs": (37, 16, 3)}
+    bucket = csb_dist.FlatGradBucket(shapes, "cpu")
+    mine = csb_dist.shard_units(n_views, rank, world)
+    for v in mine:
+        bucket.add_(_fake_view_grads(v, shapes))
+    bucket.all_reduce()
+    if rank == 0:
+        torch.save({"flat": bucket.flat.clone(), "mine": mine, "numel": bucket.numel}, out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_view_sharding_and_flat_allreduce(tmp_path):
+    sys.path.insert(0, conftest.PKG)
+    import csb_dist
+
+    n_views, world = 7, 2
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker, args=(world, _free_port(), n_views, out), nprocs=world, join=True)
+    got = torch.load(out)
+    shapes = {"means3D": (37, 3), "scales": (37, 3), "rotations": (37, 4), "opacities": (37, 1), "shs": (37, 16, 3)}
+    ref = csb_dist.FlatGradBucket(shapes, "cpu")
+    for v in range(n_views):
+        ref.add_(_fake_view_grads(v, shapes))
+    assert got["numel"] == 37 * 59 and got["mine"] == [0, 2, 4, 6]
+    assert torch.allclose(got["flat"], ref.flat, atol=1e-5)
+
+
+def test_shards_partition_units():
+    sys.path.insert(0, conftest.PKG)
+    import csb_dist
+
+    for n, w in ((64, 8), (5, 4), (3, 8), (0, 2)):
+        seen = sorted(sum((csb_dist.shard_units(n, r, w) for r in range(w)), []))
+        assert seen == list(range(n))
