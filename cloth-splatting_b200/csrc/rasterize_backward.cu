@@ -25,6 +25,7 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
     __shared__ float2 s_xy[BW_BATCH];
     __shared__ float4 s_co[BW_BATCH];
     __shared__ float4 s_cd[BW_BATCH];
+    __shared__ uint32_t s_mask[BW_BATCH];  // bit w: the Gaussian can reach the pixel patch of warp w (patch_mask)
     __shared__ uint32_t s_max_last;
 
     const int v = blockIdx.z;
@@ -36,6 +37,7 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
     const uint32_t py = blockIdx.y * CSB_TILE_Y + ly;
     const bool inside = px < (uint32_t)vb.W && py < (uint32_t)vb.H;
     const float pxf = (float)px, pyf = (float)py;
+    const float tile_x0 = (float)(blockIdx.x * CSB_TILE_X), tile_y0 = (float)(blockIdx.y * CSB_TILE_Y);
     const size_t hw = (size_t)vb.W * vb.H;
     const size_t pix = (size_t)py * vb.W + px;
 
@@ -72,7 +74,6 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
     const float ddelx_dx = 0.5 * vb.W;
     const float ddely_dy = 0.5 * vb.H;
 
-    uint32_t contributor = used;  // position (1-based) of the entry about to be visited, back to front
     const int rounds = (int)((used + BW_BATCH - 1) / BW_BATCH);
     int todo = (int)used;
     for (int r = 0; r < rounds; ++r, todo -= BW_BATCH) {
@@ -80,15 +81,25 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
         const uint32_t progress = (uint32_t)r * BW_BATCH + tid;
         if (progress < used) {
             const uint32_t id = point_list[range.x + used - progress - 1];
+            const float2 xy = means2D[id];
+            const float4 co = conic_opacity[id];
             s_id[tid] = id;
-            s_xy[tid] = means2D[id];
-            s_co[tid] = conic_opacity[id];
+            s_xy[tid] = xy;
+            s_co[tid] = co;
             s_cd[tid] = rgb_depth[id];
+            s_mask[tid] = patch_mask(xy, co, tile_x0, tile_y0);
         }
         __syncthreads();
         const int cnt = min(BW_BATCH, todo);
-        for (int j = 0; j < cnt; ++j) {
-            contributor--;
+        // entry j of this batch sits at list position used - 1 - (r * BW_BATCH + j)
+        const uint32_t top = used - 1u - (uint32_t)r * BW_BATCH;
+        for (int g = 0; g < cnt; g += 32) {
+          const uint32_t mk = (g + lane < cnt) ? s_mask[g + lane] : 0u;
+          uint32_t bits = __ballot_sync(0xFFFFFFFFu, (mk >> warp) & 1u);
+          while (bits) {
+            const int j = g + __ffs(bits) - 1;
+            bits &= bits - 1;
+            const uint32_t contributor = top - (uint32_t)j;
             if (contributor >= wmax) continue;  // warp-uniform
             bool valid = inside && contributor < last_contributor;
             const float2 xy = s_xy[j];
@@ -164,6 +175,7 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
             mine = lane == 7 ? g_c1 : mine;
             mine = lane == 8 ? g_c2 : mine;
             if (lane < 9) atomicAdd(&grad_acc[(size_t)s_id[j] * ACC_STRIDE + lane], mine);
+          }
         }
     }
 }

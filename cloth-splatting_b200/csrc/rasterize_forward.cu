@@ -355,6 +355,7 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
     __shared__ float2 s_xy[RENDER_BATCH];
     __shared__ float4 s_co[RENDER_BATCH];
     __shared__ float4 s_cd[RENDER_BATCH];
+    __shared__ uint32_t s_mask[RENDER_BATCH];  // bit w: the Gaussian can reach the 8x4 pixel patch of warp w
 
     const int v = blockIdx.z;
     const int tid = threadIdx.x;
@@ -366,6 +367,7 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
     const uint32_t py = blockIdx.y * CSB_TILE_Y + ly;
     const bool inside = px < (uint32_t)vb.W && py < (uint32_t)vb.H;
     const float pxf = (float)px, pyf = (float)py;
+    const float tile_x0 = (float)(blockIdx.x * CSB_TILE_X), tile_y0 = (float)(blockIdx.y * CSB_TILE_Y);
 
     const uint2 range = ranges[(size_t)v * vb.tiles + blockIdx.y * vb.gx + blockIdx.x];
     int todo = (int)(range.y - range.x);
@@ -373,7 +375,7 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
 
     bool done = !inside;
     float T = 1.0f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
     float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dacc = 0.f;
 
     for (int r = 0; r < rounds; ++r, todo -= RENDER_BATCH) {
@@ -381,33 +383,44 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
         const int progress = r * RENDER_BATCH + tid;
         if (range.x + progress < range.y) {
             const uint32_t id = point_list[range.x + progress];
-            s_xy[tid] = means2D[id];
-            s_co[tid] = conic_opacity[id];
+            const float2 xy = means2D[id];
+            const float4 co = conic_opacity[id];
+            s_xy[tid] = xy;
+            s_co[tid] = co;
             s_cd[tid] = rgb_depth[id];
+            s_mask[tid] = patch_mask(xy, co, tile_x0, tile_y0);
         }
         __syncthreads();
         const int cnt = min(RENDER_BATCH, todo);
-        for (int j = 0; !done && j < cnt; ++j) {
-            contributor++;
-            const float2 xy = s_xy[j];
-            const float dx = xy.x - pxf, dy = xy.y - pyf;
-            const float4 con_o = s_co[j];
-            const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
-            if (power > 0.0f) continue;
-            const float alpha = fminf(0.99f, con_o.w * expf(power));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) {
-                done = true;
-                continue;
+        const uint32_t base = (uint32_t)r * RENDER_BATCH;
+        for (int g = 0; g < cnt; g += 32) {
+            const uint32_t m = (g + lane < cnt) ? s_mask[g + lane] : 0u;
+            uint32_t bits = __ballot_sync(0xFFFFFFFFu, (m >> warp) & 1u);
+            while (bits) {
+                const int j = g + __ffs(bits) - 1;
+                bits &= bits - 1;
+                if (done) continue;
+                const float2 xy = s_xy[j];
+                const float dx = xy.x - pxf, dy = xy.y - pyf;
+                const float4 con_o = s_co[j];
+                const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
+                if (power > 0.0f) continue;
+                const float alpha = fminf(0.99f, con_o.w * expf(power));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) {
+                    done = true;
+                    continue;
+                }
+                const float4 cd = s_cd[j];
+                C0 += cd.x * alpha * T;
+                C1 += cd.y * alpha * T;
+                C2 += cd.z * alpha * T;
+                Dacc += cd.w * alpha * T;
+                T = test_T;
+                last_contributor = base + (uint32_t)j + 1u;  // 1-based list position, skipped entries count
             }
-            const float4 cd = s_cd[j];
-            C0 += cd.x * alpha * T;
-            C1 += cd.y * alpha * T;
-            C2 += cd.z * alpha * T;
-            Dacc += cd.w * alpha * T;
-            T = test_T;
-            last_contributor = contributor;
+            if (__all_sync(0xFFFFFFFFu, done)) break;
         }
     }
     if (inside) {

@@ -139,4 +139,36 @@ __device__ const float kSH_C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0
                                     0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
                                     -0.5900435899266435f};
 
+
+// Which of the eight 8x4 pixel patches of a 16x16 tile (bit w = patch of warp w: column w & 1, row w >> 1)
+// a Gaussian can reach.  A pixel is only blended when alpha = o * exp(-q/2) >= 1/255 with
+// q = a dx^2 + 2 b dx dy + c dy^2, i.e. inside the ellipse q <= t = 2 ln(255 o); the axis-aligned box of that
+// ellipse has half extents sqrt(t c / det), sqrt(t a / det).  The test is conservative (0.1 % + 0.02 px
+// of slack, far above the fp32 rounding of the per-pixel expression), so skipping the other patches does
+// not change any result of the per-pixel loops of forward.cu:309-367 / backward.cu:464-556.
+__device__ __forceinline__ uint32_t patch_mask(const float2 xy, const float4 con_o, float tile_x0, float tile_y0) {
+    const float o = con_o.w;
+    if (!(o * 255.0f >= 0.999f)) return 0u;  // alpha <= o < 1/255 everywhere
+    const float det = con_o.x * con_o.z - con_o.y * con_o.y;
+    if (!(det > 0.0f) || !(con_o.x > 0.0f) || !(con_o.z > 0.0f)) return 0xFFu;
+    const float t = 2.0f * logf(fminf(o, 1e30f) * 255.0f) * 1.001f + 1e-3f;
+    const float inv = t / det;
+    const float ex = sqrtf(inv * con_o.z) * 1.001f + 0.02f;
+    const float ey = sqrtf(inv * con_o.x) * 1.001f + 0.02f;
+    if (!(ex < 1e30f) || !(ey < 1e30f)) return 0xFFu;
+    const float x_lo = xy.x - ex - tile_x0, x_hi = xy.x + ex - tile_x0;  // reach in tile-local pixels
+    const float y_lo = xy.y - ey - tile_y0, y_hi = xy.y + ey - tile_y0;
+    uint32_t cols = 0, rows = 0;
+    if (x_lo <= 7.0f && x_hi >= 0.0f) cols |= 1u;
+    if (x_lo <= 15.0f && x_hi >= 8.0f) cols |= 2u;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        if (y_lo <= (float)(4 * j + 3) && y_hi >= (float)(4 * j)) rows |= 1u << j;
+    uint32_t m = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w)
+        if (((cols >> (w & 1)) & 1u) && ((rows >> (w >> 1)) & 1u)) m |= 1u << w;
+    return m;
+}
+
 }  // namespace csb
