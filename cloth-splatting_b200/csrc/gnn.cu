@@ -19,56 +19,11 @@
 // The reference never replaces the edge latents by the edge MLP output: e_m = 2^m e_0 (SURVEY.md fact
 // 0.3).  e_0 is therefore stored once (bf16, in dst-sorted edge order) and the factor 2^m is folded into
 // the edge block of the first edge Linear when the weights are packed (exact in bf16).
-#include <cuda_bf16.h>
-#include "common.cuh"
+
+#include "gnn_common.cuh"
 
 namespace csb {
 namespace gnn {
-
-constexpr int LAT = 128;  // latent width == hidden width (only configuration supported)
-constexpr int TILE_M = 128;
-constexpr int CHUNK_BYTES = 128 * 128;  // 128 rows x 64 bf16, one swizzle-128B K block
-constexpr int THREADS = 256;
-constexpr int TMEM_COLS = 128;
-
-enum Mode { ENC = 0, EDGE = 1, NODE = 2, DEC = 3 };
-
-// ---- unit images ------------------------------------------------------------------------------
-// bf16 chunks first, then an fp32 block.
-//   EDGE: chunks W0(6) W1(2) W2(2); f32 b0 b1 b2 ln_g ln_b
-//   NODE: chunks W0(4) W1(2) W2(2); f32 b0 b1 b2 ln_g ln_b
-//   ENC : chunks W1(2) W2(2);       f32 b0 b1 b2 ln_g ln_b W0[128 x kin]
-//   DEC : chunks W0(2) W1(2);       f32 b0 b1 W2[nout x 128] b2[nout]
-__host__ __device__ inline int unit_chunks(int mode) { return mode == EDGE ? 10 : mode == NODE ? 8 : 4; }
-__host__ __device__ inline int unit_f32(int mode, int kin, int nout) {
-    if (mode == ENC) return 5 * LAT + LAT * kin;
-    if (mode == DEC) return 2 * LAT + nout * LAT + ((nout + 3) & ~3);
-    return 5 * LAT;
-}
-__host__ __device__ inline size_t unit_bytes(int mode, int kin, int nout) {
-    const size_t b = (size_t)unit_chunks(mode) * CHUNK_BYTES + (size_t)unit_f32(mode, kin, nout) * 4;
-    return (b + 127) / 128 * 128;
-}
-// floats of one MLP (+LN) in the flat parameter buffer: W0[128,k0] b0 W1[128,128] b1 W2[n2,128] b2 (g, beta)
-__host__ __device__ inline size_t mlp_floats(int k0, int n2, bool ln) {
-    return (size_t)LAT * k0 + LAT + (size_t)LAT * LAT + LAT + (size_t)n2 * LAT + n2 + (ln ? 2 * LAT : 0);
-}
-
-struct UnitDesc {
-    unsigned long long src;  // float offset in the flat parameter buffer
-    unsigned long long dst;  // byte offset in the packed buffer
-    int mode, k0, n2;
-    float e_scale;           // EDGE: factor of the columns >= 256 of W0 (2^m)
-};
-constexpr int MAX_UNITS = 2 + 2 * 30 + 1;
-struct PackTable {
-    int n;
-    UnitDesc u[MAX_UNITS];
-};
-
-__device__ __forceinline__ uint32_t swz_off(int row, int c16) {
-    return (uint32_t)((row >> 3) * 1024 + (row & 7) * 128 + ((c16 ^ (row & 7)) << 4));
-}
 
 // W [128, K] row-major fp32 -> chunks of [128 rows x 64 k] bf16, swizzle-128B K-major
 __device__ void pack_linear(const float* __restrict__ W, int K, int col_scale_from, float scale, uint8_t* dst) {
@@ -119,82 +74,6 @@ __global__ void __launch_bounds__(256) gnn_pack_kernel(const float* __restrict__
     }
 }
 
-// ---- PTX wrappers -------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    const long long t0 = clock64();
-    while (true) {
-        uint32_t ok;
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-        if (ok) return;
-        if (clock64() - t0 > 4000000000ll) __trap();  // ~2 s: never hang the device on a protocol bug
-    }
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
-}
-// K-major, swizzle-128B shared-memory matrix descriptor (LBO = 1, SBO = 1024 B, version 1)
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
-    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) |
-           (2ull << 61);
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, bf16 x bf16 -> fp32, M = 128, N = 128, K = 16
-constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
-__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(IDESC), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// 32 lanes x 32 columns of fp32: thread l of the warp gets row (lane base + l), columns [col, col+32)
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
-    uint32_t r[32];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr) : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&t);
-}
-
 // ---- kernel arguments ---------------------------------------------------------------------------
 struct Args {
     const uint8_t* unit;  // packed unit image
@@ -211,6 +90,7 @@ struct Args {
     const float* in;                 // ENC input [rows_src, kin]
     const int* perm;                 // ENC: source row of output row i (NULL = identity)
     float* y;                        // DEC out [N, nout]
+    __nv_bfloat16* agg_save;         // NODE (training): bf16 copy of the aggregated messages it consumed [N,128]
 };
 
 template <int MODE> struct Cfg {
@@ -362,6 +242,8 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_mlp_kernel(const __grid_consta
                                            pack_bf16(f1.z, f1.w));
                 *reinterpret_cast<uint4*>(sA + (size_t)kb * CHUNK_BYTES + swz_off(r, c)) = v;
                 *reinterpret_cast<uint4*>(sA + (size_t)(kb + 2) * CHUNK_BYTES + swz_off(r, c)) = xb[it];
+                if (n < a.rows && a.agg_save)  // the exact operand, kept for the backward's recomputation
+                    *reinterpret_cast<uint4*>(a.agg_save + (size_t)n * LAT + kb * 64 + c * 8) = v;
                 if (n < a.rows) {  // agg is ready for the next step's scatter
                     float4* p = reinterpret_cast<float4*>(a.agg + (size_t)n * LAT + kb * 64 + c * 8);
                     p[0] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -612,41 +494,6 @@ __global__ void gnn_edge_finish_kernel(int E, const long long* __restrict__ edge
     perm[i] = (int)e;
 }
 
-struct Dims {
-    int node_in, edge_in, node_out, steps;
-};
-static int check_dims(const csb_gnn_dims* d) {
-    if (!d) return CSB_ERR_BAD_ARG;
-    if (d->latent_dim != LAT || d->mlp_hidden_dim != LAT || d->nmlp_layers != 2) return CSB_ERR_UNSUPPORTED;
-    if (d->nnode_in < 1 || d->nnode_in > 16 || d->nedge_in < 1 || d->nedge_in > 16) return CSB_ERR_UNSUPPORTED;
-    if (d->nnode_out < 1 || d->nnode_out > 8) return CSB_ERR_UNSUPPORTED;
-    if (d->nmessage_passing_steps < 0 || d->nmessage_passing_steps > 30) return CSB_ERR_UNSUPPORTED;
-    return 0;
-}
-
-static void build_table(const csb_gnn_dims* d, PackTable& t, size_t* total_floats, size_t* total_bytes) {
-    size_t src = 0, dst = 0;
-    int n = 0;
-    auto add = [&](int mode, int k0, int n2, bool ln, float scale) {
-        UnitDesc& u = t.u[n++];
-        u.src = src; u.dst = dst; u.mode = mode; u.k0 = k0; u.n2 = n2; u.e_scale = scale;
-        src += mlp_floats(k0, n2, ln);
-        dst += unit_bytes(mode, k0, n2);
-    };
-    add(ENC, d->nnode_in, LAT, true, 1.f);
-    add(ENC, d->nedge_in, LAT, true, 1.f);
-    float sc = 1.f;
-    for (int m = 0; m < d->nmessage_passing_steps; ++m) {
-        add(EDGE, 3 * LAT, LAT, true, sc);
-        add(NODE, 2 * LAT, LAT, true, 1.f);
-        sc *= 2.f;
-    }
-    add(DEC, LAT, d->nnode_out, false, 1.f);
-    t.n = n;
-    if (total_floats) *total_floats = src;
-    if (total_bytes) *total_bytes = dst;
-}
-
 struct Workspace {
     float* x_f32;
     __nv_bfloat16* x_bf16;
@@ -763,6 +610,57 @@ size_t csb_gnn_workspace_bytes(const csb_gnn_dims* d, int N, int E) {
     return Workspace::carve(nullptr, N, E).bytes;
 }
 
+static int forward_impl(const csb_gnn_dims* d, const void* packed, int N, int E, const float* x,
+                        const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
+                        const int32_t* perm, float* y, float* x_latent_out, float* x_f32, float* agg,
+                        __nv_bfloat16* e0, __nv_bfloat16* x_stack, size_t x_stride, __nv_bfloat16* agg_stack,
+                        cudaStream_t stream) {
+    PackTable t;
+    build_table(d, t, nullptr, nullptr);
+    const uint8_t* pk = (const uint8_t*)packed;
+    int rc;
+
+    CSB_CUDA_TRY(cudaMemsetAsync(agg, 0, (size_t)N * LAT * sizeof(float), stream));
+    Args a{};
+    a.N = N;
+    // encoders
+    a.unit = pk + t.u[0].dst; a.rows = N; a.kin = d->nnode_in; a.nout = LAT;
+    a.in = x; a.perm = nullptr; a.out_bf16 = x_stack; a.x_f32 = x_f32;
+    rc = launch_role<ENC>(a, a.kin, LAT, stream, "gnn_encode");
+    if (rc) return rc;
+    if (E > 0) {
+        a.unit = pk + t.u[1].dst; a.rows = E; a.kin = d->nedge_in;
+        a.in = edge_features; a.perm = perm; a.out_bf16 = e0; a.x_f32 = nullptr;
+        rc = launch_role<ENC>(a, a.kin, LAT, stream, "gnn_encode");
+        if (rc) return rc;
+    }
+    // processor
+    __nv_bfloat16* xcur = x_stack;
+    for (int m = 0; m < d->nmessage_passing_steps; ++m) {
+        Args e{};
+        e.N = N; e.kin = 0; e.nout = LAT;
+        e.unit = pk + t.u[2 + 2 * m].dst; e.rows = E;
+        e.dst_sorted = dst_sorted; e.src_sorted = src_sorted; e.x_bf16 = xcur; e.e0 = e0; e.agg = agg;
+        rc = launch_role<EDGE>(e, 0, LAT, stream, "gnn_edge");
+        if (rc) return rc;
+        Args n{};
+        n.N = N; n.kin = 0; n.nout = LAT;
+        n.unit = pk + t.u[3 + 2 * m].dst; n.rows = N;
+        n.agg = agg; n.x_bf16 = xcur; n.x_f32 = x_f32; n.out_bf16 = xcur + x_stride;
+        n.agg_save = agg_stack ? agg_stack + (size_t)m * N * LAT : nullptr;
+        rc = launch_role<NODE>(n, 0, LAT, stream, "gnn_node");
+        if (rc) return rc;
+        xcur += x_stride;
+    }
+    if (x_latent_out)
+        CSB_CUDA_TRY(cudaMemcpyAsync(x_latent_out, x_f32, (size_t)N * LAT * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+    // decoder
+    Args c{};
+    c.N = N; c.kin = 0; c.nout = d->nnode_out;
+    c.unit = pk + t.u[t.n - 1].dst; c.rows = N; c.x_bf16 = xcur; c.y = y;
+    return launch_role<DEC>(c, 0, d->nnode_out, stream, "gnn_decode");
+}
+
 int csb_gnn_forward(const csb_gnn_dims* d, const void* packed, int N, int E, const float* x,
                     const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
                     const int32_t* perm, float* y, float* x_latent_out, void* ws, size_t ws_bytes, void* stream_) {
@@ -774,47 +672,28 @@ int csb_gnn_forward(const csb_gnn_dims* d, const void* packed, int N, int E, con
     if (E > 0 && (!edge_features || !dst_sorted || !src_sorted || !perm)) return CSB_ERR_BAD_ARG;
     Workspace w = Workspace::carve(ws, N, E);
     if (ws_bytes < w.bytes) return CSB_ERR_WORKSPACE;
-    cudaStream_t stream = (cudaStream_t)stream_;
-    PackTable t;
-    build_table(d, t, nullptr, nullptr);
-    const uint8_t* pk = (const uint8_t*)packed;
+    return forward_impl(d, packed, N, E, x, edge_features, dst_sorted, src_sorted, perm, y, x_latent_out, w.x_f32,
+                        w.agg, w.e0, w.x_bf16, 0, nullptr, (cudaStream_t)stream_);
+}
 
-    CSB_CUDA_TRY(cudaMemsetAsync(w.agg, 0, (size_t)N * LAT * sizeof(float), stream));
-    Args a{};
-    a.N = N;
-    // encoders
-    a.unit = pk + t.u[0].dst; a.rows = N; a.kin = d->nnode_in; a.nout = LAT;
-    a.in = x; a.perm = nullptr; a.out_bf16 = w.x_bf16; a.x_f32 = w.x_f32;
-    rc = launch_role<ENC>(a, a.kin, LAT, stream, "gnn_encode");
+size_t csb_gnn_train_state_bytes(const csb_gnn_dims* d, int N, int E) {
+    if (check_dims(d) || N < 0 || E < 0) return 0;
+    return TrainState::carve(nullptr, N, E, d->nmessage_passing_steps).bytes;
+}
+
+int csb_gnn_forward_train(const csb_gnn_dims* d, const void* packed, int N, int E, const float* x,
+                          const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
+                          const int32_t* perm, float* y, void* state, size_t state_bytes, void* stream_) {
+    int rc = check_dims(d);
     if (rc) return rc;
-    if (E > 0) {
-        a.unit = pk + t.u[1].dst; a.rows = E; a.kin = d->nedge_in;
-        a.in = edge_features; a.perm = perm; a.out_bf16 = w.e0; a.x_f32 = nullptr;
-        rc = launch_role<ENC>(a, a.kin, LAT, stream, "gnn_encode");
-        if (rc) return rc;
-    }
-    // processor
-    for (int m = 0; m < d->nmessage_passing_steps; ++m) {
-        Args e{};
-        e.N = N; e.kin = 0; e.nout = LAT;
-        e.unit = pk + t.u[2 + 2 * m].dst; e.rows = E;
-        e.dst_sorted = dst_sorted; e.src_sorted = src_sorted; e.x_bf16 = w.x_bf16; e.e0 = w.e0; e.agg = w.agg;
-        rc = launch_role<EDGE>(e, 0, LAT, stream, "gnn_edge");
-        if (rc) return rc;
-        Args n{};
-        n.N = N; n.kin = 0; n.nout = LAT;
-        n.unit = pk + t.u[3 + 2 * m].dst; n.rows = N;
-        n.agg = w.agg; n.x_bf16 = w.x_bf16; n.x_f32 = w.x_f32; n.out_bf16 = w.x_bf16;
-        rc = launch_role<NODE>(n, 0, LAT, stream, "gnn_node");
-        if (rc) return rc;
-    }
-    if (x_latent_out)
-        CSB_CUDA_TRY(cudaMemcpyAsync(x_latent_out, w.x_f32, (size_t)N * LAT * sizeof(float), cudaMemcpyDeviceToDevice, stream));
-    // decoder
-    Args c{};
-    c.N = N; c.kin = 0; c.nout = d->nnode_out;
-    c.unit = pk + t.u[t.n - 1].dst; c.rows = N; c.x_bf16 = w.x_bf16; c.y = y;
-    return launch_role<DEC>(c, 0, d->nnode_out, stream, "gnn_decode");
+    if (N < 0 || E < 0) return CSB_ERR_BAD_ARG;
+    if (N == 0) return 0;
+    if (!packed || !x || !y || !state) return CSB_ERR_BAD_ARG;
+    if (E > 0 && (!edge_features || !dst_sorted || !src_sorted || !perm)) return CSB_ERR_BAD_ARG;
+    TrainState w = TrainState::carve(state, N, E, d->nmessage_passing_steps);
+    if (state_bytes < w.bytes) return CSB_ERR_WORKSPACE;
+    return forward_impl(d, packed, N, E, x, edge_features, dst_sorted, src_sorted, perm, y, nullptr, w.x_f32, w.agg,
+                        w.e0, w.x_stack, (size_t)N * LAT, w.agg_stack, (cudaStream_t)stream_);
 }
 
 }  // extern "C"

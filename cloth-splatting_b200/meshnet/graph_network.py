@@ -102,6 +102,17 @@ def _bind(lib):
     lib.csb_gnn_forward.restype = c_int
     lib.csb_gnn_forward.argtypes = [P(GnnDims), c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+    lib.csb_gnn_train_state_bytes.restype = c_size_t
+    lib.csb_gnn_train_state_bytes.argtypes = [P(GnnDims), c_int, c_int]
+    lib.csb_gnn_forward_train.restype = c_int
+    lib.csb_gnn_forward_train.argtypes = [P(GnnDims), c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                          c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+    lib.csb_gnn_backward_workspace_bytes.restype = c_size_t
+    lib.csb_gnn_backward_workspace_bytes.argtypes = [P(GnnDims), c_int, c_int]
+    lib.csb_gnn_backward.restype = c_int
+    lib.csb_gnn_backward.argtypes = [P(GnnDims), c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_size_t, c_void_p]
     lib._gnn_bound = True
 
 
@@ -131,6 +142,73 @@ class PreparedGraph:
             _abi.check(rc, "csb_gnn_prepare_graph")
 
 
+class _GnnFunction(torch.autograd.Function):
+    """EncodeProcessDecode.forward with gradients: csb_gnn_forward_train / csb_gnn_backward.
+
+    Replaces torch autograd over graph_network.py:98-111,178-222,323-332 (what `loss.backward()` walks in
+    train_meshnet_sim.py:529).  Inputs after the fixed ones are the module's parameters in flat-buffer order;
+    the backward returns one gradient view per parameter out of ONE flat buffer (so a data-parallel run can
+    all-reduce it in one call)."""
+
+    @staticmethod
+    def forward(ctx, module, graph, x, edge_features, *params):
+        lib = _abi.lib()
+        dims = module._dims
+        dev = x.device
+        N, E = x.size(0), graph.E
+        xin = x.detach().to(torch.float32).contiguous()
+        ef = edge_features.detach().to(torch.float32).contiguous()
+        packed = module._packed_weights(dev)
+        y = torch.empty((N, dims.nnode_out), dtype=torch.float32, device=dev)
+        state = torch.empty(lib.csb_gnn_train_state_bytes(ctypes.byref(dims), N, E), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.csb_gnn_forward_train(ctypes.byref(dims), packed.data_ptr(), N, E, xin.data_ptr(),
+                                           ef.data_ptr() if E else None, graph.dst.data_ptr() if E else None,
+                                           graph.src.data_ptr() if E else None, graph.perm.data_ptr() if E else None,
+                                           y.data_ptr(), state.data_ptr(), state.numel(), _abi.current_stream_ptr())
+        _abi.check(rc, "csb_gnn_forward_train")
+        ctx.module, ctx.graph, ctx.packed = module, graph, packed
+        ctx.save_for_backward(xin, ef, state)
+        ctx.shapes = [p.shape for p in params]
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _abi.lib()
+        module, graph = ctx.module, ctx.graph
+        dims = module._dims
+        xin, ef, state = ctx.saved_tensors
+        dev = xin.device
+        N, E = xin.size(0), graph.E
+        dy = dy.to(torch.float32).contiguous()
+        nfl = lib.csb_gnn_param_floats(ctypes.byref(dims))
+        flat = torch.zeros(nfl, dtype=torch.float32, device=dev)
+        dx = torch.empty_like(xin) if ctx.needs_input_grad[2] else None
+        # rows of edges with out-of-range endpoints are never visited: zeros, as autograd would give
+        de = torch.zeros_like(ef) if ctx.needs_input_grad[3] else None
+        need = lib.csb_gnn_backward_workspace_bytes(ctypes.byref(dims), N, E)
+        if module._bws is None or module._bws.numel() < need or module._bws.device != dev:
+            module._bws = torch.empty(need, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.csb_gnn_backward(ctypes.byref(dims), ctx.packed.data_ptr(), N, E, xin.data_ptr(),
+                                      ef.data_ptr() if E else None, graph.dst.data_ptr() if E else None,
+                                      graph.src.data_ptr() if E else None, graph.perm.data_ptr() if E else None,
+                                      state.data_ptr(), state.numel(), dy.data_ptr(), flat.data_ptr(),
+                                      dx.data_ptr() if dx is not None else None,
+                                      de.data_ptr() if (de is not None and E) else None, module._bws.data_ptr(),
+                                      module._bws.numel(), _abi.current_stream_ptr())
+        _abi.check(rc, "csb_gnn_backward")
+        module.last_flat_grad = flat
+        grads, o = [], 0
+        for shp in ctx.shapes:
+            n = 1
+            for d in shp:
+                n *= d
+            grads.append(flat[o:o + n].view(shp))
+            o += n
+        return (None, None, dx, de, *grads)
+
+
 class EncodeProcessDecode(nn.Module):
     def __init__(self, nnode_in_features: int, nnode_out_features: int, nedge_in_features: int, latent_dim: int,
                  nmessage_passing_steps: int, nmlp_layers: int, mlp_hidden_dim: int):
@@ -148,6 +226,8 @@ class EncodeProcessDecode(nn.Module):
         self._graph_key = None
         self._graph_src = None
         self._ws = None
+        self._bws = None
+        self.last_flat_grad = None  # flat fp32 gradient buffer of the latest backward (csb_gnn_pack order)
         self.last_latent = None  # filled when forward(..., return_latent=True)
 
     # ---- parameters -> packed image -------------------------------------------------------------
@@ -203,14 +283,18 @@ class EncodeProcessDecode(nn.Module):
         _bind(lib)
         if not x.is_cuda:
             raise ValueError("EncodeProcessDecode (B200) needs CUDA tensors; there is no CPU path")
-        if torch.is_grad_enabled() and (x.requires_grad or edge_features.requires_grad or
-                                        any(p.requires_grad for p in self.parameters())):
-            raise NotImplementedError("EncodeProcessDecode (B200): the backward pass is not built yet; call under "
-                                      "torch.no_grad() (the reference's rollout does, train_meshnet_sim.py:92-160)")
         dev = x.device
         N, E = x.size(0), edge_index.size(1)
         if x.size(1) != self._dims.nnode_in or edge_features.size(1) != self._dims.nedge_in:
             raise ValueError("feature widths do not match the constructor arguments")
+        if torch.is_grad_enabled() and (x.requires_grad or edge_features.requires_grad or
+                                        any(p.requires_grad for p in self.parameters())):
+            if return_latent:
+                raise ValueError("return_latent is an inference-only debugging aid")
+            if self._packed_weights(dev) is None:  # raises for unsupported widths
+                raise RuntimeError("unreachable")
+            g = self.prepare_graph(edge_index, N)
+            return _GnnFunction.apply(self, g, x, edge_features, *self._ordered_params())
         xin = x.detach().to(torch.float32).contiguous()
         ef = edge_features.detach().to(torch.float32).contiguous()
         packed = self._packed_weights(dev)

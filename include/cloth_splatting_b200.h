@@ -185,6 +185,27 @@ int csb_gnn_forward(const csb_gnn_dims* dims, const void* packed, int N, int E, 
                     const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
                     const int32_t* perm, float* y, float* x_latent_out, void* ws, size_t ws_bytes, void* stream);
 
+/* Training (the reference back-propagates `loss.backward()` through EncodeProcessDecode in its multi-step
+ * loop, train_meshnet_sim.py:491-532; torch autograd over graph_network.py:98-111,178-222,323-332).
+ * csb_gnn_forward_train = csb_gnn_forward that keeps, in the caller-owned `state`, the bf16 operands every
+ * message-passing step consumed (node latents x_m, aggregated messages agg_m, encoded edge latents e_0).
+ * csb_gnn_backward recomputes the MLP activations from them and ACCUMULATES (+=)
+ *   grad_flat          f32[csb_gnn_param_floats]  same layout as flat_params (caller zeroes it),
+ * and writes (each may be NULL)
+ *   dL_dx              f32[N, nnode_in],
+ *   dL_dedge_features  f32[E, nedge_in]  in the ORIGINAL edge order,
+ * given dL_dy f32[N, nnode_out].  x / edge_features / graph arrays / packed must be the forward's. */
+size_t csb_gnn_train_state_bytes(const csb_gnn_dims* dims, int N, int E);
+int csb_gnn_forward_train(const csb_gnn_dims* dims, const void* packed, int N, int E, const float* x,
+                          const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
+                          const int32_t* perm, float* y, void* state, size_t state_bytes, void* stream);
+size_t csb_gnn_backward_workspace_bytes(const csb_gnn_dims* dims, int N, int E);
+int csb_gnn_backward(const csb_gnn_dims* dims, const void* packed, int N, int E, const float* x,
+                     const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
+                     const int32_t* perm, const void* state, size_t state_bytes, const float* dL_dy,
+                     float* grad_flat, float* dL_dx, float* dL_dedge_features, void* ws, size_t ws_bytes,
+                     void* stream);
+
 /* ------------------------------------------------------------------------- *
  * mesh-anchored Gaussians (MultiGaussianMesh.get_xyz, scene_reconstruction/gaussian_mesh.py:151-169)
  * ------------------------------------------------------------------------- */

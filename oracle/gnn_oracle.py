@@ -24,6 +24,19 @@ def _bf(t, on):
     return t.to(torch.bfloat16).to(torch.float32) if on else t
 
 
+class _RoundGradBf16(torch.autograd.Function):
+    """Identity whose backward rounds the gradient to bf16: the CUDA backward feeds dZ_l to its dgrad / wgrad
+    tensor-core contractions as bf16 (fp32 accumulation), the bias gradient still sums the fp32 values."""
+
+    @staticmethod
+    def forward(ctx, t):
+        return t.view_as(t)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).to(torch.float32)
+
+
 def _mlp(sd, prefix, h, nlayers, bf16, first_on_cuda_cores=False, last_on_cuda_cores=False, w0_scale=None):
     """prefix.NN-k.{weight,bias}: Linear + ReLU, last layer Identity (build_mlp, graph_network.py:7-45)."""
     for k in range(nlayers):
@@ -33,7 +46,10 @@ def _mlp(sd, prefix, h, nlayers, bf16, first_on_cuda_cores=False, last_on_cuda_c
         fp32_layer = (k == 0 and first_on_cuda_cores) or (k == nlayers - 1 and last_on_cuda_cores)
         on = bf16 and not fp32_layer
         hin = _bf(h, on)
-        h = F.linear(hin, _bf(W, on)) + b
+        h = F.linear(hin, _bf(W, on))
+        if on and h.requires_grad:
+            h = _RoundGradBf16.apply(h)
+        h = h + b
         if k < nlayers - 1:
             h = F.relu(h)
     return h
@@ -50,11 +66,19 @@ def count_layers(sd, prefix):
     return n
 
 
-def forward(sd, x, edge_index, edge_features, emulate_bf16=False, return_intermediates=False, device="cpu"):
-    """EncodeProcessDecode.forward (graph_network.py:387-408) -> f32[N, nnode_out]."""
-    sd = {k: v.detach().to(torch.float32).to(device) for k, v in sd.items()}
-    x = x.detach().float().to(device)
-    ea = edge_features.detach().float().to(device)
+def forward(sd, x, edge_index, edge_features, emulate_bf16=False, return_intermediates=False, device="cpu",
+            differentiable=False):
+    """EncodeProcessDecode.forward (graph_network.py:387-408) -> f32[N, nnode_out].
+
+    differentiable=True keeps the autograd graph (sd / x / edge_features are used as they are, already on
+    `device`): torch autograd over this function is the oracle of csb_gnn_backward, exactly what the
+    reference's loss.backward() differentiates (train_meshnet_sim.py:529)."""
+    if differentiable:
+        ea = edge_features
+    else:
+        sd = {k: v.detach().to(torch.float32).to(device) for k, v in sd.items()}
+        x = x.detach().float().to(device)
+        ea = edge_features.detach().float().to(device)
     src, dst = edge_index[0].long().to(device), edge_index[1].long().to(device)
     bf = emulate_bf16
     nl = count_layers(sd, "_encoder.node_fn.0")

@@ -124,8 +124,4 @@ def test_ragged_sizes_and_no_edges():
     assert float((y - yb).abs().max()) < TIGHT * _scale(yb)
 
 
-def test_grad_request_fails_loudly():
-    m = _model(0, 1)
-    x, ei, ef, _, _ = S.gnn_inputs(4, 0)
-    with pytest.raises(NotImplementedError):
-        m(torch.from_numpy(x).cuda(), torch.from_numpy(ei).cuda(), torch.from_numpy(ef).cuda())
+
