@@ -241,6 +241,78 @@ def gnn_bench(dev, impl, peaks, flush, with_cpu=True, iters=30):
                                          "meshnet/graph_network.py (oracle/gnn_oracle.py) on the host cores"}
     return out
 
+def c5_batch(graphs, n=40, F=10, L=2, seed=4):
+    """`graphs` copies of the n x n cloth (BASELINE.json configs[4]: 1600-node graphs, 10-step rollout loss)."""
+    _, ei, ef, verts, _ = S.gnn_inputs(n, seed)
+    N = verts.shape[0]
+    rng = np.random.default_rng(seed)
+    NN = N * graphs
+    d = dict(
+        velocity=(rng.standard_normal((NN, 3 * L)) * 0.01).astype(np.float32),
+        node_types=np.tile(np.eye(1, N, 0, dtype=np.float32).T, (graphs, 1)),
+        edge_index=np.ascontiguousarray(np.concatenate([ei + g * N for g in range(graphs)], 1)),
+        edge_features=np.tile(ef, (graphs, 1)),
+        target=(rng.standard_normal((NN, F, 3)) * 0.01).astype(np.float32),
+        actions=np.zeros((NN, F + 1, 3), np.float32),
+        positions=np.tile(verts.astype(np.float32), (graphs, 1)),
+        noise=(rng.standard_normal((NN, 3 * L)) * 0.003).astype(np.float32))
+    d["actions"][::N] = (rng.standard_normal((graphs, F + 1, 3)) * 0.02).astype(np.float32)
+    return d
+
+
+def gnn_train_bench(dev, impl, peaks, graphs, F=10, iters=5, world=1):
+    """One optimisation step of the cloth simulator on this rank's share of C5 (1024 graphs of 1600 nodes over
+    8 GPUs = 128 per GPU): zero_grad, 10-step rollout loss (train_meshnet_sim.py:491-527), backward, ONE flat
+    all-reduce of the 2.33 M parameter gradients, fused Adam step."""
+    import csb_dist
+    from meshnet import ClothMeshSimulator
+    from meshnet.rollout import multi_step_loss
+
+    torch.manual_seed(0)
+    sim = ClothMeshSimulator(3, 8, 4, 128, 15, 2, 128, 2, 2, normalize=True, device=dev).to(dev)
+    if impl == "reference":
+        from oracle import gnn_oracle
+
+        class OracleGnn(torch.nn.Module):  # the reference's fp32 op sequence under torch autograd
+            def __init__(self, inner):
+                super().__init__()
+                self.inner = inner
+
+            def forward(self, x, ei, ea):
+                sd = dict(self.inner.named_parameters())
+                return gnn_oracle.forward(sd, x, ei, ea, device=x.device, differentiable=True)
+
+        sim._encode_process_decode = OracleGnn(sim._encode_process_decode)
+    sim.train()
+    d = c5_batch(graphs, F=F)
+    t = {k: torch.from_numpy(v).to(dev) for k, v in d.items()}
+    N, E = t["velocity"].shape[0], t["edge_index"].shape[1]
+    flat = csb_dist.attach_flat_grads(sim.parameters())
+    opt = torch.optim.Adam(sim.parameters(), lr=1e-4, fused=True)
+    last = {}
+
+    def step():
+        flat.zero_()
+        loss = multi_step_loss(sim, t["velocity"], t["node_types"], t["edge_index"], t["edge_features"], t["target"],
+                               t["actions"], t["positions"], F, velocity_noise=t["noise"])
+        loss.backward()
+        csb_dist.all_reduce_flat(flat, average=True)
+        opt.step()
+        last["loss"] = loss.detach()
+
+    ms, _ = _time_cuda(step, iters, 3, None)
+    fl = 3.0 * F * gnn_flops(N, E)
+    peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1590.0)))
+    return {"graphs": graphs, "nodes": N, "edges": E, "rollout_steps": F, "ms_per_step": ms,
+            "graphs_per_s": world * graphs / (ms * 1e-3), "loss": float(last["loss"]),
+            "tflops": fl / (ms * 1e-3) / 1e12,
+            "roofline": {"bound": "tensor", "achieved": fl / (ms * 1e-3) / 1e12, "peak": peak, "unit": "TFLOP/s",
+                         "frac": fl / (ms * 1e-3) / 1e12 / peak, "flops": "3 x forward (SURVEY.md 8d), recompute not counted",
+                         "peak_source": "measured sustained" if peaks else "fallback"},
+            "inputs": "resident (the batch is larger than L2: %.0f MB of saved state per prediction)" % (
+                (31.0 * N + E) * 256 / 1e6)}
+
+
 # ------------------------------------------------------------------------------------------
 # product arm
 # ------------------------------------------------------------------------------------------
@@ -408,13 +480,25 @@ def run_b200(args, rank, world, dev):
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "impl": "b200",
     }
-    if rank == 0:
-        if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(g_np, cams, dl_np)
-        if not args.no_gnn:
-            l0 = lib.csb_launch_count()
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(g_np, cams, dl_np)
+    if not args.no_gnn:
+        l0 = lib.csb_launch_count()
+        if rank == 0:
             line["gnn"] = gnn_bench(dev, "b200", peaks, flush, with_cpu=(world == 1 and not args.no_cpu_baseline))
+        if world > 1:
+            dist.barrier()
+        # every rank trains on its own 128 graphs of C5 (1024 graphs over 8 GPUs), gradients all-reduced
+        tr = gnn_train_bench(dev, "b200", peaks, args.gnn_graphs, world=world)
+        if world > 1:
+            tms = torch.tensor([tr["ms_per_step"]], dtype=torch.float64, device=dev)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            tr["graphs_per_s"] *= tr["ms_per_step"] / float(tms.item())
+            tr["ms_per_step"] = float(tms.item())
+        if rank == 0:
+            line["gnn"]["train_c5"] = tr
             line["gnn"]["gpu_launches"] = int(lib.csb_launch_count() - l0)
+    if rank == 0:
         print(json.dumps(line), flush=True)
 
 
@@ -549,6 +633,10 @@ def run_reference(args, rank, world, dev):
         # the reference's GNN = stock PyTorch fp32 ops (index_select, cat, addmm, layer_norm, index_add_); its
         # op sequence, restated in oracle/gnn_oracle.py (torch_geometric is not installed), timed on this B200
         base["gnn"] = gnn_bench(dev, "reference", peaks, flush, with_cpu=True)
+        # bounded sample: torch autograd keeps every [E, 384] / [E, 128] activation of the 150 message-passing
+        # steps of a 10-step rollout (~8 GB per graph-batch of 1), 128 graphs do not fit in 180 GB
+        base["gnn"]["train_c5"] = gnn_train_bench(dev, "reference", peaks, args.gnn_ref_graphs, iters=3)
+        base["gnn"]["train_c5"]["sample"] = f"{args.gnn_ref_graphs} of the 128 graphs a GPU owns in C5"
     print(json.dumps(base), flush=True)
 
 
@@ -561,6 +649,8 @@ def main():
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gnn", action="store_true")
+    ap.add_argument("--gnn-graphs", type=int, default=128, help="graphs per GPU of the C5 training leg")
+    ap.add_argument("--gnn-ref-graphs", type=int, default=4, help="graphs of the reference arm's bounded sample")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 

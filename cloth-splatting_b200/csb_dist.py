@@ -58,3 +58,25 @@ class FlatGradBucket:
 
     def as_dict(self):
         return {k: self.view(k) for k in self.names}
+
+
+def attach_flat_grads(params) -> torch.Tensor:
+    """Makes every parameter's .grad a view into ONE flat fp32 buffer (returned), so that the gradients autograd
+    accumulates over a multi-step rollout are summed over the ranks with a single all-reduce
+    (`all_reduce_flat`).  Use `flat.zero_()` (or optimizer.zero_grad(set_to_none=False)) between steps."""
+    params = [p for p in params if p.requires_grad]
+    n = sum(p.numel() for p in params)
+    flat = torch.zeros(n, dtype=torch.float32, device=params[0].device)
+    o = 0
+    for p in params:
+        p.grad = flat[o:o + p.numel()].view_as(p)
+        o += p.numel()
+    return flat
+
+
+def all_reduce_flat(flat: torch.Tensor, average: bool = False) -> torch.Tensor:
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+        if average:
+            flat.div_(dist.get_world_size())
+    return flat
