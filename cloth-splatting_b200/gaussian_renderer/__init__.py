@@ -1,0 +1,90 @@
+"""`gaussian_renderer.render`: the refinement step's forward glue (gaussian_renderer/__init__.py:22-206 of
+KTH-RPL/cloth-splatting) over the sm_100a kernels:
+
+    vertices  = simulator(time)                       ResidualMeshSimulator (mesh prediction + residual MLP)
+    means3D   = pc.get_xyz(vertices)                  csb_mesh_xyz_*
+    rotations = pc.get_rotation(vertices)             csb_mesh_rotation_*   (closed-form Kabsch, no SVD)
+    image, radii, depth = GaussianRasterizer(...)     csb_rasterize_*
+
+Same signature and the same 14-field RenderResults.  The `shadow_scalars` branch of the reference is dead code
+(always None, :92); `pipe.compute_cov3D_python` needs GaussianModel.get_covariance and is not part of the loop
+(arguments/__init__.py default False): it raises here instead of silently taking another path."""
+import math
+from typing import NamedTuple, Optional
+
+import numpy as np
+import torch
+
+from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+
+
+class RenderResults(NamedTuple):
+    render: torch.Tensor
+    viewspace_points: torch.Tensor
+    visibility_filter: torch.Tensor
+    radii: torch.Tensor
+    depth: torch.Tensor
+    means3D_deform: torch.Tensor
+    vertice_deform: torch.Tensor
+    shadows_mean: Optional[torch.Tensor]
+    shadows_std: Optional[torch.Tensor]
+    projections: torch.Tensor
+    rotations: torch.Tensor
+    opacities: torch.Tensor
+    shadows: Optional[torch.Tensor]
+    vertice_projections: Optional[torch.Tensor]
+
+
+def project_to_pixels(cam, points):
+    """Pixel coordinates of 3D points under cam.full_proj_transform (gaussian_renderer/__init__.py:166-180)."""
+    ph = torch.cat([points, torch.ones_like(points[:, 0:1])], dim=1).T
+    proj = cam.full_proj_transform.to(ph.device).T.matmul(ph)
+    proj = (proj / proj[3, :])[:2].T
+    H, W = int(cam.image_height), int(cam.image_width)
+    return torch.stack([((proj[:, 0] + 1.0) * W - 1.0) * 0.5, ((proj[:, 1] + 1.0) * H - 1.0) * 0.5], dim=1)
+
+
+def render(viewpoint_camera, pc, simulator, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None,
+           log_deform_path=None, no_shadow=False, render_static=False, project_vertices=False) -> RenderResults:
+    """Render one view of the mesh-anchored Gaussians at viewpoint_camera.time.  bg_color must be on the GPU."""
+    if getattr(pipe, "compute_cov3D_python", False):
+        raise NotImplementedError("compute_cov3D_python is outside the accelerated path (SURVEY.md section 8)")
+    dev = pc.mesh.pos.device
+    base_xyz = pc.get_xyz()
+    screenspace_points = torch.zeros_like(base_xyz, requires_grad=True) + 0
+    try:
+        screenspace_points.retain_grad()
+    except Exception:
+        pass
+    settings = GaussianRasterizationSettings(
+        image_height=int(viewpoint_camera.image_height), image_width=int(viewpoint_camera.image_width),
+        tanfovx=math.tan(viewpoint_camera.FoVx * 0.5), tanfovy=math.tan(viewpoint_camera.FoVy * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=viewpoint_camera.world_view_transform.to(dev),
+        projmatrix=viewpoint_camera.full_proj_transform.to(dev), sh_degree=pc.active_sh_degree,
+        campos=viewpoint_camera.camera_center.to(dev), prefiltered=False, debug=False)
+    rasterizer = GaussianRasterizer(raster_settings=settings)
+
+    if render_static:
+        vertice_deform = pc.mesh.pos
+        means3D_deform = base_xyz
+        rotations_deform = pc.get_rotation()
+    else:
+        time = torch.tensor(viewpoint_camera.time).to(dev).repeat(pc.mesh.pos.shape[0], 1)
+        vertice_deform = simulator(time_vector=time)
+        means3D_deform = pc.get_xyz(vertice_deform)
+        rotations_deform = pc.get_rotation(vertice_deform)
+    opacity = pc.get_opacity
+    if log_deform_path is not None:
+        np.savez(log_deform_path, means3D=base_xyz.detach().cpu().numpy(),
+                 means3D_deform=means3D_deform.detach().cpu().numpy(),
+                 vertice_deform=vertice_deform.detach().cpu().numpy(), rotations=rotations_deform.detach().cpu().numpy())
+    shs, colors_precomp = (pc.get_features, None) if override_color is None else (None, override_color)
+    rendered_image, radii, depth = rasterizer(means3D=means3D_deform, means2D=screenspace_points, shs=shs,
+                                              colors_precomp=colors_precomp, opacities=opacity,
+                                              scales=pc.get_scaling, rotations=rotations_deform, cov3D_precomp=None)
+    return RenderResults(
+        render=rendered_image, viewspace_points=screenspace_points, visibility_filter=radii > 0, radii=radii,
+        depth=depth, means3D_deform=means3D_deform, vertice_deform=vertice_deform, shadows_mean=None, shadows_std=None,
+        projections=project_to_pixels(viewpoint_camera, means3D_deform), rotations=rotations_deform,
+        opacities=opacity, shadows=None,
+        vertice_projections=project_to_pixels(viewpoint_camera, vertice_deform) if project_vertices else None)

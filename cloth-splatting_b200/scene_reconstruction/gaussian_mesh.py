@@ -22,6 +22,10 @@ def _bind(lib):
     lib.csb_mesh_xyz_forward.argtypes = [c_int, c_int, c_int] + [c_void_p] * 6
     lib.csb_mesh_xyz_backward.restype = c_int
     lib.csb_mesh_xyz_backward.argtypes = [c_int, c_int, c_int] + [c_void_p] * 8
+    lib.csb_mesh_rotation_forward.restype = c_int
+    lib.csb_mesh_rotation_forward.argtypes = [c_int, c_int, c_int] + [c_void_p] * 7
+    lib.csb_mesh_rotation_backward.restype = c_int
+    lib.csb_mesh_rotation_backward.argtypes = [c_int, c_int, c_int] + [c_void_p] * 9
     lib._mesh_bound = True
 
 
@@ -61,6 +65,51 @@ class _MeshXYZ(torch.autograd.Function):
         return dv, None, None, db
 
 
+class _MeshRotation(torch.autograd.Function):
+    """get_rotation(deformed_vertices) (gaussian_mesh.py:171-188): closed-form Kabsch of the face triangle,
+    rotmat -> XYZW quaternion, composed with the normalised parameter; csb_mesh_rotation_*."""
+
+    @staticmethod
+    def forward(ctx, rest_vertices, vertices, face, face_ids, rotation):
+        lib = _abi.lib()
+        _bind(lib)
+        if not vertices.is_cuda:
+            raise ValueError("get_rotation (B200) needs CUDA tensors; there is no CPU path")
+        v0 = rest_vertices.detach().float().contiguous()
+        v = vertices.detach().float().contiguous()
+        q = rotation.detach().float().contiguous()
+        f = face.to(torch.int64).contiguous()
+        ids = face_ids.to(torch.int64).contiguous()
+        P, Nv, F = ids.numel(), v.size(0), f.size(1)
+        out = torch.empty((P, 4), dtype=torch.float32, device=v.device)
+        with torch.cuda.device(v.device):
+            rc = lib.csb_mesh_rotation_forward(P, Nv, F, _abi.ptr(v0), _abi.ptr(v), _abi.ptr(f), _abi.ptr(ids),
+                                               _abi.ptr(q), _abi.ptr(out), _abi.current_stream_ptr())
+        _abi.check(rc, "csb_mesh_rotation_forward")
+        ctx.save_for_backward(v0, v, f, ids, q)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        lib = _abi.lib()
+        v0, v, f, ids, q = ctx.saved_tensors
+        g = grad_out.float().contiguous()
+        P, Nv, F = ids.numel(), v.size(0), f.size(1)
+        dv = torch.empty_like(v) if ctx.needs_input_grad[1] else None
+        dq = torch.empty_like(q) if ctx.needs_input_grad[4] else None
+        with torch.cuda.device(v.device):
+            rc = lib.csb_mesh_rotation_backward(P, Nv, F, _abi.ptr(v0), _abi.ptr(v), _abi.ptr(f), _abi.ptr(ids),
+                                                _abi.ptr(q), _abi.ptr(g), _abi.ptr(dv) if dv is not None else None,
+                                                _abi.ptr(dq) if dq is not None else None, _abi.current_stream_ptr())
+        _abi.check(rc, "csb_mesh_rotation_backward")
+        return None, dv, None, None, dq
+
+
+def mesh_rotation(rest_vertices, vertices, face, face_ids, rotation):
+    """[P,4] XYZW quaternions: normalize(rotation) composed with the rest -> deformed rotation of each face."""
+    return _MeshRotation.apply(rest_vertices, vertices, face, face_ids, rotation)
+
+
 def barycentric_xyz(vertices, face, face_ids, face_bary):
     """[P,3] positions of Gaussians anchored at barycentric coordinates `face_bary` of faces `face_ids`."""
     return _MeshXYZ.apply(vertices, face, face_ids, face_bary)
@@ -72,21 +121,84 @@ class _Mesh:
 
 
 class MultiGaussianMesh(torch.nn.Module):
-    """The attributes `get_xyz` reads in the reference class (`mesh.pos`, `mesh.face`, `face_ids`, `face_bary`)
-    and the method itself; everything else of the reference class is bookkeeping outside the hot path."""
+    """What `render()` reads from the reference class (scene_reconstruction/gaussian_mesh.py:105-262 and the
+    GaussianModel accessors, gaussian_model.py:96-118): `mesh.pos`, `mesh.face`, `face_ids`, `face_bary`,
+    `_features_dc/_features_rest/_scaling/_rotation/_opacity`, `get_xyz`, `get_rotation`, `get_scaling`,
+    `get_opacity`, `get_features`, `active_sh_degree`.  Optimiser set-up, densification and PLY / hdf5 IO of the
+    reference class are bookkeeping outside the hot path."""
 
-    def __init__(self, pos, face, face_ids, face_bary):
+    def __init__(self, pos, face, face_ids, face_bary, sh_degree: int = 3):
         super().__init__()
         self.mesh = _Mesh(pos, face)
         self.face_ids = face_ids
         self.face_bary = torch.nn.Parameter(face_bary.clone()) if not isinstance(face_bary, torch.nn.Parameter) else face_bary
+        self.max_sh_degree = sh_degree
+        self.active_sh_degree = 0
+        self._features_dc = self._features_rest = self._scaling = self._rotation = self._opacity = None
+
+    @classmethod
+    def from_mesh(cls, pos, face, gaussian_init_factor=2, sh_degree=3, generator=None):
+        """Initialisation of `_setup_callback` (gaussian_mesh.py:206-262): `gaussian_init_factor` Gaussians per
+        face at jittered barycentres, scale = sqrt of the mean squared distance to the 3 nearest Gaussians
+        (distCUDA2), identity rotation parameter (1,0,0,0), opacity 0.1, DC colour ~ U(0,1)/255."""
+        from simple_knn._C import distCUDA2
+
+        dev = pos.device
+        n_faces = face.shape[1]
+        P = gaussian_init_factor * n_faces
+        bary = torch.full((P, 3), 1.0 / 3.0, device=dev)
+        if gaussian_init_factor > 1:
+            bary = torch.clip(bary + 0.05 * torch.randn((P, 3), device=dev, generator=generator), 0.0, 1.0)
+            bary = bary / bary.sum(dim=1, keepdim=True)
+        face_ids = torch.arange(n_faces, dtype=torch.long, device=dev).repeat(gaussian_init_factor).sort().values
+        self = cls(pos, face, face_ids, bary, sh_degree)
+        rgb = torch.rand((P, 3), device=dev, generator=generator) / 255.0
+        feats = torch.zeros((P, 3, (sh_degree + 1) ** 2), device=dev)
+        feats[:, :3, 0] = (rgb - 0.5) / 0.28209479177387814
+        with torch.no_grad():
+            dist2 = torch.clamp_min(distCUDA2(self.get_xyz().detach()), 1e-7)
+        rots = torch.zeros((P, 4), device=dev)
+        rots[:, 0] = 1
+        op = torch.full((P, 1), 0.1, device=dev)
+        self.set_gaussians(feats[:, :, 0:1].transpose(1, 2).contiguous(), feats[:, :, 1:].transpose(1, 2).contiguous(),
+                           torch.log(torch.sqrt(dist2))[..., None].repeat(1, 3), rots, torch.log(op / (1 - op)))
+        return self
+
+    def set_gaussians(self, features_dc, features_rest, scaling, rotation, opacity):
+        """Raw (pre-activation) parameters: [P,1,3], [P,(D+1)^2-1,3], log-scales [P,3], quaternion [P,4], logit [P,1]."""
+        P = torch.nn.Parameter
+        self._features_dc, self._features_rest = P(features_dc), P(features_rest)
+        self._scaling, self._rotation, self._opacity = P(scaling), P(rotation), P(opacity)
 
     @property
     def num_gaussians(self):
         return self.face_ids.shape[0]
+
+    @property
+    def get_scaling(self):
+        return torch.exp(self._scaling)
+
+    @property
+    def get_opacity(self):
+        return torch.sigmoid(self._opacity)
+
+    @property
+    def get_features(self):
+        return torch.cat((self._features_dc, self._features_rest), dim=1)
+
+    def oneupSHdegree(self):
+        if self.active_sh_degree < self.max_sh_degree:
+            self.active_sh_degree += 1
 
     def get_xyz(self, deformed_vertices=None):
         if deformed_vertices is not None:
             assert deformed_vertices.shape[0] == self.mesh.pos.shape[0]
         verts = self.mesh.pos if deformed_vertices is None else deformed_vertices
         return barycentric_xyz(verts, self.mesh.face, self.face_ids, self.face_bary)
+
+    def get_rotation(self, deformed_vertices=None):
+        """normalize(_rotation), composed with each face's rest -> deformed rotation when a deformed mesh is given
+        (gaussian_mesh.py:171-188)."""
+        if deformed_vertices is None:
+            return torch.nn.functional.normalize(self._rotation)
+        return mesh_rotation(self.mesh.pos, deformed_vertices, self.mesh.face, self.face_ids, self._rotation)

@@ -220,6 +220,18 @@ int csb_mesh_xyz_backward(int P, int Nv, int F, const float* vertices, const int
                           const float* face_bary, const float* dL_dxyz, float* dL_dvertices, float* dL_dface_bary,
                           void* stream);
 
+/* MultiGaussianMesh.get_rotation(deformed_vertices) (scene_reconstruction/gaussian_mesh.py:171-188):
+ *   out[p] = quat_product(normalize(rotation[p]), rotmat_to_unitquat(Kabsch(rest[face_p] -> vertices[face_p])))
+ * quaternions in roma's XYZW layout, as the reference composes them.  rest_vertices / vertices f32[Nv,3];
+ * face i64[3,F]; face_ids i64[P]; rotation f32[P,4] (raw parameter); out f32[P,4].
+ * Backward: dL_dvertices f32[Nv,3] (zeroed inside, then accumulated) and dL_drotation f32[P,4]; either may be NULL. */
+int csb_mesh_rotation_forward(int P, int Nv, int F, const float* rest_vertices, const float* vertices,
+                              const int64_t* face, const int64_t* face_ids, const float* rotation, float* out,
+                              void* stream);
+int csb_mesh_rotation_backward(int P, int Nv, int F, const float* rest_vertices, const float* vertices,
+                               const int64_t* face, const int64_t* face_ids, const float* rotation,
+                               const float* dL_dout, float* dL_dvertices, float* dL_drotation, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
