@@ -405,16 +405,28 @@ def run_b200(args, rank, world, dev):
     h2d = sum(t.numel() * 4 for t in host.values()) + dl_host.numel() * 4
     d2h = sum(t.numel() * 4 for t in grads_host.values())
 
+    copy_stream = torch.cuda.Stream(device=dev)
+    dl_ready = torch.cuda.Event()
+
     def e2e_step():
+        # dL/dpixel (the large input) is only needed by the backward: its H2D copy runs on a side stream
+        # while the forward renders; the parameters go first on the compute stream
+        copy_stream.wait_stream(stream)
+        with torch.cuda.stream(copy_stream):
+            dl_dev.copy_(dl_host, non_blocking=True)
+            dl_ready.record(copy_stream)
         with torch.no_grad():
             for k in PARAM_NAMES:
                 leaves[k].copy_(host[k], non_blocking=True)
                 leaves[k].grad = None
-            dl_dev.copy_(dl_host, non_blocking=True)
+        first = True
         for b in view_batches:
             color, radii, depth = dgr.rasterize_views([sl[v] for v in b], leaves["means3D"], leaves["opacities"],
                                                       shs=leaves["shs"], scales=leaves["scales"],
                                                       rotations=leaves["rotations"])
+            if first:
+                stream.wait_event(dl_ready)
+                first = False
             color.backward(dl_dev[b[0]:b[-1] + 1])
         if world > 1:
             flat = torch.cat([leaves[k].grad.reshape(-1) for k in PARAM_NAMES])

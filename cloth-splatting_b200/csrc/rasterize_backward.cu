@@ -74,6 +74,27 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
     const float ddelx_dx = 0.5 * vb.W;
     const float ddely_dy = 0.5 * vb.H;
 
+    // which of the 9 accumulator components (mx my cx cy cw op c0 c1 c2) this lane ends up holding, see XCH below
+    const bool up16 = (lane & 16) != 0, up8 = (lane & 8) != 0, up4 = (lane & 4) != 0, up2 = (lane & 2) != 0;
+    int my_comp = -1;
+    if (!(lane & 1)) {
+        const int base = up16 ? 5 : 0;
+        if (!up8) my_comp = up4 ? (up2 ? -1 : base + 2) : base + (up2 ? 1 : 0);
+        else if (!up4) my_comp = up16 ? (up2 ? -1 : 8) : 3 + (up2 ? 1 : 0);
+    }
+#define XCH2(a, b, o, up)                                               \
+    {                                                                   \
+        const float snd_ = (up) ? (a) : (b);                            \
+        const float kp_ = (up) ? (b) : (a);                             \
+        (a) = kp_ + __shfl_xor_sync(0xFFFFFFFFu, snd_, (o));            \
+    }
+#define XCH1(a, o, up)                                                  \
+    {                                                                   \
+        const float snd_ = (up) ? (a) : 0.f;                            \
+        const float kp_ = (up) ? 0.f : (a);                             \
+        (a) = kp_ + __shfl_xor_sync(0xFFFFFFFFu, snd_, (o));            \
+    }
+
     const int rounds = (int)((used + BW_BATCH - 1) / BW_BATCH);
     int todo = (int)used;
     for (int r = 0; r < rounds; ++r, todo -= BW_BATCH) {
@@ -152,29 +173,16 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
                 g_cw = -0.5f * gdy * dy * dL_dG;
                 g_op = G * dL_dalpha;
             }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                g_mx += __shfl_xor_sync(0xFFFFFFFFu, g_mx, o);
-                g_my += __shfl_xor_sync(0xFFFFFFFFu, g_my, o);
-                g_cx += __shfl_xor_sync(0xFFFFFFFFu, g_cx, o);
-                g_cy += __shfl_xor_sync(0xFFFFFFFFu, g_cy, o);
-                g_cw += __shfl_xor_sync(0xFFFFFFFFu, g_cw, o);
-                g_op += __shfl_xor_sync(0xFFFFFFFFu, g_op, o);
-                g_c0 += __shfl_xor_sync(0xFFFFFFFFu, g_c0, o);
-                g_c1 += __shfl_xor_sync(0xFFFFFFFFu, g_c1, o);
-                g_c2 += __shfl_xor_sync(0xFFFFFFFFu, g_c2, o);
-            }
-            // lanes 0..8 add one component each: one 9-lane reduction instruction per warp
-            float mine = g_mx;
-            mine = lane == 1 ? g_my : mine;
-            mine = lane == 2 ? g_cx : mine;
-            mine = lane == 3 ? g_cy : mine;
-            mine = lane == 4 ? g_cw : mine;
-            mine = lane == 5 ? g_op : mine;
-            mine = lane == 6 ? g_c0 : mine;
-            mine = lane == 7 ? g_c1 : mine;
-            mine = lane == 8 ? g_c2 : mine;
-            if (lane < 9) atomicAdd(&grad_acc[(size_t)s_id[j] * ACC_STRIDE + lane], mine);
+            // Transposed butterfly: at every step a lane hands one half of its remaining partial sums to its
+            // partner and keeps the other half (9 -> 5 -> 3 -> 2 -> 1 values: 12 shuffles instead of 9 x 5).
+            // Afterwards lane l (even) holds the warp total of component comp_of_lane (set up before the loop).
+            XCH2(g_mx, g_op, 16, up16); XCH2(g_my, g_c0, 16, up16); XCH2(g_cx, g_c1, 16, up16);
+            XCH2(g_cy, g_c2, 16, up16); XCH1(g_cw, 16, up16);
+            XCH2(g_mx, g_cy, 8, up8); XCH2(g_my, g_cw, 8, up8); XCH1(g_cx, 8, up8);
+            XCH2(g_mx, g_cx, 4, up4); XCH1(g_my, 4, up4);
+            XCH2(g_mx, g_my, 2, up2);
+            g_mx += __shfl_xor_sync(0xFFFFFFFFu, g_mx, 1);
+            if (my_comp >= 0) atomicAdd(&grad_acc[(size_t)s_id[j] * ACC_STRIDE + my_comp], g_mx);
           }
         }
     }
