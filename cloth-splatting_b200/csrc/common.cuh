@@ -145,9 +145,26 @@ static inline int sorted_side(size_t total_tiles) {
     return ((bits + 7) / 8) & 1;
 }
 int fill_view_batch(struct ViewBatch& vb, int num_views, const csb_view* views, int P, int width, int height);
+// hist_ready: the caller's producer kernel already accumulated the digit histograms of all passes into `hist`
+// (warp_hist_add below), so the separate histogram launch is skipped.
 int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
                      const uint32_t* n_dev, size_t n_max, int end_bit, uint32_t* hist /*4x256, zeroed*/,
                      uint32_t* tickets /*4, zeroed*/, uint32_t* lookback /*zeroed*/, int* side_out,
-                     cudaStream_t stream);
+                     cudaStream_t stream, bool hist_ready = false);
+
+#ifdef __CUDACC__
+// One key per lane -> shared-memory digit histograms of `passes` 8-bit digits (sh[p * 256 + d]).  Neighbouring keys
+// mostly share their upper digits (depth exponents, tile rows): the lanes that agree with lane 0 are counted with one
+// ballot, only the others fall back to their own atomic.  All 32 lanes must call it; `ok` masks lanes without a key.
+__device__ __forceinline__ void warp_hist_add(uint32_t* sh, int passes, uint32_t key, bool ok, int lane) {
+    for (int p = 0; p < passes; ++p) {
+        const uint32_t dd = ok ? ((key >> (8 * p)) & 255u) : 0x1FFu;
+        const uint32_t d0 = __shfl_sync(0xFFFFFFFFu, dd, 0);
+        const uint32_t same = __ballot_sync(0xFFFFFFFFu, dd == d0);
+        if (lane == 0 && d0 < 256u) atomicAdd(&sh[p * 256 + d0], (uint32_t)__popc(same));
+        if (dd != d0 && dd < 256u) atomicAdd(&sh[p * 256 + dd], 1u);
+    }
+}
+#endif
 
 }  // namespace csb

@@ -43,17 +43,11 @@ sort_histogram_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restr
     __syncthreads();
     const size_t stride = (size_t)gridDim.x * SORT_THREADS;
     const uint32_t lane = threadIdx.x & 31;
-    // warp-uniform trip count so that match_any always sees the full warp
+    // warp-uniform trip count: warp_hist_add is warp-collective
     for (size_t base = (size_t)blockIdx.x * SORT_THREADS + (threadIdx.x & ~31u); base < n; base += stride) {
         const size_t i = base + lane;
         const bool ok = i < n;
-        const uint32_t k = ok ? keys[i] : 0u;
-        for (int p = 0; p < passes; ++p) {
-            const uint32_t d = (k >> (p * RADIX_BITS)) & (RADIX - 1);
-            // adjacent instances mostly share their upper digits: aggregate equal digits of a warp
-            const uint32_t peers = __match_any_sync(0xFFFFFFFFu, ok ? d : 0xFFFFFFFFu);
-            if (ok && (peers & ((1u << lane) - 1)) == 0) atomicAdd(&sh[p * RADIX + d], __popc(peers));
-        }
+        warp_hist_add(sh, passes, ok ? keys[i] : 0u, ok, (int)lane);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < passes * RADIX; i += SORT_THREADS) {
@@ -162,14 +156,30 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
 
     uint32_t prefix = 0;
     if (tile > 0) {
+        // Look-back, LB_BATCH predecessors per round trip: the status loads of a batch are independent and in
+        // flight together (a one-at-a-time walk costs an L2 latency per predecessor, and with ~700 tiles
+        // resident the first wave walks hundreds of them).
+        constexpr int LB_BATCH = 8;
         int t = (int)tile - 1;
-        while (true) {
-            const uint32_t s = ld_volatile_u32(lookback + (size_t)t * RADIX + tid);
-            const uint32_t f = s & ~LB_VALUE_MASK;
-            if (f == 0) continue;  // predecessor not published yet (it holds an earlier ticket: it runs)
-            prefix += s & LB_VALUE_MASK;
-            if (f == LB_FLAG_INC) break;
-            --t;
+        bool done = false;
+        while (!done) {
+            uint32_t s[LB_BATCH];
+#pragma unroll
+            for (int b = 0; b < LB_BATCH; ++b)
+                s[b] = (t - b) >= 0 ? ld_volatile_u32(lookback + (size_t)(t - b) * RADIX + tid) : LB_FLAG_INC;
+            int used = 0;
+#pragma unroll
+            for (int b = 0; b < LB_BATCH; ++b) {
+                if (!done && used == b) {
+                    const uint32_t f = s[b] & ~LB_VALUE_MASK;
+                    if (f != 0) {  // published (an unpublished predecessor holds an earlier ticket: it runs)
+                        prefix += s[b] & LB_VALUE_MASK;
+                        used = b + 1;
+                        if (f == LB_FLAG_INC) done = true;
+                    }
+                }
+            }
+            t -= used;
         }
         st_volatile_u32(my_status, LB_FLAG_INC | (prefix + count));
     }
@@ -198,7 +208,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
 
 int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
                      const uint32_t* n_dev, size_t n_max, int end_bit, uint32_t* hist, uint32_t* tickets,
-                     uint32_t* lookback, int* side_out, cudaStream_t stream) {
+                     uint32_t* lookback, int* side_out, cudaStream_t stream, bool hist_ready) {
     if (end_bit < 1) end_bit = 1;
     if (end_bit > 32) return CSB_ERR_BAD_ARG;
     const int passes = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
@@ -208,7 +218,8 @@ int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint3
     int hist_blocks = (int)((n_max + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
     if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
     if (hist_blocks < 1) hist_blocks = 1;
-    CSB_LAUNCH("sort_histogram", stream, sort_histogram_kernel<<<hist_blocks, SORT_THREADS, 0, stream>>>(keys_a, n_dev, passes, hist));
+    if (!hist_ready)
+        CSB_LAUNCH("sort_histogram", stream, sort_histogram_kernel<<<hist_blocks, SORT_THREADS, 0, stream>>>(keys_a, n_dev, passes, hist));
     uint32_t *kin = keys_a, *kout = keys_b, *vin = vals_a, *vout = vals_b;
     for (int p = 0; p < passes; ++p) {
         CSB_LAUNCH("sort_onesweep", stream, sort_onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, 0, stream>>>(

@@ -104,16 +104,13 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, int M, const float* __restr
     return make_float3(fmaxf(res[0], 0.0f), fmaxf(res[1], 0.0f), fmaxf(res[2], 0.0f));
 }
 
-__global__ void __launch_bounds__(256)
-preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ means3D,
-                  const float* __restrict__ scales, float scale_modifier, const float* __restrict__ rotations,
-                  const float* __restrict__ opacities, const float* __restrict__ shs,
-                  const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
-                  int* __restrict__ radii, GeomState g) {
-    const size_t e = (size_t)blockIdx.x * 256 + threadIdx.x;  // entry = v*P + idx
-    const size_t n = (size_t)vb.V * vb.P;
-    if (e == 0) g.control[CTRL_N_ENTRIES] = (uint32_t)n;  // element count of the depth sort
-    if (e >= n) return;
+// One (view, Gaussian) entry; returns its depth-sort key (0xFFFFFFFF when culled).
+__device__ __forceinline__ uint32_t
+preprocess_entry(const size_t e, const ViewBatch& vb, int D, int M, const float* __restrict__ means3D,
+                 const float* __restrict__ scales, float scale_modifier, const float* __restrict__ rotations,
+                 const float* __restrict__ opacities, const float* __restrict__ shs,
+                 const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
+                 int* __restrict__ radii, const GeomState& g) {
     const int v = (int)(e / vb.P);
     const int idx = (int)(e - (size_t)v * vb.P);
 
@@ -128,7 +125,7 @@ preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ me
 
     // near culling (auxiliary.h:139-164): only view-space z is tested
     const float3 p_view = xform_point_4x3(p_orig, vm);
-    if (p_view.z <= 0.2f) return;
+    if (p_view.z <= 0.2f) return 0xFFFFFFFFu;
 
     const float4 p_hom = xform_point_4x4(p_orig, pm);
     const float p_w = 1.0f / (p_hom.w + 0.0000001f);
@@ -150,7 +147,7 @@ preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ me
     const float3 cov = cov2d_from_proj(ep, cov6);
 
     const float det = (cov.x * cov.z - cov.y * cov.y);
-    if (det == 0.0f) return;
+    if (det == 0.0f) return 0xFFFFFFFFu;
     const float det_inv = 1.f / det;
     const float3 conic = make_float3(cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv);
 
@@ -162,7 +159,7 @@ preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ me
     uint2 rect_min, rect_max;
     tile_rect(point_image, (int)my_radius, vb.gx, vb.gy, rect_min, rect_max);
     const uint32_t area = (rect_max.x - rect_min.x) * (rect_max.y - rect_min.y);
-    if (area == 0) return;
+    if (area == 0) return 0xFFFFFFFFu;
 
     float3 rgb;
     uint8_t clamped = 0;
@@ -181,6 +178,34 @@ preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ me
     g.tiles_touched[e] = area;
     g.rects[e] = make_uint4(rect_min.x, rect_min.y, rect_max.x - rect_min.x, __float_as_uint(p_view.z));
     g.depth_keys[e] = __float_as_uint(p_view.z);
+    return __float_as_uint(p_view.z);
+}
+
+// One thread per (view, Gaussian) entry.  The digit histograms of the depth sort's four passes are accumulated
+// here (shared-memory bins, flushed once per block), so the sort needs no histogram pass of its own.
+__global__ void __launch_bounds__(256)
+preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ means3D,
+                  const float* __restrict__ scales, float scale_modifier, const float* __restrict__ rotations,
+                  const float* __restrict__ opacities, const float* __restrict__ shs,
+                  const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
+                  int* __restrict__ radii, GeomState g) {
+    __shared__ uint32_t sh[4 * 256];
+    for (int i = threadIdx.x; i < 4 * 256; i += 256) sh[i] = 0;
+    __syncthreads();
+    const size_t e = (size_t)blockIdx.x * 256 + threadIdx.x;  // entry = v*P + idx
+    const size_t n = (size_t)vb.V * vb.P;
+    if (e == 0) g.control[CTRL_N_ENTRIES] = (uint32_t)n;  // element count of the depth sort
+    uint32_t key = 0;
+    if (e < n)
+        key = preprocess_entry(e, vb, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp,
+                               colors_precomp, radii, g);
+    warp_hist_add(sh, 4, key, e < n, threadIdx.x & 31);
+    __syncthreads();
+    uint32_t* hist = g.control + CTRL_HIST_DEPTH;
+    for (int i = threadIdx.x; i < 4 * 256; i += 256) {
+        const uint32_t c = sh[i];
+        if (c) atomicAdd(&hist[i], c);
+    }
 }
 
 // ----------------------------------------------------------------------------------
@@ -202,12 +227,14 @@ constexpr uint64_t SCAN_VAL = (1ull << 62) - 1;
 __global__ void __launch_bounds__(256)
 emit_kernel(const ViewBatch vb, const uint32_t* __restrict__ order, GeomState g, uint64_t* __restrict__ scan_state,
             uint32_t* __restrict__ out_tiles, uint32_t* __restrict__ out_vals, size_t capacity,
-            uint32_t* __restrict__ num_rendered_out) {
+            uint32_t* __restrict__ num_rendered_out, int tile_passes) {
+    __shared__ uint32_t sh[3 * 256];  // digit histograms of the tile sort's passes
     __shared__ uint32_t s_block;
     __shared__ uint32_t s_warp_tot[8];
     __shared__ uint64_t s_excl;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_block = atomicAdd(&g.control[CTRL_TICKET_SCAN], 1u);
+    for (int i = tid; i < 3 * 256; i += 256) sh[i] = 0;
     __syncthreads();
     const uint32_t blk = s_block;
     const size_t n = (size_t)vb.V * vb.P;
@@ -282,11 +309,12 @@ emit_kernel(const ViewBatch vb, const uint32_t* __restrict__ order, GeomState g,
     }
     __syncthreads();
     const uint64_t warp_base = s_excl + warp_off;
-    if (warp_base + wtotal > capacity) return;  // overflow: the caller grows the workspace and retries
+    // overflow: nothing is emitted, the caller grows the workspace and retries
+    const uint32_t wemit = (warp_base + wtotal > capacity) ? 0u : wtotal;
 
     // flat emission: item k of the warp belongs to the lane g with wexcl[g] <= k < wexcl[g] + cnt[g]
     const float inv_w = 1.0f / (float)rect.z;
-    for (uint32_t k = lane; k < ((wtotal + 31) & ~31u); k += 32) {
+    for (uint32_t k = lane; k < ((wemit + 31) & ~31u); k += 32) {
         int gl = 0;
 #pragma unroll
         for (int s = 16; s > 0; s >>= 1) {
@@ -301,15 +329,23 @@ emit_kernel(const ViewBatch vb, const uint32_t* __restrict__ order, GeomState g,
         const uint32_t g_w = __shfl_sync(0xFFFFFFFFu, rect.z, gl);
         const float g_inv_w = __shfl_sync(0xFFFFFFFFu, inv_w, gl);
         const uint32_t g_e = __shfl_sync(0xFFFFFFFFu, e, gl);
-        if (k < wtotal) {
+        uint32_t tile = 0;
+        if (k < wemit) {
             const uint32_t local = k - g_excl;
             const uint32_t ry = (uint32_t)(((float)local + 0.5f) * g_inv_w);
             const uint32_t rx = local - ry * g_w;
             const uint32_t view = g_e / (uint32_t)vb.P;
-            const uint32_t tile = view * (uint32_t)vb.tiles + (g_min_y + ry) * (uint32_t)vb.gx + (g_min_x + rx);
+            tile = view * (uint32_t)vb.tiles + (g_min_y + ry) * (uint32_t)vb.gx + (g_min_x + rx);
             out_tiles[warp_base + k] = tile;
             out_vals[warp_base + k] = g_e;
         }
+        warp_hist_add(sh, tile_passes, tile, k < wemit, lane);
+    }
+    __syncthreads();
+    uint32_t* hist = g.control + CTRL_HIST_TILE;
+    for (int i = tid; i < tile_passes * 256; i += 256) {
+        const uint32_t c = sh[i];
+        if (c) atomicAdd(&hist[i], c);
     }
 }
 
@@ -530,18 +566,20 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
         int side = 0;
         rc = radix_sort_pairs(g.depth_keys, g.keys_b, g.order_a, g.order_b, g.control + CTRL_N_ENTRIES, n, 32,
                               g.control + CTRL_HIST_DEPTH, g.control + CTRL_TICKET_DEPTH, depth_lookback, &side,
-                              stream);
+                              stream, /*hist_ready=*/true);
         if (rc) return rc;
         const uint32_t* order = side ? g.order_b : g.order_a;
+        const int tile_passes = (higher_msb((uint32_t)total_tiles) + 7) / 8;
+        const bool tile_hist_fused = tile_passes <= 3;  // emit_kernel keeps 3 x 256 bins
         CSB_LAUNCH("emit", stream, emit_kernel<<<blocks, 256, 0, stream>>>(vb, order, g, (uint64_t*)scan_state, b.tiles_a, b.vals_a,
-                                                binning_capacity, num_rendered_dev));
+                                                binning_capacity, num_rendered_dev, tile_hist_fused ? tile_passes : 0));
         if (binning_capacity > 0) {
             CSB_CUDA_TRY(cudaMemsetAsync(b.lookback, 0, b.lookback_words * sizeof(uint32_t), stream));
             const int tile_bits = higher_msb((uint32_t)total_tiles);
             int tside = 0;
             rc = radix_sort_pairs(b.tiles_a, b.tiles_b, b.vals_a, b.vals_b, g.control + CTRL_NUM_RENDERED,
                                   binning_capacity, tile_bits, g.control + CTRL_HIST_TILE,
-                                  g.control + CTRL_TICKET_TILE, b.lookback, &tside, stream);
+                                  g.control + CTRL_TICKET_TILE, b.lookback, &tside, stream, /*hist_ready=*/tile_hist_fused);
             if (rc) return rc;
             // the final order always lives in *_a for the consumers: copy back if it ended in *_b
             const uint32_t* st = tside ? b.tiles_b : b.tiles_a;
