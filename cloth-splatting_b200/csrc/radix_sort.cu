@@ -57,14 +57,14 @@ sort_histogram_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restr
 }
 
 // ---- one onesweep pass -------------------------------------------------------------
-__global__ void __launch_bounds__(SORT_THREADS)
+__global__ void __launch_bounds__(SORT_THREADS, 3)
 sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                      const uint32_t* __restrict__ n_dev, int shift, const uint32_t* __restrict__ hist,
                      uint32_t* __restrict__ ticket, uint32_t* __restrict__ lookback) {
     __shared__ uint32_t warp_cnt[SORT_WARPS][RADIX];  // per-warp digit counters -> exclusive warp offsets
     __shared__ uint32_t digit_start[RADIX];           // first slot of a digit inside the sorted tile
-    __shared__ uint32_t global_base[RADIX];           // destination of a digit's first element of this tile
+    __shared__ uint32_t global_base[RADIX];           // destination of the digit's run minus its first tile slot
     __shared__ uint32_t scan_tmp[SORT_WARPS];
     __shared__ uint32_t s_keys[CSB_SORT_TILE];
     __shared__ uint32_t s_vals[CSB_SORT_TILE];
@@ -95,7 +95,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
     }
 
     // warp-striped load: item i of lane l is element warp*512 + i*32 + l of the tile
-    uint32_t key[SORT_ITEMS], val[SORT_ITEMS];
+    uint32_t key[SORT_ITEMS];
     uint16_t rank[SORT_ITEMS];
     const uint32_t wbase = warp * (SORT_ITEMS * 32) + lane;
 #pragma unroll
@@ -103,7 +103,6 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
         const uint32_t e = wbase + i * 32;
         const bool ok = e < n_valid;
         key[i] = ok ? keys_in[tile_start + e] : 0xFFFFFFFFu;
-        val[i] = ok ? vals_in[tile_start + e] : 0u;
     }
     // stable ranking inside the warp
     const uint32_t lt_mask = (1u << lane) - 1;
@@ -184,10 +183,17 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
         st_volatile_u32(my_status, LB_FLAG_INC | (prefix + count));
     }
     digit_start[tid] = tile_excl;
-    global_base[tid] = hist_excl + prefix;
+    global_base[tid] = hist_excl + prefix - tile_excl;  // destination of tile slot p of this digit = base + p (wraps)
     __syncthreads();
 
-    // scatter into tile-sorted order in shared memory
+    // scatter into tile-sorted order in shared memory (the values are only loaded now: 16 fewer live
+    // registers while ranking and looking back, the loads overlap other blocks' work)
+    uint32_t val[SORT_ITEMS];
+#pragma unroll
+    for (int i = 0; i < SORT_ITEMS; ++i) {
+        const uint32_t e = wbase + i * 32;
+        val[i] = e < n_valid ? vals_in[tile_start + e] : 0u;
+    }
 #pragma unroll
     for (int i = 0; i < SORT_ITEMS; ++i) {
         const uint32_t d = (key[i] >> shift) & (RADIX - 1);
@@ -200,7 +206,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
     for (uint32_t p = tid; p < n_valid; p += SORT_THREADS) {
         const uint32_t k = s_keys[p];
         const uint32_t d = (k >> shift) & (RADIX - 1);
-        const uint32_t dst = global_base[d] + (p - digit_start[d]);
+        const uint32_t dst = global_base[d] + p;
         keys_out[dst] = k;
         vals_out[dst] = s_vals[p];
     }

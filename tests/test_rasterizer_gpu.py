@@ -128,7 +128,9 @@ def _compare_with_reference(g, cam, sh_degree=3, bg=(1.0, 1.0, 1.0)):
     assert float((depth[0] - d_ref).abs().max()) <= COLOR_ATOL * zmax
     # gradients
     dl = torch.from_numpy(S.pixel_grad(1, H, W)).cuda()
-    g_ref = ref.backward(dl[0])
+    g_ref = {k: (v.clone() if v is not None else None) for k, v in ref.backward(dl[0]).items()}
+    # the reference accumulates with float atomics: its own run-to-run spread is part of the budget
+    g_ref2 = ref.backward(dl[0])
     got = Hh.product_backward(gc, cam, views, fwd, dl, sh_degree)
     for k in ("means2D", "opacities", "means3D", "cov3D", "shs", "scales", "rotations", "colors"):
         if g_ref.get(k) is None or got[k].numel() == 0:
@@ -139,7 +141,9 @@ def _compare_with_reference(g, cam, sh_degree=3, bg=(1.0, 1.0, 1.0)):
             continue
         a = got[k][0] if k == "means2D" else got[k]
         rel = Hh.rel_err(a.cpu().numpy(), g_ref[k].cpu().numpy())
-        assert rel < _grad_tol(k), f"grad {k}: rel {rel}"
+        spread = Hh.rel_err(g_ref2[k].cpu().numpy(), g_ref[k].cpu().numpy())
+        assert spread < 3e-4, f"reference run-to-run spread of grad {k}: {spread}"
+        assert rel < _grad_tol(k) + 2 * spread, f"grad {k}: rel {rel} (reference vs itself: {spread})"
 
 
 needs_ref = pytest.mark.skipif(not _ref_available(), reason="oracle/_ref/libref_cuda.so not built")
