@@ -95,6 +95,7 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
         (a) = kp_ + __shfl_xor_sync(0xFFFFFFFFu, snd_, (o));            \
     }
 
+    const uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd), a_id = smem_addr(s_id);
     const int rounds = (int)((used + BW_BATCH - 1) / BW_BATCH);
     int todo = (int)used;
     for (int r = 0; r < rounds; ++r, todo -= BW_BATCH) {
@@ -123,12 +124,14 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
             const uint32_t contributor = top - (uint32_t)j;
             if (contributor >= wmax) continue;  // warp-uniform
             bool valid = inside && contributor < last_contributor;
-            const float2 xy = s_xy[j];
+            const float2 xy = lds_f2(a_xy + (uint32_t)j * 8u);
             const float dx = xy.x - pxf, dy = xy.y - pyf;
-            const float4 con_o = s_co[j];
+            const float4 con_o = lds_f4(a_co + (uint32_t)j * 16u);
             const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
             valid = valid && !(power > 0.0f);
-            const float G = expf(power);
+            // 2^(power log2 e) on the SFU: |power| <= 5.6 wherever a pair is blended (alpha >= 1/255), there the
+            // result is within 4e-7 relative of the forward's expf, far inside the gradient tolerance
+            const float G = exp2f_fast(power * 1.4426950408889634f);
             const float alpha = fminf(0.99f, con_o.w * G);
             valid = valid && !(alpha < 1.0f / 255.0f);
             if (!__any_sync(0xFFFFFFFFu, valid)) continue;
@@ -136,9 +139,11 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
             float g_mx = 0.f, g_my = 0.f, g_cx = 0.f, g_cy = 0.f, g_cw = 0.f, g_op = 0.f;
             float g_c0 = 0.f, g_c1 = 0.f, g_c2 = 0.f;
             if (valid) {
-                T = T / (1.f - alpha);
+                // one correctly rounded reciprocal serves T / (1 - alpha) and T_final / (1 - alpha)
+                const float inv_1ma = __frcp_rn(1.f - alpha);
+                T = T * inv_1ma;
                 const float dchannel_dcolor = alpha * T;
-                const float4 cd = s_cd[j];
+                const float4 cd = lds_f4(a_cd + (uint32_t)j * 16u);
                 float dL_dalpha = 0.0f;
                 accum0 = last_alpha * lastc0 + (1.f - last_alpha) * accum0;
                 lastc0 = cd.x;
@@ -159,7 +164,7 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
                 bg_dot_dpixel += bg0 * dpix0;
                 bg_dot_dpixel += bg1 * dpix1;
                 bg_dot_dpixel += bg2 * dpix2;
-                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
 
                 const float dL_dG = con_o.w * dL_dalpha;
                 const float gdx = G * dx;
@@ -182,7 +187,7 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
             XCH2(g_mx, g_cx, 4, up4); XCH1(g_my, 4, up4);
             XCH2(g_mx, g_my, 2, up2);
             g_mx += __shfl_xor_sync(0xFFFFFFFFu, g_mx, 1);
-            if (my_comp >= 0) atomicAdd(&grad_acc[(size_t)s_id[j] * ACC_STRIDE + my_comp], g_mx);
+            if (my_comp >= 0) atomicAdd(&grad_acc[(size_t)lds_u32(a_id + (uint32_t)j * 4u) * ACC_STRIDE + my_comp], g_mx);
           }
         }
     }

@@ -414,6 +414,7 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
     uint32_t last_contributor = 0;
     float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dacc = 0.f;
 
+    const uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd);
     for (int r = 0; r < rounds; ++r, todo -= RENDER_BATCH) {
         if (__syncthreads_count(done) == CSB_TILE_PIX) break;
         const int progress = r * RENDER_BATCH + tid;
@@ -436,9 +437,9 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
                 const int j = g + __ffs(bits) - 1;
                 bits &= bits - 1;
                 if (done) continue;
-                const float2 xy = s_xy[j];
+                const float2 xy = lds_f2(a_xy + (uint32_t)j * 8u);
                 const float dx = xy.x - pxf, dy = xy.y - pyf;
-                const float4 con_o = s_co[j];
+                const float4 con_o = lds_f4(a_co + (uint32_t)j * 16u);
                 const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
                 if (power > 0.0f) continue;
                 const float alpha = fminf(0.99f, con_o.w * expf(power));
@@ -448,7 +449,7 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
                     done = true;
                     continue;
                 }
-                const float4 cd = s_cd[j];
+                const float4 cd = lds_f4(a_cd + (uint32_t)j * 16u);
                 C0 += cd.x * alpha * T;
                 C1 += cd.y * alpha * T;
                 C2 += cd.z * alpha * T;
