@@ -41,6 +41,34 @@ struct LaunchScope {
         CSB_LAUNCH_CHECK();                        \
     } while (0)
 
+// Programmatic dependent launch: the kernel is queued behind its predecessor in the stream and may be scheduled
+// before that one has drained; every kernel launched this way starts with grid_dep_wait(), which returns once
+// the predecessor grid has completed and its writes are visible (same semantics as stream order, minus the launch
+// gap between dependent small kernels).  grid_dep_launch() lets the NEXT kernel of the chain be scheduled early.
+#ifdef __CUDACC__
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() {
+#ifdef CSB_PDL_EARLY_TRIGGER
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Bump allocator over a caller-provided workspace (256-byte aligned slices).

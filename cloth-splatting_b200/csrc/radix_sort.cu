@@ -71,6 +71,8 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
     __shared__ uint32_t s_tile;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    grid_dep_wait();
+    grid_dep_launch();
     if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&warp_cnt[0][0])[i] = 0;
     __syncthreads();
@@ -228,7 +230,7 @@ int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint3
         CSB_LAUNCH("sort_histogram", stream, sort_histogram_kernel<<<hist_blocks, SORT_THREADS, 0, stream>>>(keys_a, n_dev, passes, hist));
     uint32_t *kin = keys_a, *kout = keys_b, *vin = vals_a, *vout = vals_b;
     for (int p = 0; p < passes; ++p) {
-        CSB_LAUNCH("sort_onesweep", stream, sort_onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, 0, stream>>>(
+        CSB_LAUNCH("sort_onesweep", stream, launch_pdl(sort_onesweep_kernel, dim3((unsigned)tiles), dim3(SORT_THREADS), 0, stream, 
             kin, kout, vin, vout, n_dev, p * RADIX_BITS, hist + p * RADIX, tickets + p,
             lookback + (size_t)p * (tiles + 1) * RADIX));
         uint32_t* t = kin; kin = kout; kout = t;

@@ -28,6 +28,8 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
     __shared__ uint32_t s_mask[BW_BATCH];  // bit w: the Gaussian can reach the pixel patch of warp w (patch_mask)
     __shared__ uint32_t s_max_last;
 
+    grid_dep_wait();
+    grid_dep_launch();
     const int v = blockIdx.z;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -301,6 +303,8 @@ gaussian_backward_kernel(const ViewBatch vb, int D, int M, const float* __restri
                          float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
                          float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
                          float* __restrict__ dL_drots) {
+    grid_dep_wait();
+    grid_dep_launch();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= vb.P) return;
     const float3 mean = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
@@ -513,12 +517,13 @@ int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, i
     if (binning_capacity > 0 && binning_ws) {
         const uint32_t* point_list = sorted_side(total_tiles) ? b.vals_b : b.vals_a;
         dim3 tgrid(vb.gx, vb.gy, num_views);
-        CSB_LAUNCH("render_backward", stream, render_backward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, point_list, g.means2D,
+        CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, point_list, g.means2D,
                                                                   g.conic_opacity, g.rgb_depth, im.final_T,
                                                                   im.n_contrib, dL_dpix, g.grad_acc));
     }
     const float* cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
-    CSB_LAUNCH("gaussian_backward", stream, gaussian_backward_kernel<<<(P + 127) / 128, 128, 0, stream>>>(
+    const int gb = P < 148 * 256 ? 64 : 128;  // few Gaussians (C2: 10 k): smaller blocks reach every SM
+    CSB_LAUNCH("gaussian_backward", stream, launch_pdl(gaussian_backward_kernel, dim3((P + gb - 1) / gb), dim3(gb), 0, stream, 
         vb, D, M, means3D, shs, cov3D_precomp ? nullptr : scales, scale_modifier, rotations, cov3D, radii, g.clamped,
         g.grad_acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations));
     return 0;

@@ -190,6 +190,8 @@ preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ me
                   const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
                   int* __restrict__ radii, GeomState g) {
     __shared__ uint32_t sh[4 * 256];
+    grid_dep_wait();
+    grid_dep_launch();
     for (int i = threadIdx.x; i < 4 * 256; i += 256) sh[i] = 0;
     __syncthreads();
     const size_t e = (size_t)blockIdx.x * 256 + threadIdx.x;  // entry = v*P + idx
@@ -233,6 +235,8 @@ emit_kernel(const ViewBatch vb, const uint32_t* __restrict__ order, GeomState g,
     __shared__ uint32_t s_warp_tot[8];
     __shared__ uint64_t s_excl;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    grid_dep_wait();
+    grid_dep_launch();
     if (tid == 0) s_block = atomicAdd(&g.control[CTRL_TICKET_SCAN], 1u);
     for (int i = tid; i < 3 * 256; i += 256) sh[i] = 0;
     __syncthreads();
@@ -356,6 +360,8 @@ __global__ void __launch_bounds__(256)
 tile_ranges_kernel(const uint32_t* __restrict__ n_dev, const uint32_t* __restrict__ tiles,
                    const uint32_t* __restrict__ vals, const float4* __restrict__ rgb_depth,
                    uint2* __restrict__ ranges, uint64_t* __restrict__ keys_out, uint32_t tiles_per_view) {
+    grid_dep_wait();
+    grid_dep_launch();
     const uint32_t n = *n_dev;
     const size_t stride = (size_t)gridDim.x * 256;
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) {
@@ -393,6 +399,8 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
     __shared__ float4 s_cd[RENDER_BATCH];
     __shared__ uint32_t s_mask[RENDER_BATCH];  // bit w: the Gaussian can reach the 8x4 pixel patch of warp w
 
+    grid_dep_wait();
+    grid_dep_launch();
     const int v = blockIdx.z;
     const int tid = threadIdx.x;
     // a warp covers an 8x4 pixel patch of the tile (compact footprint -> coherent early-outs)
@@ -556,10 +564,13 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
     const size_t total_tiles = (size_t)num_views * vb.tiles;
     CSB_CUDA_TRY(cudaMemsetAsync(g.control, 0, g.control_words * sizeof(uint32_t), stream));
     CSB_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, total_tiles * sizeof(uint2), stream));
+    // all memsets first: the kernels behind them form one programmatic-dependent-launch chain
+    if (n > 0 && binning_capacity > 0)
+        CSB_CUDA_TRY(cudaMemsetAsync(b.lookback, 0, b.lookback_words * sizeof(uint32_t), stream));
     dim3 tgrid(vb.gx, vb.gy, num_views);
     if (n > 0) {
         const unsigned blocks = (unsigned)((n + 255) / 256);
-        CSB_LAUNCH("preprocess", stream, preprocess_kernel<<<blocks, 256, 0, stream>>>(vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
+        CSB_LAUNCH("preprocess", stream, launch_pdl(preprocess_kernel, dim3(blocks), dim3(256), 0, stream, vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
                                                       shs, cov3D_precomp, colors_precomp, radii, g));
         // depth order of the (view, Gaussian) entries
         uint32_t* scan_state = g.control + CTRL_SCAN_STATE;
@@ -572,10 +583,9 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
         const uint32_t* order = side ? g.order_b : g.order_a;
         const int tile_passes = (higher_msb((uint32_t)total_tiles) + 7) / 8;
         const bool tile_hist_fused = tile_passes <= 3;  // emit_kernel keeps 3 x 256 bins
-        CSB_LAUNCH("emit", stream, emit_kernel<<<blocks, 256, 0, stream>>>(vb, order, g, (uint64_t*)scan_state, b.tiles_a, b.vals_a,
+        CSB_LAUNCH("emit", stream, launch_pdl(emit_kernel, dim3(blocks), dim3(256), 0, stream, vb, order, g, (uint64_t*)scan_state, b.tiles_a, b.vals_a,
                                                 binning_capacity, num_rendered_dev, tile_hist_fused ? tile_passes : 0));
         if (binning_capacity > 0) {
-            CSB_CUDA_TRY(cudaMemsetAsync(b.lookback, 0, b.lookback_words * sizeof(uint32_t), stream));
             const int tile_bits = higher_msb((uint32_t)total_tiles);
             int tside = 0;
             rc = radix_sort_pairs(b.tiles_a, b.tiles_b, b.vals_a, b.vals_b, g.control + CTRL_NUM_RENDERED,
@@ -587,17 +597,17 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             const uint32_t* sv = tside ? b.vals_b : b.vals_a;
             int rblocks = (int)((binning_capacity + 255) / 256);
             if (rblocks > 148 * 16) rblocks = 148 * 16;
-            CSB_LAUNCH("tile_ranges", stream, tile_ranges_kernel<<<rblocks, 256, 0, stream>>>(g.control + CTRL_NUM_RENDERED, st, sv, g.rgb_depth,
+            CSB_LAUNCH("tile_ranges", stream, launch_pdl(tile_ranges_kernel, dim3(rblocks), dim3(256), 0, stream, g.control + CTRL_NUM_RENDERED, st, sv, g.rgb_depth,
                                                             im.ranges, (flags & 1) ? b.keys : nullptr,
                                                             (uint32_t)vb.tiles));
-            CSB_LAUNCH("render_forward", stream, render_forward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, sv, g.means2D, g.conic_opacity,
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, sv, g.means2D, g.conic_opacity,
                                                                      g.rgb_depth, im.final_T, im.n_contrib, out_color,
                                                                      out_depth));
             if (tside != sorted_side(total_tiles)) return CSB_ERR_UNSUPPORTED;  // consumers recompute the side
         }
     } else {
         CSB_CUDA_TRY(cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream));
-        CSB_LAUNCH("render_forward", stream, render_forward_kernel<<<tgrid, CSB_TILE_PIX, 0, stream>>>(vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity,
+        CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity,
                                                                  g.rgb_depth, im.final_T, im.n_contrib, out_color,
                                                                  out_depth));
     }
