@@ -52,6 +52,7 @@ __device__ __forceinline__ void grid_dep_launch() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 #endif
 }
+__device__ __forceinline__ void grid_dep_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                                      Args... args) {

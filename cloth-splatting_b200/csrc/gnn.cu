@@ -151,6 +151,10 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_mlp_kernel(const __grid_consta
             bulk_g2s(smem_u32(sW + (size_t)c * CHUNK_BYTES), a.unit + (size_t)c * CHUNK_BYTES, CHUNK_BYTES, bar_w);
         bulk_g2s(smem_u32(sF), a.unit + wbytes, fbytes, bar_w);
     }
+    // Programmatic dependent launch: everything above (barriers, TMEM, the bulk copy of the constant weight image)
+    // overlaps the tail of the previous kernel of the forward; its activations are only touched below.
+    grid_dep_trigger();
+    grid_dep_wait();
     bool weights_ready = false;
     uint32_t mma_parity = 0;
     const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW);
@@ -544,7 +548,7 @@ static int launch_role(const Args& a, int kin, int nout, cudaStream_t stream, co
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = tiles < sms ? tiles : sms;
-    CSB_LAUNCH(name, stream, gnn_mlp_kernel<MODE><<<grid, THREADS, smem, stream>>>(a));
+    CSB_LAUNCH(name, stream, launch_pdl(gnn_mlp_kernel<MODE>, dim3(grid), dim3(THREADS), smem, stream, a));
     return 0;
 }
 

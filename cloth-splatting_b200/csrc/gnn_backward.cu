@@ -140,6 +140,8 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_bwd_kernel(const __grid_consta
             bulk_g2s(smem_u32(sW + (size_t)c * CHUNK_BYTES), a.unit + (size_t)c * CHUNK_BYTES, CHUNK_BYTES, bar_w);
         bulk_g2s(smem_u32(sF), a.unit + wbytes, fbytes, bar_w);
     }
+    grid_dep_trigger();  // the next kernel's prologue (weight image copy) may overlap this one's tail
+    grid_dep_wait();
     bool weights_ready = false;
     uint32_t mma_parity = 0;
     const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW);
@@ -680,6 +682,7 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool v
 
 __global__ void __launch_bounds__(THREADS, 1) gnn_wgrad_kernel(const __grid_constant__ WArgs a) {
     const int num_tiles = (a.rows + TILE_M - 1) / TILE_M;
+    grid_dep_trigger();
     if ((int)blockIdx.x >= num_tiles) return;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -721,6 +724,7 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_wgrad_kernel(const __grid_cons
             cp_async16(base + (uint32_t)(2 + kb) * CHUNK_BYTES + swz_off(r, c), job.A + ar * LAT + kb * 64 + c * 8, aok);
         }
     };
+    grid_dep_wait();
     int it = 0;
     load(0, blockIdx.x);
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -818,7 +822,7 @@ static int launch_bwd(const BArgs& a, cudaStream_t stream, const char* name) {
     const int tiles = (a.rows + TILE_M - 1) / TILE_M;
     if (tiles == 0) return 0;
     const int grid = tiles < sm_count() ? tiles : sm_count();
-    CSB_LAUNCH(name, stream, gnn_bwd_kernel<MODE><<<grid, THREADS, smem, stream>>>(a));
+    CSB_LAUNCH(name, stream, launch_pdl(gnn_bwd_kernel<MODE>, dim3(grid), dim3(THREADS), smem, stream, a));
     return 0;
 }
 
@@ -834,7 +838,7 @@ static int launch_wgrad(WArgs& w, cudaStream_t stream) {
     if (per_job < 1) per_job = 1;
     if (per_job > tiles) per_job = tiles;
     dim3 grid(per_job, w.njobs);
-    CSB_LAUNCH("gnn_wgrad", stream, gnn_wgrad_kernel<<<grid, THREADS, WGRAD_SMEM, stream>>>(w));
+    CSB_LAUNCH("gnn_wgrad", stream, launch_pdl(gnn_wgrad_kernel, grid, dim3(THREADS), WGRAD_SMEM, stream, w));
     return 0;
 }
 
