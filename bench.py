@@ -681,11 +681,22 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world, dev)
         return
+    saved_stdout = None
     if world > 1:
         import torch.distributed as dist
 
+        # NCCL prints its version banner on fd 1: keep stdout to the ONE JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+        t = torch.zeros(1, device=dev)
+        dist.all_reduce(t)  # communicator set-up (and its banner) happens here
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     try:
         run_b200(args, rank, world, dev)
     finally:
