@@ -293,20 +293,16 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __res
     return dnormvdv3(dir_orig, dL_ddir);
 }
 
-__global__ void __launch_bounds__(128)
-gaussian_backward_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ means3D,
-                         const float* __restrict__ shs, const float* __restrict__ scales, float scale_modifier,
-                         const float* __restrict__ rotations, const float* __restrict__ cov3D_in,
-                         const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
-                         const float* __restrict__ grad_acc, float* __restrict__ dL_dmeans2D,
-                         float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
-                         float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
-                         float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
-                         float* __restrict__ dL_drots) {
-    grid_dep_wait();
-    grid_dep_launch();
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= vb.P) return;
+// One Gaussian: `sh_row` = its SH record, `my_dsh` = where its dL/dsh record goes (both may live in shared memory).
+__device__ __forceinline__ void
+gaussian_backward_one(const int idx, const ViewBatch& vb, int D, int M, const float* __restrict__ means3D,
+                      const float* sh_row, const float* __restrict__ scales, float scale_modifier,
+                      const float* __restrict__ rotations, const float* __restrict__ cov3D_in,
+                      const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
+                      const float* __restrict__ grad_acc, float* __restrict__ dL_dmeans2D,
+                      float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
+                      float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* my_dsh,
+                      float* __restrict__ dL_dscales, float* __restrict__ dL_drots) {
     const float3 mean = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
 
     float3 dmean_tot = make_float3(0.f, 0.f, 0.f);
@@ -314,7 +310,6 @@ gaussian_backward_kernel(const ViewBatch vb, int D, int M, const float* __restri
     float3 dcolor_tot = make_float3(0.f, 0.f, 0.f);
     float dop_tot = 0.f;
     bool first_sh = true, any_visible = false;
-    float* my_dsh = dL_dsh ? dL_dsh + (size_t)idx * M * 3 : nullptr;
 
     for (int v = 0; v < vb.V; ++v) {
         const size_t e = (size_t)v * vb.P + idx;
@@ -324,12 +319,14 @@ gaussian_backward_kernel(const ViewBatch vb, int D, int M, const float* __restri
             continue;
         }
         any_visible = true;
-        const float* acc = grad_acc + e * ACC_STRIDE;
-        const float2 dmean2D = make_float2(acc[0], acc[1]);
-        const float3 dL_dconic = make_float3(acc[2], acc[3], acc[4]);
+        // 12 floats (48 B, 16-byte aligned) per entry: three vector loads instead of nine scalar ones
+        const float4* acc4 = reinterpret_cast<const float4*>(grad_acc + e * ACC_STRIDE);
+        const float4 acc_a = acc4[0], acc_b = acc4[1], acc_c = acc4[2];
+        const float2 dmean2D = make_float2(acc_a.x, acc_a.y);
+        const float3 dL_dconic = make_float3(acc_a.z, acc_a.w, acc_b.x);
         m2d[0] = dmean2D.x; m2d[1] = dmean2D.y; m2d[2] = 0.f;
-        dop_tot += acc[5];
-        const float3 dL_dcol = make_float3(acc[6], acc[7], acc[8]);
+        dop_tot += acc_b.y;
+        const float3 dL_dcol = make_float3(acc_b.z, acc_b.w, acc_c.x);
         dcolor_tot.x += dL_dcol.x; dcolor_tot.y += dL_dcol.y; dcolor_tot.z += dL_dcol.z;
 
         const float* __restrict__ vm = vb.viewmatrix[v];
@@ -414,10 +411,9 @@ gaussian_backward_kernel(const ViewBatch vb, int D, int M, const float* __restri
         dmean.x += dproj.x; dmean.y += dproj.y; dmean.z += dproj.z;
 
         // ---- colour -> SH and view direction (backward.cu:20-139) ----
-        if (shs != nullptr) {
+        if (sh_row != nullptr) {
             const float3 campos = make_float3(vb.campos[v][0], vb.campos[v][1], vb.campos[v][2]);
-            const float3 dsh_mean = sh_backward(D, M, shs + (size_t)idx * M * 3, mean, campos, clamped[e], dL_dcol,
-                                                my_dsh, first_sh);
+            const float3 dsh_mean = sh_backward(D, M, sh_row, mean, campos, clamped[e], dL_dcol, my_dsh, first_sh);
             first_sh = false;
             dmean.x += dsh_mean.x; dmean.y += dsh_mean.y; dmean.z += dsh_mean.z;
         }
@@ -485,6 +481,47 @@ gaussian_backward_kernel(const ViewBatch vb, int D, int M, const float* __restri
     if (dL_drots) reinterpret_cast<float4*>(dL_drots)[idx] = drot;
 }
 
+// One thread per Gaussian; the block's SH records (192 B each at degree 3) and its dL/dsh records are staged through
+// shared memory so that global memory only sees coalesced 16-byte accesses (the per-thread walk over an AoS record
+// touches 32 different lines per warp instruction).  Row pitch M*3+1 words: conflict-free per-thread access.
+__global__ void __launch_bounds__(128)
+gaussian_backward_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ means3D,
+                         const float* __restrict__ shs, const float* __restrict__ scales, float scale_modifier,
+                         const float* __restrict__ rotations, const float* __restrict__ cov3D_in,
+                         const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
+                         const float* __restrict__ grad_acc, float* __restrict__ dL_dmeans2D,
+                         float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
+                         float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
+                         float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
+                         float* __restrict__ dL_drots) {
+    extern __shared__ float s_rec[];  // [2][blockDim.x][M*3+1]: SH in, dL/dsh out
+    grid_dep_wait();
+    grid_dep_launch();
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int first = blockIdx.x * nthr;
+    const int idx = first + tid;
+    const int rec = M * 3, pitch = rec + 1;
+    const int count = min(nthr, vb.P - first);
+    const bool staged = shs != nullptr && dL_dsh != nullptr;
+    if (staged) {
+        if (rec == 48) stage_records_in<48>(shs + (size_t)first * rec, s_rec, count, rec, tid, nthr);
+        else stage_records_in<0>(shs + (size_t)first * rec, s_rec, count, rec, tid, nthr);
+        __syncthreads();
+    }
+    if (idx < vb.P)
+        gaussian_backward_one(idx, vb, D, M, means3D,
+                              staged ? s_rec + tid * pitch : (shs ? shs + (size_t)idx * rec : nullptr), scales,
+                              scale_modifier, rotations, cov3D_in, radii, clamped, grad_acc, dL_dmeans2D, dL_dcolors,
+                              dL_dopacity, dL_dmeans3D, dL_dcov3D,
+                              staged ? s_rec + (nthr + tid) * pitch : (dL_dsh ? dL_dsh + (size_t)idx * rec : nullptr),
+                              dL_dscales, dL_drots);
+    if (staged) {
+        __syncthreads();
+        if (rec == 48) stage_records_out<48>(dL_dsh + (size_t)first * rec, s_rec + nthr * pitch, count, rec, tid, nthr);
+        else stage_records_out<0>(dL_dsh + (size_t)first * rec, s_rec + nthr * pitch, count, rec, tid, nthr);
+    }
+}
+
 }  // namespace csb
 
 using namespace csb;
@@ -523,7 +560,16 @@ int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, i
     }
     const float* cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
     const int gb = P < 148 * 256 ? 64 : 128;  // few Gaussians (C2: 10 k): smaller blocks reach every SM
-    CSB_LAUNCH("gaussian_backward", stream, launch_pdl(gaussian_backward_kernel, dim3((P + gb - 1) / gb), dim3(gb), 0, stream, 
+    const size_t gsmem = (shs && dL_dsh) ? (size_t)2 * gb * (M * 3 + 1) * sizeof(float) : 0;
+    {
+        static bool configured = false;
+        if (!configured) {
+            CSB_CUDA_TRY(cudaFuncSetAttribute(gaussian_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+            configured = true;
+        }
+    }
+    if (gsmem > 64 * 1024) return CSB_ERR_UNSUPPORTED;
+    CSB_LAUNCH("gaussian_backward", stream, launch_pdl(gaussian_backward_kernel, dim3((P + gb - 1) / gb), dim3(gb), gsmem, stream, 
         vb, D, M, means3D, shs, cov3D_precomp ? nullptr : scales, scale_modifier, rotations, cov3D, radii, g.clamped,
         g.grad_acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations));
     return 0;

@@ -110,7 +110,7 @@ preprocess_entry(const size_t e, const ViewBatch& vb, int D, int M, const float*
                  const float* __restrict__ scales, float scale_modifier, const float* __restrict__ rotations,
                  const float* __restrict__ opacities, const float* __restrict__ shs,
                  const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
-                 int* __restrict__ radii, const GeomState& g) {
+                 int* __restrict__ radii, const GeomState& g, const float* sh_row) {
     const int v = (int)(e / vb.P);
     const int idx = (int)(e - (size_t)v * vb.P);
 
@@ -165,7 +165,7 @@ preprocess_entry(const size_t e, const ViewBatch& vb, int D, int M, const float*
     uint8_t clamped = 0;
     if (colors_precomp == nullptr) {
         const float3 campos = make_float3(vb.campos[v][0], vb.campos[v][1], vb.campos[v][2]);
-        rgb = sh_to_rgb(D, M, shs + (size_t)idx * M * 3, p_orig, campos, clamped);
+        rgb = sh_to_rgb(D, M, sh_row ? sh_row : shs + (size_t)idx * M * 3, p_orig, campos, clamped);
     } else {
         rgb = make_float3(colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]);
     }
@@ -188,19 +188,36 @@ preprocess_kernel(const ViewBatch vb, int D, int M, const float* __restrict__ me
                   const float* __restrict__ scales, float scale_modifier, const float* __restrict__ rotations,
                   const float* __restrict__ opacities, const float* __restrict__ shs,
                   const float* __restrict__ cov3D_precomp, const float* __restrict__ colors_precomp,
-                  int* __restrict__ radii, GeomState g) {
+                  int* __restrict__ radii, GeomState g, int stage_sh) {
     __shared__ uint32_t sh[4 * 256];
+    extern __shared__ float s_rec[];  // [256][M*3+1] SH records of the block (only when the launch provides it)
     grid_dep_wait();
     grid_dep_launch();
     for (int i = threadIdx.x; i < 4 * 256; i += 256) sh[i] = 0;
-    __syncthreads();
     const size_t e = (size_t)blockIdx.x * 256 + threadIdx.x;  // entry = v*P + idx
     const size_t n = (size_t)vb.V * vb.P;
     if (e == 0) g.control[CTRL_N_ENTRIES] = (uint32_t)n;  // element count of the depth sort
+    // Stage the block's SH records with coalesced 16-byte loads (a thread walking its own 192-byte record touches
+    // 32 lines per warp instruction).  Blocks that straddle a view boundary read their records directly.
+    const float* sh_row = nullptr;
+    {
+        const size_t e0 = (size_t)blockIdx.x * 256;
+        const size_t e1 = (e0 + 255 < n ? e0 + 255 : n - 1);
+        const bool one_view = stage_sh && e0 < n && (e0 / vb.P) == (e1 / vb.P);
+        if (one_view) {
+            const int rec = M * 3, pitch = rec + 1;
+            const size_t first = e0 % vb.P;
+            const int count = (int)(e1 - e0 + 1);
+            if (rec == 48) stage_records_in<48>(shs + first * rec, s_rec, count, rec, threadIdx.x, 256);
+            else stage_records_in<0>(shs + first * rec, s_rec, count, rec, threadIdx.x, 256);
+            sh_row = s_rec + threadIdx.x * pitch;
+        }
+    }
+    __syncthreads();
     uint32_t key = 0;
     if (e < n)
         key = preprocess_entry(e, vb, D, M, means3D, scales, scale_modifier, rotations, opacities, shs, cov3D_precomp,
-                               colors_precomp, radii, g);
+                               colors_precomp, radii, g, sh_row);
     warp_hist_add(sh, 4, key, e < n, threadIdx.x & 31);
     __syncthreads();
     uint32_t* hist = g.control + CTRL_HIST_DEPTH;
@@ -570,8 +587,17 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
     dim3 tgrid(vb.gx, vb.gy, num_views);
     if (n > 0) {
         const unsigned blocks = (unsigned)((n + 255) / 256);
-        CSB_LAUNCH("preprocess", stream, launch_pdl(preprocess_kernel, dim3(blocks), dim3(256), 0, stream, vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
-                                                      shs, cov3D_precomp, colors_precomp, radii, g));
+        const size_t rec_smem = (size_t)256 * (M * 3 + 1) * sizeof(float);
+        const int stage_sh = (shs != nullptr && colors_precomp == nullptr && rec_smem <= 56 * 1024) ? 1 : 0;
+        {
+            static bool configured = false;
+            if (!configured) {
+                CSB_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 56 * 1024));
+                configured = true;
+            }
+        }
+        CSB_LAUNCH("preprocess", stream, launch_pdl(preprocess_kernel, dim3(blocks), dim3(256), stage_sh ? rec_smem : 0, stream, vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
+                                                      shs, cov3D_precomp, colors_precomp, radii, g, stage_sh));
         // depth order of the (view, Gaussian) entries
         uint32_t* scan_state = g.control + CTRL_SCAN_STATE;
         uint32_t* depth_lookback = scan_state + 2 * (blocks + 1);

@@ -196,4 +196,45 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
     return v;
 }
 
+// Cooperative copy between `count` consecutive AoS records of `rec` floats in global memory and shared-memory rows of
+// pitch rec+1 words (conflict-free per-thread walks): coalesced 16-byte global accesses.  REC > 0 fixes the record
+// length at compile time (48 = SH degree 3): the row/column split of the flat index becomes a multiply-shift.
+template <int REC>
+__device__ __forceinline__ void stage_records_in(const float* __restrict__ src, float* s_rows, int count, int rec_rt,
+                                                 int tid, int nthr) {
+    const int rec = REC > 0 ? REC : rec_rt, pitch = rec + 1, total = count * rec;
+    const bool vec = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+    for (int i = tid * 4; i < total; i += nthr * 4) {
+        float v[4] = {0.f, 0.f, 0.f, 0.f};
+        if (vec && i + 3 < total) {
+            const float4 q = *reinterpret_cast<const float4*>(src + i);
+            v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+        } else {
+            for (int j = 0; j < 4 && i + j < total; ++j) v[j] = src[i + j];
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int f = i + j;
+            if (f < total) s_rows[(f / rec) * pitch + (f % rec)] = v[j];
+        }
+    }
+}
+template <int REC>
+__device__ __forceinline__ void stage_records_out(float* __restrict__ dst, const float* s_rows, int count, int rec_rt,
+                                                  int tid, int nthr) {
+    const int rec = REC > 0 ? REC : rec_rt, pitch = rec + 1, total = count * rec;
+    const bool vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    for (int i = tid * 4; i < total; i += nthr * 4) {
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int f = i + j;
+            v[j] = f < total ? s_rows[(f / rec) * pitch + (f % rec)] : 0.f;
+        }
+        if (vec && i + 3 < total) *reinterpret_cast<float4*>(dst + i) = make_float4(v[0], v[1], v[2], v[3]);
+        else
+            for (int j = 0; j < 4 && i + j < total; ++j) dst[i + j] = v[j];
+    }
+}
+
 }  // namespace csb
