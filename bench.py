@@ -510,8 +510,85 @@ def run_b200(args, rank, world, dev):
         if rank == 0:
             line["gnn"]["train_c5"] = tr
             line["gnn"]["gpu_launches"] = int(lib.csb_launch_count() - l0)
+    if rank == 0 and not args.no_loss:
+        l0 = lib.csb_launch_count()
+        line["refine_tail"] = loss_adam_bench(dev, "b200", peaks, flush)
+        line["refine_tail"]["gpu_launches"] = int(lib.csb_launch_count() - l0)
     if rank == 0:
         print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+# Photometric loss + optimiser step of the refinement loop
+# ------------------------------------------------------------------------------------------
+def loss_adam_bench(dev, impl, peaks, flush, V=4, H=800, W=800, P=10108, iters=20):
+    """image_losses(fwd+bwd) on the C2 views and the 7-group Adam step over the C2 Gaussians.  impl 'b200': the fused
+    kernels through utils.loss_utils / csb_optim; impl 'reference': the reference's own torch op sequence
+    (utils/loss_utils.py via oracle/loss_oracle.py, torch.optim.Adam) on the same B200."""
+    rng = np.random.default_rng(5)
+    gt = rng.random((V, 3, H, W), dtype=np.float32)
+    img = np.clip(gt + 0.05 * rng.standard_normal(gt.shape).astype(np.float32), 0, 1)
+    x = torch.from_numpy(img).to(dev).requires_grad_(True)
+    y = torch.from_numpy(gt).to(dev)
+    shapes = {"face_bary": (P, 3), "face_offset": (P, 1), "f_dc": (P, 1, 3), "f_rest": (P, 15, 3), "opacity": (P, 1),
+              "scaling": (P, 3), "rotation": (P, 4)}
+    lrs = {"face_bary": 1.6e-4, "face_offset": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 1.25e-4, "opacity": 0.05,
+           "scaling": 5e-3, "rotation": 1e-3}
+    params = {k: torch.nn.Parameter(torch.from_numpy(rng.standard_normal(sh).astype(np.float32)).to(dev))
+              for k, sh in shapes.items()}
+    for k, p_ in params.items():
+        p_.grad = torch.from_numpy(rng.standard_normal(shapes[k]).astype(np.float32)).to(dev)
+    groups = [{"params": [params[k]], "lr": lrs[k], "name": k} for k in shapes]
+    if impl == "b200":
+        from csb_optim import Adam
+        from utils.loss_utils import image_loss
+
+        opt = Adam(groups, lr=0.0, eps=1e-15)
+
+        def loss_step():
+            x.grad = None
+            image_loss(x, y, 0.1)[0].backward()
+    else:
+        from oracle import loss_oracle
+
+        opt = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+
+        def loss_step():
+            x.grad = None
+            loss_oracle.image_losses(x, y, 0.1)[0].backward()
+
+    ms_loss, _ = _time_cuda(loss_step, iters, 3, flush)
+    ms_adam, _ = _time_cuda(opt.step, iters, 3, flush)
+    n = V * 3 * H * W
+    elems = sum(int(np.prod(sh)) for sh in shapes.values())
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    out = {"impl": impl,
+           "image_loss": {"shape": [V, 3, H, W], "lambda_dssim": 0.1, "ms_fwd_bwd": ms_loss,
+                          "mpix_per_s": V * H * W / 1e6 / (ms_loss * 1e-3)},
+           "adam": {"tensors": len(shapes), "elements": elems, "ms_per_step": ms_adam}}
+    if impl == "b200":
+        import csb_cabi
+
+        lib = csb_cabi.lib()
+        lib.csb_profile_enable(1)
+        for _ in range(5):
+            flush()
+            loss_step()
+            opt.step()
+        torch.cuda.synchronize()
+        prof = csb_cabi.profile_read()
+        lib.csb_profile_enable(0)
+        alg = {"image_loss_forward": 20.0 * n, "image_loss_backward": 24.0 * n, "adam_step": 28.0 * elems}
+        for k, b in alg.items():
+            if k in prof:
+                ms, cnt = prof[k]
+                ach = b / (ms / cnt * 1e-3) / 1e9
+                tgt = out["image_loss"] if k.startswith("image") else out["adam"]
+                tgt.setdefault("kernels", {})[k] = {
+                    "ms_per_launch": ms / cnt,
+                    "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                 "peak_source": "measured" if peaks else "fallback"}}
+    return out
 
 
 # ------------------------------------------------------------------------------------------
@@ -649,6 +726,13 @@ def run_reference(args, rank, world, dev):
         # steps of a 10-step rollout (~8 GB per graph-batch of 1), 128 graphs do not fit in 180 GB
         base["gnn"]["train_c5"] = gnn_train_bench(dev, "reference", peaks, args.gnn_ref_graphs, iters=3)
         base["gnn"]["train_c5"]["sample"] = f"{args.gnn_ref_graphs} of the 128 graphs a GPU owns in C5"
+    if not args.no_loss:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        base["refine_tail"] = loss_adam_bench(dev, "reference", peaks, flush)
     print(json.dumps(base), flush=True)
 
 
@@ -661,6 +745,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gnn", action="store_true")
+    ap.add_argument("--no-loss", action="store_true", help="skip the image-loss / Adam leg")
     ap.add_argument("--gnn-graphs", type=int, default=128, help="graphs per GPU of the C5 training leg")
     ap.add_argument("--gnn-ref-graphs", type=int, default=4, help="graphs of the reference arm's bounded sample")
     args = ap.parse_args()

@@ -170,6 +170,27 @@ class MultiGaussianMesh(torch.nn.Module):
         self._features_dc, self._features_rest = P(features_dc), P(features_rest)
         self._scaling, self._rotation, self._opacity = P(scaling), P(rotation), P(opacity)
 
+    def training_setup(self, training_args):
+        """The seven Adam groups of MultiGaussianMesh.training_setup (gaussian_mesh.py:121-135), same names, learning
+        rates and `torch.optim.Adam(l, lr=0.0, eps=1e-15)` settings, stepped by ONE multi-tensor launch
+        (csb_optim.Adam -> csb_adam_step).  Densification statistics and the xyz scheduler stay with the caller."""
+        from csb_optim import Adam
+
+        if not hasattr(self, "face_offset"):
+            self.face_offset = torch.nn.Parameter(torch.zeros((self.num_gaussians, 1), device=self.face_bary.device))
+        scale = getattr(self, "spatial_lr_scale", 1.0)
+        groups = [
+            {"params": [self.face_bary], "lr": training_args.position_lr_init * scale, "name": "face_bary"},
+            {"params": [self.face_offset], "lr": training_args.position_lr_init * scale, "name": "face_offset"},
+            {"params": [self._features_dc], "lr": training_args.feature_lr, "name": "f_dc"},
+            {"params": [self._features_rest], "lr": training_args.feature_lr / 20.0, "name": "f_rest"},
+            {"params": [self._opacity], "lr": training_args.opacity_lr, "name": "opacity"},
+            {"params": [self._scaling], "lr": training_args.scaling_lr, "name": "scaling"},
+            {"params": [self._rotation], "lr": training_args.rotation_lr, "name": "rotation"},
+        ]
+        self.optimizer = Adam(groups, lr=0.0, eps=1e-15)
+        return self.optimizer
+
     @property
     def num_gaussians(self):
         return self.face_ids.shape[0]

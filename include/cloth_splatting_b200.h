@@ -21,6 +21,8 @@
  *   csb_gnn_*               <- EncodeProcessDecode.forward           meshnet/graph_network.py:387-408
  *                              (PyG MessagePassing.propagate + torch addmm/layer_norm/scatter_add_)
  *   csb_mesh_xyz_*          <- MultiGaussianMesh.get_xyz             scene_reconstruction/gaussian_mesh.py:151-169
+ *   csb_image_loss_*        <- image_losses / l1_loss / ssim         scene_reconstruction/train_utils.py:50-74, utils/loss_utils.py:20-70
+ *   csb_adam_step           <- torch.optim.Adam(...).step()          scene_reconstruction/gaussian_mesh.py:121-135, train_utils.py:312-317
  */
 #ifndef CLOTH_SPLATTING_B200_H
 #define CLOTH_SPLATTING_B200_H
@@ -231,6 +233,52 @@ int csb_mesh_rotation_forward(int P, int Nv, int F, const float* rest_vertices, 
 int csb_mesh_rotation_backward(int P, int Nv, int F, const float* rest_vertices, const float* vertices,
                                const int64_t* face, const int64_t* face_ids, const float* rotation,
                                const float* dL_dout, float* dL_dvertices, float* dL_drotation, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Photometric loss
+ * ------------------------------------------------------------------------- */
+
+/* image_losses(image_tensor, gt_image_tensor, opt, mask_tensor)  (scene_reconstruction/train_utils.py:50-74):
+ *   loss = l1_loss(img, gt, mask) + lambda_dssim * ssim_loss,           utils/loss_utils.py:20-23
+ *   ssim_loss = 1 - ssim(img, gt)                (no mask)              utils/loss_utils.py:39-70
+ *             = ((1 - ssim_map) * mask).mean()   (mask)
+ * img, gt f32[n_img, C, H, W]; mask f32[n_img, mask_channels, H, W] or NULL, mask_channels 1 or C; the SSIM
+ * window is the reference's 11x11 Gaussian (sigma 1.5) with zero padding.  Outputs (all device):
+ *   losses   f32[3] = {loss, l1, ssim_loss}
+ *   ssim_map f32[n_img, C, H, W] or NULL          (ssim(..., return_map=True))
+ *   dmaps    f32[3, n_img, C, H, W] or NULL: per pixel dS/dmu1 (total), dS/dsigma1^2, dS/dsigma12 -- what
+ *            csb_image_loss_backward needs; NULL for an evaluation-only call.
+ * workspace: csb_image_loss_workspace_bytes(...) bytes (per-tile partial sums, folded in a fixed order). */
+size_t csb_image_loss_workspace_bytes(int n_img, int C, int H, int W);
+int csb_image_loss_forward(int n_img, int C, int H, int W, const float* img, const float* gt, const float* mask,
+                           int mask_channels, float lambda_dssim, float* ssim_map, float* dmaps, float* losses,
+                           void* workspace, size_t workspace_bytes, void* stream);
+/* dL/dimg f32[n_img, C, H, W] of  L = scale * (w_l1 * sum |(img - gt) mask| + sum_q g(q) S(q)),
+ *   g(q) = grad_map[q] if grad_map != NULL (autograd through a returned ssim_map) else w_ssim * mask(q);
+ * scale = *grad_scale, a DEVICE scalar (the upstream gradient of the loss; NULL = 1) so that no host
+ * synchronisation is needed.  image_losses: w_l1 = 1/count, w_ssim = -lambda_dssim/count, count = n_img*C*H*W. */
+int csb_image_loss_backward(int n_img, int C, int H, int W, const float* img, const float* gt, const float* mask,
+                            int mask_channels, const float* dmaps, const float* grad_map, const float* grad_scale,
+                            float w_ssim, float w_l1, float* dL_dimg, void* stream);
+
+/* ------------------------------------------------------------------------- *
+ * Optimiser step
+ * ------------------------------------------------------------------------- */
+
+/* torch.optim.Adam(param_groups, lr=0.0, eps=1e-15).step() over the parameter tensors of
+ * MultiGaussianMesh.training_setup (scene_reconstruction/gaussian_mesh.py:121-135, called at
+ * scene_reconstruction/train_utils.py:312-317) -- and of any other fp32 parameter list (the meshnet
+ * optimiser) -- in ONE launch per 48 tensors instead of ~8 elementwise launches per tensor:
+ *   m += (g - m)(1 - beta1);  v = beta2 v + (1 - beta2) g g
+ *   p -= (lr / (1 - beta1^t)) * m / (sqrt(v) / sqrt(1 - beta2^t) + eps)       (amsgrad off, weight decay 0)
+ * params/grads/exp_avg/exp_avg_sq: HOST arrays of n_tensors DEVICE pointers; numel, lr: host arrays (per
+ * tensor).  `step` is t after the increment (1 on the first call).  A NULL grads[i] skips tensor i, like a
+ * parameter whose .grad is None.  Scalars are doubles because torch derives step size and bias corrections in
+ * Python doubles before rounding to fp32.  If zero_grads != 0 the gradients are zeroed in passing
+ * (optimizer.zero_grad(set_to_none=False) fused). */
+int csb_adam_step(int n_tensors, float* const* params, float* const* grads, float* const* exp_avg,
+                  float* const* exp_avg_sq, const int64_t* numel, const double* lr, double beta1, double beta2,
+                  double eps, int step, int zero_grads, void* stream);
 
 #ifdef __cplusplus
 }
