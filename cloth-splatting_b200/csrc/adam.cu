@@ -3,7 +3,7 @@
 // Replaces torch.optim.Adam(l, lr=0.0, eps=1e-15).step() as set up by MultiGaussianMesh.training_setup
 // (scene_reconstruction/gaussian_mesh.py:121-135) and called at scene_reconstruction/train_utils.py:312-317:
 // per parameter tensor torch issues lerp_, mul_, addcmul_, sqrt, div, add_, addcdiv_ (7 groups -> ~50 launches,
-// 262 meshnet tensors -> ~1800).  Here one launch covers up to 48 tensors; a block owns 4096 consecutive elements of
+// 262 meshnet tensors -> ~1800).  Here one launch covers up to 48 tensors; a block owns 1024 consecutive elements of
 // one tensor.  HBM-bound: 16 B read (p, g, m, v) + 12 B written (+4 when the gradient is zeroed) per element.
 // Arithmetic follows torch/optim/adam.py:_single_tensor_adam operation by operation (fp32, scalars derived in
 // double on the host and rounded once).
@@ -12,7 +12,7 @@
 namespace csb {
 
 constexpr int ADAM_MAX_TENSORS = 48;
-constexpr int ADAM_BLOCK_ELEMS = 4096;
+constexpr int ADAM_BLOCK_ELEMS = 1024;
 
 struct AdamTable {
     float* p[ADAM_MAX_TENSORS];

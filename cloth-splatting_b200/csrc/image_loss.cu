@@ -24,7 +24,7 @@ namespace csb {
 constexpr int LT = 32;             // tile edge (outputs)
 constexpr int LR = 5;              // window radius (11 taps)
 constexpr int LH = LT + 2 * LR;    // 42: tile + halo
-constexpr int LP = 43;             // pitch of the halo tiles (conflict-free for the 4-wide horizontal groups)
+constexpr int LP = 43;             // pitch of the halo tiles in elements (odd: conflict-free 64-bit accesses, see below)
 constexpr int LG = 4;              // outputs per thread along the pass direction
 
 struct LossWindow {
@@ -38,123 +38,196 @@ struct LossShape {
     int tiles_x, tiles_y;
 };
 
-__device__ __forceinline__ float mask_at(const float* __restrict__ mask, const LossShape& s, int plane, int y, int x) {
-    if (!mask) return 1.f;
-    const int img = plane / s.C, c = plane - img * s.C;
-    const size_t mp = s.mask_c == 1 ? (size_t)img : (size_t)img * s.C + c;
-    return mask[(mp * s.H + y) * s.W + x];
+// Packed fp32x2 arithmetic of sm_100 (FFMA2 / FMUL2): one issue slot, two lanes.  The separable convolutions below
+// are almost pure FMA streams, so pairing (x, y), (x^2, y^2), (gA, gB) halves their instruction count.
+__device__ __forceinline__ float2 ffma2(float w, float2 b, float2 c) {
+    unsigned long long rw, rb, rc, rd;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(rw) : "f"(w));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(rw), "l"(rb), "l"(rc));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+    unsigned long long ra, rb, rd;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
 }
 
-// grid: x = tiles_x * tiles_y, y = planes.  256 threads.
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ const float* mask_plane(const float* __restrict__ mask, const LossShape& s, int plane) {
+    if (!mask) return nullptr;
+    const int img = plane / s.C;
+    const size_t mp = s.mask_c == 1 ? (size_t)img : (size_t)plane;
+    return mask + mp * s.H * s.W;
+}
+
+// Horizontal-pass work item of lane-linear index i: 4 rows x 4 column groups per half-warp, so that the 16 64-bit
+// shared-memory accesses of a half-warp fall into 16 distinct bank pairs (2 * LP * r mod 8 takes 0, 6, 4, 2).
+__device__ __forceinline__ void h_item(int i, int& r, int& cg) {
+    cg = ((i & 3) + ((i >> 2) & 4)) * LG;
+    r = ((i >> 2) & 3) + ((i >> 5) << 2);
+}
+constexpr int H_ITEMS = ((LH + 3) / 4) * 32;  // 352 slots, rows >= LH idle
+
+// grid: x = tiles_x * tiles_y, y = planes.  256 threads.  MAP / GRAD: ssim_map / dmaps are written.
+template <bool MAP, bool GRAD>
+__global__ void __launch_bounds__(256, 3)
 image_loss_forward_kernel(LossShape s, LossWindow win, const float* __restrict__ img, const float* __restrict__ gt,
                           const float* __restrict__ mask, float* __restrict__ ssim_map, float* __restrict__ dmaps,
                           float* __restrict__ partials) {
-    __shared__ float sx[LH * LP], sy[LH * LP];
-    __shared__ __align__(16) float hs[5][LH][LT];
+    __shared__ __align__(16) float2 sxy[LH * LP];       // (x - cx, y - cy)
+    __shared__ __align__(16) float2 h01[LH][LT];        // horizontal sums of (x, y)
+    __shared__ __align__(16) float2 h23[LH][LT];        // ... of (x^2, y^2)
+    __shared__ __align__(16) float h4[LH][LT];          // ... of x y
     __shared__ float red[2][8];
 
     const int plane = blockIdx.y;
     const int ty = blockIdx.x / s.tiles_x, tx = blockIdx.x - ty * s.tiles_x;
     const int x0 = tx * LT - LR, y0 = ty * LT - LR;
-    const size_t pbase = (size_t)plane * s.H * s.W;
-    const int tid = threadIdx.x;
+    const float* __restrict__ pimg = img + (size_t)plane * s.H * s.W;
+    const float* __restrict__ pgt = gt + (size_t)plane * s.H * s.W;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     // The moments are taken about the tile's centre values (cx, cy): variances and the covariance do not depend on
     // the origin, and E[x^2] - mu^2 about a nearby origin loses |x - cx|^2 / x^2 fewer bits to cancellation than
     // about 0 (exact zeros in flat regions, where the fp32 reference carries ~1e-7 / C2 = 1e-4 of noise).  Zero
     // padding is kept: a padded sample is the value 0, i.e. -cx after the shift.
     const int ccy = min(ty * LT + LT / 2, s.H - 1), ccx = min(tx * LT + LT / 2, s.W - 1);
-    const float cx = img[pbase + (size_t)ccy * s.W + ccx], cy = gt[pbase + (size_t)ccy * s.W + ccx];
-    for (int i = tid; i < LH * LH; i += 256) {
-        const int r = i / LH, c = i - r * LH;
-        const int gy = y0 + r, gx = x0 + c;
-        float a = 0.f, b = 0.f;
-        if (gy >= 0 && gy < s.H && gx >= 0 && gx < s.W) {
-            a = img[pbase + (size_t)gy * s.W + gx];
-            b = gt[pbase + (size_t)gy * s.W + gx];
+    const float cx = pimg[(size_t)ccy * s.W + ccx], cy = pgt[(size_t)ccy * s.W + ccx];
+    {
+        // every warp stages rows warp, warp + 8, ...: all global loads are issued before the first use so that one
+        // DRAM latency covers the whole tile instead of one per row
+        constexpr int NR = (LH + 7) / 8;
+        float va[NR][2], vb[NR][2];
+#pragma unroll
+        for (int j = 0; j < NR; ++j) {
+            const int r = warp + 8 * j, gy = y0 + r;
+            const bool rok = r < LH && gy >= 0 && gy < s.H;
+            const int rowoff = (rok ? gy : 0) * s.W;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int c = lane + 32 * h, gx = x0 + c;
+                const bool ok = rok && c < LH && gx >= 0 && gx < s.W;
+                va[j][h] = ok ? pimg[rowoff + gx] : 0.f;
+                vb[j][h] = ok ? pgt[rowoff + gx] : 0.f;
+            }
         }
-        sx[r * LP + c] = a - cx;
-        sy[r * LP + c] = b - cy;
+#pragma unroll
+        for (int j = 0; j < NR; ++j) {
+            const int r = warp + 8 * j;
+            if (r < LH) {
+                sxy[r * LP + lane] = make_float2(va[j][0] - cx, vb[j][0] - cy);
+                if (lane < LH - 32) sxy[r * LP + lane + 32] = make_float2(va[j][1] - cx, vb[j][1] - cy);
+            }
+        }
     }
     __syncthreads();
 
     // horizontal pass: item = (row, group of 4 columns)
-    for (int i = tid; i < LH * (LT / LG); i += 256) {
-        const int r = i >> 3, cg = (i & 7) * LG;
-        float vx[LG + 10], vy[LG + 10];
+    for (int i = tid; i < H_ITEMS; i += 256) {
+        int r, cg;
+        h_item(i, r, cg);
+        if (r >= LH) continue;
+        float2 v[LG + 10], sq[LG + 10];
+        float xy[LG + 10];
 #pragma unroll
         for (int k = 0; k < LG + 10; ++k) {
-            vx[k] = sx[r * LP + cg + k];
-            vy[k] = sy[r * LP + cg + k];
+            v[k] = sxy[r * LP + cg + k];
+            sq[k] = fmul2(v[k], v[k]);
+            xy[k] = v[k].x * v[k].y;
         }
-        float acc[5][LG];
+        float2 a01[LG], a23[LG];
+        float a4[LG];
 #pragma unroll
         for (int o = 0; o < LG; ++o) {
-#pragma unroll
-            for (int q = 0; q < 5; ++q) acc[q][o] = 0.f;
+            a01[o] = make_float2(0.f, 0.f);
+            a23[o] = make_float2(0.f, 0.f);
+            a4[o] = 0.f;
 #pragma unroll
             for (int k = 0; k < 11; ++k) {
-                const float a = vx[o + k], b = vy[o + k], w = win.w[k];
-                acc[0][o] = fmaf(w, a, acc[0][o]);
-                acc[1][o] = fmaf(w, b, acc[1][o]);
-                acc[2][o] = fmaf(w, a * a, acc[2][o]);
-                acc[3][o] = fmaf(w, b * b, acc[3][o]);
-                acc[4][o] = fmaf(w, a * b, acc[4][o]);
+                a01[o] = ffma2(win.w[k], v[o + k], a01[o]);
+                a23[o] = ffma2(win.w[k], sq[o + k], a23[o]);
+                a4[o] = fmaf(win.w[k], xy[o + k], a4[o]);
             }
         }
-#pragma unroll
-        for (int q = 0; q < 5; ++q)
-            *reinterpret_cast<float4*>(&hs[q][r][cg]) = make_float4(acc[q][0], acc[q][1], acc[q][2], acc[q][3]);
+        float4* d01 = reinterpret_cast<float4*>(&h01[r][cg]);
+        float4* d23 = reinterpret_cast<float4*>(&h23[r][cg]);
+        d01[0] = make_float4(a01[0].x, a01[0].y, a01[1].x, a01[1].y);
+        d01[1] = make_float4(a01[2].x, a01[2].y, a01[3].x, a01[3].y);
+        d23[0] = make_float4(a23[0].x, a23[0].y, a23[1].x, a23[1].y);
+        d23[1] = make_float4(a23[2].x, a23[2].y, a23[3].x, a23[3].y);
+        *reinterpret_cast<float4*>(&h4[r][cg]) = make_float4(a4[0], a4[1], a4[2], a4[3]);
     }
     __syncthreads();
 
     // vertical pass: thread = (column, group of 4 rows)
-    const int col = tid & 31, rg = (tid >> 5) * LG;
-    float out[5][LG];
+    const int col = lane, rg = warp * LG;
+    float2 o01[LG], o23[LG];
+    float o4[LG];
+    {
+        float2 v01[LG + 10], v23[LG + 10];
+        float v4[LG + 10];
 #pragma unroll
-    for (int q = 0; q < 5; ++q) {
-        float v[LG + 10];
-#pragma unroll
-        for (int k = 0; k < LG + 10; ++k) v[k] = hs[q][rg + k][col];
+        for (int k = 0; k < LG + 10; ++k) {
+            v01[k] = h01[rg + k][col];
+            v23[k] = h23[rg + k][col];
+            v4[k] = h4[rg + k][col];
+        }
 #pragma unroll
         for (int o = 0; o < LG; ++o) {
-            float a = 0.f;
+            o01[o] = make_float2(0.f, 0.f);
+            o23[o] = make_float2(0.f, 0.f);
+            o4[o] = 0.f;
 #pragma unroll
-            for (int k = 0; k < 11; ++k) a = fmaf(win.w[k], v[o + k], a);
-            out[q][o] = a;
+            for (int k = 0; k < 11; ++k) {
+                o01[o] = ffma2(win.w[k], v01[o + k], o01[o]);
+                o23[o] = ffma2(win.w[k], v23[o + k], o23[o]);
+                o4[o] = fmaf(win.w[k], v4[o + k], o4[o]);
+            }
         }
     }
 
     const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
     const size_t n = (size_t)s.planes * s.H * s.W;
+    const size_t pbase = (size_t)plane * s.H * s.W;
+    const float* __restrict__ pmask = mask_plane(mask, s, plane);
     float sum_l1 = 0.f, sum_ds = 0.f;
     const int gx = tx * LT + col;
+    if (gx < s.W) {
 #pragma unroll
-    for (int o = 0; o < LG; ++o) {
-        const int gy = ty * LT + rg + o;
-        if (gx < s.W && gy < s.H) {
-            const float a0 = out[0][o], a1 = out[1][o];
-            const float mu1 = cx + a0, mu2 = cy + a1;
-            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-            const float s1 = out[2][o] - a0 * a0, s2 = out[3][o] - a1 * a1, s12 = out[4][o] - a0 * a1;
-            const float N1 = 2.f * mu12 + C1, N2 = 2.f * s12 + C2;
-            const float D1 = mu1_sq + mu2_sq + C1, D2 = s1 + s2 + C2;
-            const float S = (N1 * N2) / (D1 * D2);
-            const size_t pix = pbase + (size_t)gy * s.W + gx;
-            const float m = mask_at(mask, s, plane, gy, gx);
-            const float xv = img[pix], yv = gt[pix];  // L1/L2 hits: the tile was just staged from these lines
-            sum_l1 += fabsf((xv - yv) * m);
-            sum_ds += (1.f - S) * m;
-            if (ssim_map) ssim_map[pix] = S;
-            if (dmaps) {
-                const float inv = 1.f / (D1 * D2);
-                const float dS_dmu1 = 2.f * N2 * inv * (mu2 - mu1 * N1 / D1);
-                const float dS_ds1 = -S / D2;
-                const float dS_ds12 = 2.f * N1 * inv;
-                dmaps[pix] = dS_dmu1 - 2.f * mu1 * dS_ds1 - mu2 * dS_ds12;
-                dmaps[n + pix] = dS_ds1;
-                dmaps[2 * n + pix] = dS_ds12;
+        for (int o = 0; o < LG; ++o) {
+            const int gy = ty * LT + rg + o;
+            if (gy < s.H) {
+                const float a0 = o01[o].x, a1 = o01[o].y;
+                const float mu1 = cx + a0, mu2 = cy + a1;
+                const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+                const float s1 = o23[o].x - a0 * a0, s2 = o23[o].y - a1 * a1, s12 = o4[o] - a0 * a1;
+                const float N1 = 2.f * mu12 + C1, N2 = 2.f * s12 + C2;
+                const float D1 = mu1_sq + mu2_sq + C1, D2 = s1 + s2 + C2;
+                const float inv = __fdividef(1.f, D1 * D2);  // D1 D2 >= C1 C2 = 9e-8: no range issue; 1 ulp
+                const float S = N1 * N2 * inv;
+                const size_t off = (size_t)gy * s.W + gx;
+                const float m = pmask ? pmask[off] : 1.f;
+                // (x - cx) - (y - cy) + (cx - cy) would round differently from the reference's x - y: re-read
+                const float xv = pimg[off], yv = pgt[off];  // L1 hits: the tile was just staged from these lines
+                sum_l1 += fabsf((xv - yv) * m);
+                sum_ds += (1.f - S) * m;
+                if (MAP) ssim_map[pbase + off] = S;
+                if (GRAD) {
+                    const float invD1 = D2 * inv, invD2 = D1 * inv;
+                    const float dS_dmu1 = 2.f * N2 * inv * (mu2 - mu1 * N1 * invD1);
+                    const float dS_ds1 = -S * invD2;
+                    const float dS_ds12 = 2.f * N1 * inv;
+                    dmaps[pbase + off] = dS_dmu1 - 2.f * mu1 * dS_ds1 - mu2 * dS_ds12;
+                    dmaps[n + pbase + off] = dS_ds1;
+                    dmaps[2 * n + pbase + off] = dS_ds12;
+                }
             }
         }
     }
@@ -164,9 +237,9 @@ image_loss_forward_kernel(LossShape s, LossWindow win, const float* __restrict__
         sum_l1 += __shfl_xor_sync(0xffffffffu, sum_l1, d);
         sum_ds += __shfl_xor_sync(0xffffffffu, sum_ds, d);
     }
-    if ((tid & 31) == 0) {
-        red[0][tid >> 5] = sum_l1;
-        red[1][tid >> 5] = sum_ds;
+    if (lane == 0) {
+        red[0][warp] = sum_l1;
+        red[1][warp] = sum_ds;
     }
     __syncthreads();
     if (tid == 0) {
@@ -189,8 +262,9 @@ image_loss_finalize_kernel(size_t blocks, double inv_count, float lambda, const 
     __shared__ double red[2][256];
     double a = 0.0, b = 0.0;
     for (size_t i = threadIdx.x; i < blocks; i += 256) {
-        a += (double)partials[2 * i];
-        b += (double)partials[2 * i + 1];
+        const float2 p = reinterpret_cast<const float2*>(partials)[i];
+        a += (double)p.x;
+        b += (double)p.y;
     }
     red[0][threadIdx.x] = a;
     red[1][threadIdx.x] = b;
@@ -212,89 +286,133 @@ image_loss_finalize_kernel(size_t blocks, double inv_count, float lambda, const 
 
 // dL/dimg.  g(q) = grad_map ? grad_map[q] : w_ssim * m(q) * scale,  L1 term l1w * m(p) * sign(x - y) * scale,
 // scale = *grad_scale (device scalar; NULL = 1).
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 image_loss_backward_kernel(LossShape s, LossWindow win, const float* __restrict__ img, const float* __restrict__ gt,
                            const float* __restrict__ mask, const float* __restrict__ dmaps,
                            const float* __restrict__ grad_map, const float* __restrict__ grad_scale, float w_ssim,
                            float w_l1, float* __restrict__ dimg) {
-    __shared__ float sa[3][LH * LP];
-    __shared__ __align__(16) float hs[3][LH][LT];
+    __shared__ __align__(16) float2 sab[LH * LP];   // (g A, g B)
+    __shared__ float sc[LH * LP];                   // g C
+    __shared__ __align__(16) float2 hab[LH][LT];
+    __shared__ __align__(16) float hc[LH][LT];
 
     const int plane = blockIdx.y;
     const int ty = blockIdx.x / s.tiles_x, tx = blockIdx.x - ty * s.tiles_x;
     const int x0 = tx * LT - LR, y0 = ty * LT - LR;
     const size_t pbase = (size_t)plane * s.H * s.W;
     const size_t n = (size_t)s.planes * s.H * s.W;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const float scale = grad_scale ? *grad_scale : 1.f;
     const float ws = w_ssim * scale;
+    const float* __restrict__ pmask = mask_plane(mask, s, plane);
+    const float* __restrict__ pA = dmaps + pbase;
+    const float* __restrict__ pB = dmaps + n + pbase;
+    const float* __restrict__ pC = dmaps + 2 * n + pbase;
+    const float* __restrict__ pG = grad_map ? grad_map + pbase : nullptr;
 
-    for (int i = tid; i < LH * LH; i += 256) {
-        const int r = i / LH, c = i - r * LH;
-        const int gy = y0 + r, gx = x0 + c;
-        float a = 0.f, b = 0.f, cc = 0.f;
-        if (gy >= 0 && gy < s.H && gx >= 0 && gx < s.W) {
-            const size_t pix = pbase + (size_t)gy * s.W + gx;
-            const float g = grad_map ? grad_map[pix] : ws * mask_at(mask, s, plane, gy, gx);
-            a = g * dmaps[pix];
-            b = g * dmaps[n + pix];
-            cc = g * dmaps[2 * n + pix];
-        }
-        sa[0][r * LP + c] = a;
-        sa[1][r * LP + c] = b;
-        sa[2][r * LP + c] = cc;
-    }
-    __syncthreads();
-
-    for (int i = tid; i < LH * (LT / LG); i += 256) {
-        const int r = i >> 3, cg = (i & 7) * LG;
+    {
+        constexpr int NR = (LH + 7) / 8;
+        float va[NR][2], vb[NR][2], vc[NR][2], vg[NR][2];
 #pragma unroll
-        for (int q = 0; q < 3; ++q) {
-            float v[LG + 10];
+        for (int j = 0; j < NR; ++j) {
+            const int r = warp + 8 * j, gy = y0 + r;
+            const bool rok = r < LH && gy >= 0 && gy < s.H;
+            const int rowoff = (rok ? gy : 0) * s.W;
 #pragma unroll
-            for (int k = 0; k < LG + 10; ++k) v[k] = sa[q][r * LP + cg + k];
-            float acc[LG];
-#pragma unroll
-            for (int o = 0; o < LG; ++o) {
-                acc[o] = 0.f;
-#pragma unroll
-                for (int k = 0; k < 11; ++k) acc[o] = fmaf(win.w[k], v[o + k], acc[o]);
+            for (int h = 0; h < 2; ++h) {
+                const int c = lane + 32 * h, gx = x0 + c;
+                const bool ok = rok && c < LH && gx >= 0 && gx < s.W;
+                const int off = ok ? rowoff + gx : 0;
+                va[j][h] = ok ? pA[off] : 0.f;
+                vb[j][h] = ok ? pB[off] : 0.f;
+                vc[j][h] = ok ? pC[off] : 0.f;
+                vg[j][h] = !ok ? 0.f : (pG ? pG[off] : (pmask ? ws * pmask[off] : ws));
             }
-            *reinterpret_cast<float4*>(&hs[q][r][cg]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        }
+#pragma unroll
+        for (int j = 0; j < NR; ++j) {
+            const int r = warp + 8 * j;
+            if (r < LH) {
+                sab[r * LP + lane] = make_float2(vg[j][0] * va[j][0], vg[j][0] * vb[j][0]);
+                sc[r * LP + lane] = vg[j][0] * vc[j][0];
+                if (lane < LH - 32) {
+                    sab[r * LP + lane + 32] = make_float2(vg[j][1] * va[j][1], vg[j][1] * vb[j][1]);
+                    sc[r * LP + lane + 32] = vg[j][1] * vc[j][1];
+                }
+            }
         }
     }
     __syncthreads();
 
-    const int col = tid & 31, rg = (tid >> 5) * LG;
-    float out[3][LG];
+    for (int i = tid; i < H_ITEMS; i += 256) {
+        int r, cg;
+        h_item(i, r, cg);
+        if (r >= LH) continue;
+        float2 v[LG + 10];
+        float u[LG + 10];
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
-        float v[LG + 10];
-#pragma unroll
-        for (int k = 0; k < LG + 10; ++k) v[k] = hs[q][rg + k][col];
+        for (int k = 0; k < LG + 10; ++k) {
+            v[k] = sab[r * LP + cg + k];
+            u[k] = sc[r * LP + cg + k];
+        }
+        float2 aab[LG];
+        float ac[LG];
 #pragma unroll
         for (int o = 0; o < LG; ++o) {
-            float a = 0.f;
+            aab[o] = make_float2(0.f, 0.f);
+            ac[o] = 0.f;
 #pragma unroll
-            for (int k = 0; k < 11; ++k) a = fmaf(win.w[k], v[o + k], a);
-            out[q][o] = a;
+            for (int k = 0; k < 11; ++k) {
+                aab[o] = ffma2(win.w[k], v[o + k], aab[o]);
+                ac[o] = fmaf(win.w[k], u[o + k], ac[o]);
+            }
+        }
+        float4* dab = reinterpret_cast<float4*>(&hab[r][cg]);
+        dab[0] = make_float4(aab[0].x, aab[0].y, aab[1].x, aab[1].y);
+        dab[1] = make_float4(aab[2].x, aab[2].y, aab[3].x, aab[3].y);
+        *reinterpret_cast<float4*>(&hc[r][cg]) = make_float4(ac[0], ac[1], ac[2], ac[3]);
+    }
+    __syncthreads();
+
+    const int col = lane, rg = warp * LG;
+    float2 oab[LG];
+    float oc[LG];
+    {
+        float2 v[LG + 10];
+        float u[LG + 10];
+#pragma unroll
+        for (int k = 0; k < LG + 10; ++k) {
+            v[k] = hab[rg + k][col];
+            u[k] = hc[rg + k][col];
+        }
+#pragma unroll
+        for (int o = 0; o < LG; ++o) {
+            oab[o] = make_float2(0.f, 0.f);
+            oc[o] = 0.f;
+#pragma unroll
+            for (int k = 0; k < 11; ++k) {
+                oab[o] = ffma2(win.w[k], v[o + k], oab[o]);
+                oc[o] = fmaf(win.w[k], u[o + k], oc[o]);
+            }
         }
     }
     const int gx = tx * LT + col;
     const float l1w = w_l1 * scale;
+    if (gx < s.W) {
 #pragma unroll
-    for (int o = 0; o < LG; ++o) {
-        const int gy = ty * LT + rg + o;
-        if (gx < s.W && gy < s.H) {
-            const size_t pix = pbase + (size_t)gy * s.W + gx;
-            const float xv = img[pix], yv = gt[pix];
-            float g = out[0][o] + 2.f * xv * out[1][o] + yv * out[2][o];
-            if (l1w != 0.f) {
-                const float m = mask_at(mask, s, plane, gy, gx);
-                const float d = (xv - yv) * m;
-                g += l1w * m * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));
+        for (int o = 0; o < LG; ++o) {
+            const int gy = ty * LT + rg + o;
+            if (gy < s.H) {
+                const size_t off = (size_t)gy * s.W + gx;
+                const float xv = img[pbase + off], yv = gt[pbase + off];
+                float g = oab[o].x + 2.f * xv * oab[o].y + yv * oc[o];
+                if (l1w != 0.f) {
+                    const float m = pmask ? pmask[off] : 1.f;
+                    const float d = (xv - yv) * m;
+                    g += l1w * m * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));
+                }
+                dimg[pbase + off] = g;
             }
-            dimg[pix] = g;
         }
     }
 }
@@ -352,7 +470,9 @@ int csb_image_loss_forward(int n_img, int C, int H, int W, const float* img, con
     cudaStream_t stream = (cudaStream_t)stream_;
     const dim3 grid(s.tiles_x * s.tiles_y, s.planes);
     const LossWindow win = make_window();
-    CSB_LAUNCH("image_loss_forward", stream, image_loss_forward_kernel<<<grid, 256, 0, stream>>>(
+    auto kernel = ssim_map ? (dmaps ? image_loss_forward_kernel<true, true> : image_loss_forward_kernel<true, false>)
+                           : (dmaps ? image_loss_forward_kernel<false, true> : image_loss_forward_kernel<false, false>);
+    CSB_LAUNCH("image_loss_forward", stream, kernel<<<grid, 256, 0, stream>>>(
         s, win, img, gt, mask, ssim_map, dmaps, (float*)workspace));
     const size_t blocks = (size_t)grid.x * grid.y;
     const double inv_count = 1.0 / ((double)s.planes * H * W);

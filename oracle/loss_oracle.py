@@ -26,7 +26,7 @@ def create_window(window_size, channel, dtype=torch.float32):
 
 def ssim_map(img1, img2, window_size=11):
     channel = img1.size(-3)
-    window = create_window(window_size, channel, img1.dtype)
+    window = create_window(window_size, channel, img1.dtype).to(img1.device)
     pad = window_size // 2
     mu1 = F.conv2d(img1, window, padding=pad, groups=channel)
     mu2 = F.conv2d(img2, window, padding=pad, groups=channel)
