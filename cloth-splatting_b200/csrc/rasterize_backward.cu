@@ -97,7 +97,10 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
         (a) = kp_ + __shfl_xor_sync(0xFFFFFFFFu, snd_, (o));            \
     }
 
-    const uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd), a_id = smem_addr(s_id);
+    // opaque: keeps the shared-window addresses in registers instead of rematerialising them (S2R SR_CgaCtaId + LEA)
+    // at each of their uses inside the divergent loop
+    uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd), a_id = smem_addr(s_id);
+    asm volatile("" : "+r"(a_xy), "+r"(a_co), "+r"(a_cd), "+r"(a_id));
     const int rounds = (int)((used + BW_BATCH - 1) / BW_BATCH);
     int todo = (int)used;
     for (int r = 0; r < rounds; ++r, todo -= BW_BATCH) {
@@ -141,8 +144,8 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
             float g_mx = 0.f, g_my = 0.f, g_cx = 0.f, g_cy = 0.f, g_cw = 0.f, g_op = 0.f;
             float g_c0 = 0.f, g_c1 = 0.f, g_c2 = 0.f;
             if (valid) {
-                // one correctly rounded reciprocal serves T / (1 - alpha) and T_final / (1 - alpha)
-                const float inv_1ma = __frcp_rn(1.f - alpha);
+                // one SFU reciprocal (1 ulp; 1 - alpha is in [0.01, 1]) serves T / (1 - alpha) and T_final / (1 - alpha)
+                const float inv_1ma = __fdividef(1.f, 1.f - alpha);
                 T = T * inv_1ma;
                 const float dchannel_dcolor = alpha * T;
                 const float4 cd = lds_f4(a_cd + (uint32_t)j * 16u);

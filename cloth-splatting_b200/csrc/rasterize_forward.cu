@@ -437,9 +437,12 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
     bool done = !inside;
     float T = 1.0f;
     uint32_t last_contributor = 0;
-    float C0 = 0.f, C1 = 0.f, C2 = 0.f, Dacc = 0.f;
+    float2 C01 = make_float2(0.f, 0.f), C2D = make_float2(0.f, 0.f);  // (C0, C1), (C2, depth)
 
-    const uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd);
+    // shared-window addresses, made opaque so that they stay in registers: otherwise the compiler rematerialises
+    // them (S2R SR_CgaCtaId + LEA, ~8 instructions) in every iteration of the divergent inner loop
+    uint32_t a_xy = smem_addr(s_xy), a_co = smem_addr(s_co), a_cd = smem_addr(s_cd);
+    asm volatile("" : "+r"(a_xy), "+r"(a_co), "+r"(a_cd));
     for (int r = 0; r < rounds; ++r, todo -= RENDER_BATCH) {
         if (__syncthreads_count(done) == CSB_TILE_PIX) break;
         const int progress = r * RENDER_BATCH + tid;
@@ -467,6 +470,9 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
                 const float4 con_o = lds_f4(a_co + (uint32_t)j * 16u);
                 const float power = -0.5f * (con_o.x * dx * dx + con_o.z * dy * dy) - con_o.y * dx * dy;
                 if (power > 0.0f) continue;
+                // expf as in the reference (forward.cu:336): an SFU ex2 would be 7 instructions shorter, but alpha decides
+                // the 1/255 and T < 1e-4 cut-offs, and a flipped decision moves a pixel by up to 4e-3 (measured: a
+                // handful of pixels of a 1920x1080 frame) -- parity with the reference's decisions comes first
                 const float alpha = fminf(0.99f, con_o.w * expf(power));
                 if (alpha < 1.0f / 255.0f) continue;
                 const float test_T = T * (1 - alpha);
@@ -475,10 +481,9 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
                     continue;
                 }
                 const float4 cd = lds_f4(a_cd + (uint32_t)j * 16u);
-                C0 += cd.x * alpha * T;
-                C1 += cd.y * alpha * T;
-                C2 += cd.z * alpha * T;
-                Dacc += cd.w * alpha * T;
+                // (c * alpha) * T + C, two channels per packed instruction (same roundings as the scalar form)
+                C01 = ffma2_bcast(T, fmul2_bcast(alpha, make_float2(cd.x, cd.y)), C01);
+                C2D = ffma2_bcast(T, fmul2_bcast(alpha, make_float2(cd.z, cd.w)), C2D);
                 T = test_T;
                 last_contributor = base + (uint32_t)j + 1u;  // 1-based list position, skipped entries count
             }
@@ -491,10 +496,10 @@ render_forward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, cons
         const float* __restrict__ bg = vb.background[v];
         final_T[v * hw + pix] = T;
         n_contrib[v * hw + pix] = last_contributor;
-        out_color[(v * 3 + 0) * hw + pix] = C0 + T * bg[0];
-        out_color[(v * 3 + 1) * hw + pix] = C1 + T * bg[1];
-        out_color[(v * 3 + 2) * hw + pix] = C2 + T * bg[2];
-        out_depth[v * hw + pix] = Dacc;
+        out_color[(v * 3 + 0) * hw + pix] = C01.x + T * bg[0];
+        out_color[(v * 3 + 1) * hw + pix] = C01.y + T * bg[1];
+        out_color[(v * 3 + 2) * hw + pix] = C2D.x + T * bg[2];
+        out_depth[v * hw + pix] = C2D.y;
     }
 }
 

@@ -179,6 +179,26 @@ __device__ __forceinline__ float exp2f_fast(float x) {
 }
 // Shared-memory loads through a 32-bit shared-window address computed once per kernel: indexing a __shared__
 // array makes the compiler rebuild the window base (S2R SR_CgaCtaId + MOV + LEA ...) at every use in the hot loops.
+// Packed fp32x2 arithmetic of sm_100 (FFMA2 / FMUL2): IEEE round-to-nearest per lane, one issue slot for two lanes.
+__device__ __forceinline__ float2 ffma2_bcast(float w, float2 b, float2 c) {
+    unsigned long long rw, rb, rc, rd;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(rw) : "f"(w));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rc) : "f"(c.x), "f"(c.y));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(rw), "l"(rb), "l"(rc));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
+__device__ __forceinline__ float2 fmul2_bcast(float w, float2 b) {
+    unsigned long long rw, rb, rd;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(rw) : "f"(w));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b.x), "f"(b.y));
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(rw), "l"(rb));
+    float2 d;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(rd));
+    return d;
+}
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ float2 lds_f2(uint32_t a) {
     float2 v;
