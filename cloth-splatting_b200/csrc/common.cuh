@@ -1,6 +1,7 @@
 // Shared helpers for the sm_100a kernels of the cloth-splatting hot path.
 #pragma once
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <stdint.h>
 #include <stddef.h>
 #include "../../include/cloth_splatting_b200.h"
@@ -165,8 +166,18 @@ enum {
 // n is read from the device (n_dev), n_max bounds the grid.  Buffers ping-pong; the
 // *side_out tells which side holds the result (0 = *_a, 1 = *_b); returns 0 or an error code.
 #define CSB_SORT_TILE 4096
+#define CSB_SORT_TILE_SMALL 1024
+// Pairs per thread block of a pass: inputs that would not fill the 148 SMs with 4096-pair tiles (the per-view depth
+// sort and the tile sort of the cloth scenes) use 1024-pair tiles -- 4x the blocks, a quarter of the serial work each.
+static inline size_t sort_tile_size(size_t n_max) {
+    return n_max < (size_t)148 * CSB_SORT_TILE ? CSB_SORT_TILE_SMALL : CSB_SORT_TILE;
+}
 static inline size_t sort_lookback_words(size_t n_max, int passes) {
-    return (size_t)passes * ((n_max + CSB_SORT_TILE - 1) / CSB_SORT_TILE + 1) * 256;
+    // non-decreasing in n_max (workspace sizes are inverted by bisection, csb_rasterize_binning_capacity)
+    const size_t switch_at = (size_t)148 * CSB_SORT_TILE;
+    const size_t small = (std::min(n_max, switch_at) + CSB_SORT_TILE_SMALL - 1) / CSB_SORT_TILE_SMALL + 1;
+    const size_t large = (n_max + CSB_SORT_TILE - 1) / CSB_SORT_TILE + 1;
+    return (size_t)passes * std::max(small, large) * 256;
 }
 // Which buffer side (0 = *_a, 1 = *_b) holds the tile-sorted instance list.
 static inline int sorted_side(size_t total_tiles) {

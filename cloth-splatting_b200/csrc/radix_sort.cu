@@ -16,7 +16,6 @@ namespace csb {
 
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
-constexpr int SORT_ITEMS = CSB_SORT_TILE / SORT_THREADS;  // 16
 constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 
@@ -57,6 +56,7 @@ sort_histogram_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restr
 }
 
 // ---- one onesweep pass -------------------------------------------------------------
+template <int SORT_ITEMS>  // pairs per thread: 16 (4096-pair tiles) or 4 (1024-pair tiles, small inputs)
 __global__ void __launch_bounds__(SORT_THREADS, 3)
 sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
@@ -66,8 +66,9 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
     __shared__ uint32_t digit_start[RADIX];           // first slot of a digit inside the sorted tile
     __shared__ uint32_t global_base[RADIX];           // destination of the digit's run minus its first tile slot
     __shared__ uint32_t scan_tmp[SORT_WARPS];
-    __shared__ uint32_t s_keys[CSB_SORT_TILE];
-    __shared__ uint32_t s_vals[CSB_SORT_TILE];
+    constexpr int TILE = SORT_ITEMS * SORT_THREADS;
+    __shared__ uint32_t s_keys[TILE];
+    __shared__ uint32_t s_vals[TILE];
     __shared__ uint32_t s_tile;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -78,9 +79,9 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
     __syncthreads();
     const uint32_t tile = s_tile;
     const uint32_t n = *n_dev;
-    const size_t tile_start = (size_t)tile * CSB_SORT_TILE;
+    const size_t tile_start = (size_t)tile * TILE;
     if (tile_start >= n) return;
-    const uint32_t n_valid = (uint32_t)min((size_t)CSB_SORT_TILE, (size_t)n - tile_start);
+    const uint32_t n_valid = (uint32_t)min((size_t)TILE, (size_t)n - tile_start);
 
     // a pass in which every key has the same digit is the identity permutation: plain copy
     // (depth exponents and unused tile bits produce such passes)
@@ -96,7 +97,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
         }
     }
 
-    // warp-striped load: item i of lane l is element warp*512 + i*32 + l of the tile
+    // warp-striped load: item i of lane l is element warp*(32*SORT_ITEMS) + i*32 + l of the tile
     uint32_t key[SORT_ITEMS];
     uint16_t rank[SORT_ITEMS];
     const uint32_t wbase = warp * (SORT_ITEMS * 32) + lane;
@@ -222,7 +223,10 @@ int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint3
     const int passes = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
     *side_out = passes & 1;
     if (n_max == 0) { *side_out = 0; return 0; }
-    const size_t tiles = (n_max + CSB_SORT_TILE - 1) / CSB_SORT_TILE;
+    const size_t tile = sort_tile_size(n_max);
+    const size_t tiles = (n_max + tile - 1) / tile;
+    auto kernel = tile == CSB_SORT_TILE ? sort_onesweep_kernel<CSB_SORT_TILE / SORT_THREADS>
+                                        : sort_onesweep_kernel<CSB_SORT_TILE_SMALL / SORT_THREADS>;
     int hist_blocks = (int)((n_max + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
     if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
     if (hist_blocks < 1) hist_blocks = 1;
@@ -230,7 +234,7 @@ int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint3
         CSB_LAUNCH("sort_histogram", stream, sort_histogram_kernel<<<hist_blocks, SORT_THREADS, 0, stream>>>(keys_a, n_dev, passes, hist));
     uint32_t *kin = keys_a, *kout = keys_b, *vin = vals_a, *vout = vals_b;
     for (int p = 0; p < passes; ++p) {
-        CSB_LAUNCH("sort_onesweep", stream, launch_pdl(sort_onesweep_kernel, dim3((unsigned)tiles), dim3(SORT_THREADS), 0, stream, 
+        CSB_LAUNCH("sort_onesweep", stream, launch_pdl(kernel, dim3((unsigned)tiles), dim3(SORT_THREADS), 0, stream, 
             kin, kout, vin, vout, n_dev, p * RADIX_BITS, hist + p * RADIX, tickets + p,
             lookback + (size_t)p * (tiles + 1) * RADIX));
         uint32_t* t = kin; kin = kout; kout = t;

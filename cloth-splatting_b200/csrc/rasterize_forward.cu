@@ -246,7 +246,7 @@ constexpr uint64_t SCAN_VAL = (1ull << 62) - 1;
 __global__ void __launch_bounds__(256)
 emit_kernel(const ViewBatch vb, const uint32_t* __restrict__ order, GeomState g, uint64_t* __restrict__ scan_state,
             uint32_t* __restrict__ out_tiles, uint32_t* __restrict__ out_vals, size_t capacity,
-            uint32_t* __restrict__ num_rendered_out, int tile_passes) {
+            uint32_t* __restrict__ num_rendered_out, uint32_t* num_rendered_mapped, int tile_passes) {
     __shared__ uint32_t sh[3 * 256];  // digit histograms of the tile sort's passes
     __shared__ uint32_t s_block;
     __shared__ uint32_t s_warp_tot[8];
@@ -324,7 +324,14 @@ emit_kernel(const ViewBatch vb, const uint32_t* __restrict__ order, GeomState g,
                 const bool overflow = total > capacity;
                 g.control[CTRL_NUM_RENDERED] = overflow ? 0u : (uint32_t)total;  // n of the later stages
                 g.control[CTRL_OVERFLOW] = overflow ? 1u : 0u;
-                num_rendered_out[0] = (uint32_t)min(total, (uint64_t)0xFFFFFFFFull);
+                const uint32_t clamped = (uint32_t)min(total, (uint64_t)0xFFFFFFFEull);
+                num_rendered_out[0] = clamped;
+                if (num_rendered_mapped) {
+                    // pinned host word the caller polls: the count reaches the host while the tile sort and the
+                    // render kernel are still running, so the forward needs no stream synchronisation
+                    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(num_rendered_mapped), "r"(clamped) : "memory");
+                    __threadfence_system();
+                }
             }
         }
     }
@@ -584,6 +591,7 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
 
     const size_t n = (size_t)num_views * P;
     const size_t total_tiles = (size_t)num_views * vb.tiles;
+    const bool early_count = (flags & 2) && num_rendered_host && n > 0;
     CSB_CUDA_TRY(cudaMemsetAsync(g.control, 0, g.control_words * sizeof(uint32_t), stream));
     CSB_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, total_tiles * sizeof(uint2), stream));
     // all memsets first: the kernels behind them form one programmatic-dependent-launch chain
@@ -615,7 +623,8 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
         const int tile_passes = (higher_msb((uint32_t)total_tiles) + 7) / 8;
         const bool tile_hist_fused = tile_passes <= 3;  // emit_kernel keeps 3 x 256 bins
         CSB_LAUNCH("emit", stream, launch_pdl(emit_kernel, dim3(blocks), dim3(256), 0, stream, vb, order, g, (uint64_t*)scan_state, b.tiles_a, b.vals_a,
-                                                binning_capacity, num_rendered_dev, tile_hist_fused ? tile_passes : 0));
+                                                binning_capacity, num_rendered_dev, early_count ? num_rendered_host : nullptr,
+                                                tile_hist_fused ? tile_passes : 0));
         if (binning_capacity > 0) {
             const int tile_bits = higher_msb((uint32_t)total_tiles);
             int tside = 0;
@@ -642,7 +651,7 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
                                                                  g.rgb_depth, im.final_T, im.n_contrib, out_color,
                                                                  out_depth));
     }
-    if (num_rendered_host)
+    if (num_rendered_host && !early_count)
         CSB_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost,
                                      stream));
     return 0;

@@ -34,12 +34,36 @@ _PER_GAUSSIAN = 8
 _pinned_counter = {}
 
 
+_RING = 64
+_ring_next = {}
+
+
 def _pinned_word(device):
+    """One int32 word of a pinned (device-accessible) ring per device: calls in flight never share a word."""
     t = _pinned_counter.get(device)
     if t is None:
-        t = torch.zeros(1, dtype=torch.int32).pin_memory()
+        t = torch.zeros(_RING, dtype=torch.int32).pin_memory()
         _pinned_counter[device] = t
-    return t
+    i = _ring_next.get(device, 0)
+    _ring_next[device] = (i + 1) % _RING
+    return t[i:i + 1]
+
+
+def _await_count(word, stream):
+    """Spins on the pinned word the binning kernel writes (csb_rasterize_forward flags bit1).  The count arrives
+    while the tile sort / render kernels are still running, so the caller goes on enqueueing (the backward pass,
+    the loss) without ever draining the stream."""
+    spins = 0
+    while True:
+        v = int(word.item())
+        if v != -1:
+            return v & 0xFFFFFFFF
+        spins += 1
+        if spins % 2048 == 0 and stream.query():
+            v = int(word.item())  # the stream drained: the word is final
+            if v == -1:
+                raise RuntimeError("csb_rasterize_forward finished without reporting num_rendered")
+            return v & 0xFFFFFFFF
 
 
 def _f32c(t, name):
@@ -106,6 +130,7 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
     capacity = max(int(hint * 1.25) + 4096 if hint else 0, _PER_GAUSSIAN * V * P, _MIN_CAPACITY) if P else 0
     stream = _abi.current_stream_ptr()
     while True:
+        host_word.fill_(-1)
         nbytes = lib.csb_rasterize_binning_bytes(V, P, W, H, capacity)
         # canonical capacity of a buffer of that size: the backward pass recovers it from numel()
         capacity = lib.csb_rasterize_binning_capacity(V, P, W, H, nbytes)
@@ -115,11 +140,11 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
             _abi.ptr(scales), float(scale_modifier), _abi.ptr(rotations), _abi.ptr(cov3D_precomp), int(bool(prefiltered)),
             geom.data_ptr(), geom.numel(), img.data_ptr(), img.numel(), _abi.ptr(binning), binning.numel(), capacity,
             out_color.data_ptr(), out_depth.data_ptr(), radii.data_ptr() if P else None, counter.data_ptr(),
-            host_word.data_ptr(), flags, stream)
+            host_word.data_ptr(), flags | 2, stream)
         _abi.check(rc, "csb_rasterize_forward")
-        # one host sync per forward, at its end (the reference blocks in the middle, rasterizer_impl.cu:282)
-        torch.cuda.current_stream().synchronize()
-        rendered = int(host_word.item()) & 0xFFFFFFFF
+        # no stream synchronisation: the instance count is polled from pinned memory as soon as the binning
+        # kernel knows it (the reference blocks on a cudaMemcpy in the middle, rasterizer_impl.cu:282)
+        rendered = _await_count(host_word, torch.cuda.current_stream())
         if rendered <= capacity:
             break
         capacity = rendered + 4096  # grow and render again

@@ -97,7 +97,12 @@ size_t csb_rasterize_binning_capacity(int num_views, int P, int width, int heigh
  * workspace to csb_rasterize_binning_bytes(..., num_rendered) and call again
  * (the reference does the same resize after its blocking cudaMemcpy,
  * rasterizer_impl.cu:280-286).  flags: bit0 = also write the sorted u64
- * tile|depth keys (rasterizer_impl.cu:70-111 layout) for inspection. */
+ * tile|depth keys (rasterizer_impl.cu:70-111 layout) for inspection;
+ * bit1 = num_rendered_host is device-accessible pinned memory (cudaHostAlloc under UVA): the
+ * binning kernel stores the count (clamped to 0xFFFFFFFE) into it as soon as it is known --
+ * before the tile sort and the render kernel run -- and no copy is enqueued at the end.  A
+ * caller that pre-sets the word to 0xFFFFFFFF can poll it instead of synchronising the stream,
+ * and enqueue the backward pass while the forward is still rendering. */
 int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
                           const float* means3D, const float* shs, const float* colors_precomp,
                           const float* opacities, const float* scales, float scale_modifier,

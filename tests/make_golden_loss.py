@@ -104,7 +104,8 @@ def main():
         img, gt, mask = synth(seed, n, H, W, mc)
         r32 = run(g, img, gt, mask, lam, torch.float32)
         r64 = run(g, img, gt, mask, lam, torch.float64)
-        out = dict(img=img, gt=gt, lambda_dssim=np.float64(lam), loss=np.float64(r32["loss"]), l1=np.float64(r32["l1"]),
+        out = dict(ref_commit="KTH-RPL/cloth-splatting f7acc90: utils/loss_utils.py:20-70, "
+                              "scene_reconstruction/train_utils.py:50-74", img=img, gt=gt, lambda_dssim=np.float64(lam), loss=np.float64(r32["loss"]), l1=np.float64(r32["l1"]),
                    ssim_loss=np.float64(r32["ssim_loss"]), grad=r32["grad"].astype(np.float32),
                    ssim_map=r32["ssim_map"].astype(np.float32), loss64=np.float64(r64["loss"]),
                    grad64=r64["grad"].astype(np.float64), ssim_map64=r64["ssim_map"].astype(np.float64))
