@@ -475,8 +475,15 @@ def run_b200(args, rank, world, dev):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     ach = alg.get(top, 0.0) / (kernels[top]["ms_per_launch"] * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch of that kernel, from the committed ncu --set full
+    # capture of this same command (profiles/r1_traffic.json; not measured live: ncu replays kernels)
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))[args.workload].get(top)
+    except Exception:
+        pass
     roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                "traffic": traffic, "peak_source": "measured" if peaks else "fallback",
                 "note": "compositing kernels are FP32/SFU-issue bound, not HBM bound; see kernels{} and DESIGN.md"}
 
     line = {

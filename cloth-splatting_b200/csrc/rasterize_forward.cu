@@ -378,6 +378,205 @@ emit_kernel(const ViewBatch vb, const uint32_t* __restrict__ order, GeomState g,
 }
 
 // ----------------------------------------------------------------------------------
+// Per-tile binning for scenes with short tile lists (flags bit2): count -> scan -> fill -> per-tile sort.
+//
+// The global path above sorts V*P depth keys (4 radix passes), emits, and sorts the instances by tile (2-3 passes):
+// 7-8 launches whose cost for a cloth-sized scene (40 k entries, 270 k instances) is launch latency, not traffic.
+// Here every (view, Gaussian) entry counts itself into the tiles of its rectangle, one block scans the per-tile
+// counts into the final `ranges`, the entries are filled in arbitrary (atomic) order, and one block per tile sorts
+// its list by (depth bits, entry): keys are unique, so the result is the reference's order -- stable by depth, then by
+// Gaussian index (rasterizer_impl.cu:70-111, 304-309) -- bit for bit and independent of the atomics' order.
+// A tile list longer than TILE_SORT_MAX makes the scan kernel refuse (count word 0xFFFFFFFD): the caller falls back
+// to the global path.
+// ----------------------------------------------------------------------------------
+constexpr uint32_t TILE_SORT_MAX = 2048;
+constexpr uint32_t TILE_RANK_MAX = 256;  // lists up to here are rank-sorted (no barriers), longer ones bitonic
+constexpr uint32_t COUNT_REFUSED = 0xFFFFFFFDu;
+
+// Exclusive scan of the per-tile counts (ranges[t].y) by one block of 256 threads -> ranges[t] = (start, start); the
+// fill kernel then advances .y to the end of the run.  Publishes the instance count (device word, control word,
+// pinned host word).  Thread t owns a contiguous chunk; its loads are batched so that the chunk costs a few L2
+// round trips, not one per tile.
+__device__ void bin_scan_block(uint2* __restrict__ ranges, uint32_t n_tiles, size_t capacity,
+                               uint32_t* __restrict__ control, uint32_t* __restrict__ num_rendered_out,
+                               uint32_t* num_rendered_mapped, uint32_t* s_sum, uint32_t* s_max) {
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t per = (n_tiles + 255u) / 256u;
+    const uint32_t lo = min(tid * per, n_tiles), hi = min(lo + per, n_tiles);
+    uint32_t sum = 0, mx = 0;
+    for (uint32_t i = lo; i < hi; i += 8) {
+        uint32_t c[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) c[u] = (i + u < hi) ? __ldcg(&ranges[i + u].y) : 0u;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            sum += c[u];
+            mx = max(mx, c[u]);
+        }
+    }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= (uint32_t)o) incl += t;
+        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+    }
+    if (lane == 31) { s_sum[warp] = incl; s_max[warp] = mx; }
+    __syncthreads();
+    uint32_t base = 0, total = 0, gmax = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < 8; ++w) {
+        const uint32_t v = s_sum[w];
+        if (w < warp) base += v;
+        total += v;
+        gmax = max(gmax, s_max[w]);
+    }
+    const bool refused = gmax > TILE_SORT_MAX;
+    const bool overflow = (size_t)total > capacity;
+    if (tid == 0) {
+        control[CTRL_NUM_RENDERED] = (refused || overflow) ? 0u : total;
+        control[CTRL_OVERFLOW] = refused ? 2u : (overflow ? 1u : 0u);
+        const uint32_t word = refused ? COUNT_REFUSED : total;
+        num_rendered_out[0] = word;
+        if (num_rendered_mapped) {
+            asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(num_rendered_mapped), "r"(word) : "memory");
+            __threadfence_system();
+        }
+    }
+    uint32_t run = base + incl - sum;
+    const bool bad = refused || overflow;
+    for (uint32_t i = lo; i < hi; i += 8) {
+        uint32_t c[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) c[u] = (i + u < hi) ? __ldcg(&ranges[i + u].y) : 0u;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (i + u < hi) ranges[i + u] = bad ? make_uint2(0u, 0u) : make_uint2(run, run);
+            run += c[u];
+        }
+    }
+}
+
+// FILL = false: every (view, Gaussian) entry counts itself into the tiles of its rectangle; the last block to finish
+// scans the counts.  FILL = true: the same walk claims a slot per tile and stores (depth bits, entry) there.
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+bin_entries_kernel(const ViewBatch vb, GeomState g, uint2* __restrict__ ranges, uint32_t* __restrict__ fill_depth,
+                   uint32_t* __restrict__ fill_vals, size_t capacity, uint32_t* __restrict__ num_rendered_out,
+                   uint32_t* num_rendered_mapped) {
+    __shared__ uint32_t s_sum[8], s_max[8];
+    __shared__ uint32_t s_last;
+    grid_dep_wait();
+    grid_dep_launch();
+    if (FILL && g.control[CTRL_OVERFLOW]) return;
+    const size_t n = (size_t)vb.V * vb.P;
+    const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;
+    const uint32_t cnt = j < n ? g.tiles_touched[j] : 0u;
+    if (cnt) {
+        const uint4 rect = g.rects[j];
+        const uint32_t view = (uint32_t)(j / (size_t)vb.P);
+        const uint32_t first = view * (uint32_t)vb.tiles + rect.y * (uint32_t)vb.gx + rect.x;
+        const float inv_w = 1.0f / (float)rect.z;
+        // tile k of the rectangle (row-major); four slot claims in flight per round trip
+        for (uint32_t k = 0; k < cnt; k += 4) {
+            uint32_t t[4], slot[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t kk = min(k + u, cnt - 1);
+                const uint32_t ry = (uint32_t)(((float)kk + 0.5f) * inv_w);
+                t[u] = first + ry * (uint32_t)vb.gx + (kk - ry * rect.z);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (k + u < cnt) slot[u] = atomicAdd(&ranges[t[u]].y, 1u);
+            if (FILL) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (k + u < cnt) {
+                        fill_depth[slot[u]] = rect.w;
+                        fill_vals[slot[u]] = (uint32_t)j;
+                    }
+            }
+        }
+    }
+    if (!FILL) {
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicAdd(&g.control[CTRL_TICKET_SCAN], 1u) == gridDim.x - 1 ? 1u : 0u;
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            bin_scan_block(ranges, (uint32_t)vb.V * (uint32_t)vb.tiles, capacity, g.control, num_rendered_out,
+                           num_rendered_mapped, s_sum, s_max);
+        }
+    }
+}
+
+// Persistent blocks walk the tiles; each sorts its tile's (depth bits, entry) keys in shared memory: rank sort (no
+// barriers) for short lists, bitonic network for long ones.
+__global__ void __launch_bounds__(256)
+bin_sort_kernel(uint2* __restrict__ ranges, const uint32_t* __restrict__ control, uint32_t n_tiles,
+                const uint32_t* __restrict__ fill_depth, const uint32_t* __restrict__ fill_vals,
+                uint32_t* __restrict__ out_tiles, uint32_t* __restrict__ out_vals, uint64_t* __restrict__ keys_out) {
+    __shared__ uint64_t s_key[TILE_SORT_MAX];
+    grid_dep_wait();
+    grid_dep_launch();
+    if (control[CTRL_OVERFLOW]) return;
+    const uint32_t tid = threadIdx.x;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint2 rg = ranges[tile];
+        const uint32_t n = rg.y - rg.x;
+        if (n == 0) {
+            if (tid == 0 && rg.x != 0) ranges[tile] = make_uint2(0u, 0u);  // the reference leaves empty tiles at (0, 0)
+            continue;
+        }
+        __syncthreads();  // the previous tile's readers are done with s_key
+        if (n <= TILE_RANK_MAX) {
+            uint64_t mine = 0;
+            if (tid < n) {
+                mine = ((uint64_t)fill_depth[rg.x + tid] << 32) | fill_vals[rg.x + tid];
+                s_key[tid] = mine;
+            }
+            __syncthreads();
+            if (tid < n) {
+                uint32_t rank = 0;
+                for (uint32_t q = 0; q < n; ++q) rank += s_key[q] < mine ? 1u : 0u;  // keys are unique
+                out_vals[rg.x + rank] = (uint32_t)mine;
+                out_tiles[rg.x + rank] = tile;
+                if (keys_out) keys_out[rg.x + rank] = ((uint64_t)tile << 32) | (mine >> 32);
+            }
+            continue;
+        }
+        uint32_t m = 1;
+        while (m < n) m <<= 1;
+        for (uint32_t i = tid; i < m; i += 256)
+            s_key[i] = i < n ? ((uint64_t)fill_depth[rg.x + i] << 32) | fill_vals[rg.x + i] : ~0ull;
+        __syncthreads();
+        for (uint32_t k = 2; k <= m; k <<= 1) {
+            for (uint32_t jj = k >> 1; jj > 0; jj >>= 1) {
+                for (uint32_t i = tid; i < m; i += 256) {
+                    const uint32_t p = i ^ jj;
+                    if (p > i) {
+                        const uint64_t a = s_key[i], b = s_key[p];
+                        if ((a > b) == ((i & k) == 0)) {
+                            s_key[i] = b;
+                            s_key[p] = a;
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        for (uint32_t i = tid; i < n; i += 256) {
+            const uint64_t key = s_key[i];
+            out_vals[rg.x + i] = (uint32_t)key;
+            out_tiles[rg.x + i] = tile;
+            if (keys_out) keys_out[rg.x + i] = ((uint64_t)tile << 32) | (key >> 32);
+        }
+    }
+}
+
+// ----------------------------------------------------------------------------------
 // tile ranges (+ optional u64 keys) from the sorted tile ids
 // ----------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
@@ -595,7 +794,7 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
     CSB_CUDA_TRY(cudaMemsetAsync(g.control, 0, g.control_words * sizeof(uint32_t), stream));
     CSB_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, total_tiles * sizeof(uint2), stream));
     // all memsets first: the kernels behind them form one programmatic-dependent-launch chain
-    if (n > 0 && binning_capacity > 0)
+    if (n > 0 && binning_capacity > 0 && !(flags & 4))
         CSB_CUDA_TRY(cudaMemsetAsync(b.lookback, 0, b.lookback_words * sizeof(uint32_t), stream));
     dim3 tgrid(vb.gx, vb.gy, num_views);
     if (n > 0) {
@@ -611,6 +810,31 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
         }
         CSB_LAUNCH("preprocess", stream, launch_pdl(preprocess_kernel, dim3(blocks), dim3(256), stage_sh ? rec_smem : 0, stream, vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
                                                       shs, cov3D_precomp, colors_precomp, radii, g, stage_sh));
+        if ((flags & 4) && binning_capacity > 0) {
+            // short tile lists: count -> scan -> fill -> per-tile sort (see bin_entries_kernel)
+            if (total_tiles > 256u * 4096u) return CSB_ERR_UNSUPPORTED;
+            const bool side = sorted_side(total_tiles) != 0;
+            uint32_t* fill_d = side ? b.tiles_a : b.tiles_b;  // unsorted fill goes to the side the consumers do not read
+            uint32_t* fill_v = side ? b.vals_a : b.vals_b;
+            uint32_t* st = side ? b.tiles_b : b.tiles_a;
+            uint32_t* sv = side ? b.vals_b : b.vals_a;
+            uint32_t* mapped = early_count ? num_rendered_host : nullptr;
+            CSB_LAUNCH("bin_count", stream, launch_pdl(bin_entries_kernel<false>, dim3(blocks), dim3(256), 0, stream, vb, g, im.ranges, fill_d, fill_v,
+                                                        binning_capacity, num_rendered_dev, mapped));
+            CSB_LAUNCH("bin_fill", stream, launch_pdl(bin_entries_kernel<true>, dim3(blocks), dim3(256), 0, stream, vb, g, im.ranges, fill_d, fill_v,
+                                                       binning_capacity, num_rendered_dev, mapped));
+            const unsigned sblocks = (unsigned)std::min<size_t>(total_tiles, 148 * 8);
+            CSB_LAUNCH("bin_sort", stream, launch_pdl(bin_sort_kernel, dim3(sblocks), dim3(256), 0, stream, im.ranges, (const uint32_t*)g.control,
+                                                       (uint32_t)total_tiles, (const uint32_t*)fill_d, (const uint32_t*)fill_v, st, sv,
+                                                       (flags & 1) ? b.keys : nullptr));
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, sv, g.means2D, g.conic_opacity,
+                                                                     g.rgb_depth, im.final_T, im.n_contrib, out_color,
+                                                                     out_depth));
+            if (num_rendered_host && !early_count)
+                CSB_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                             stream));
+            return 0;
+        }
         // depth order of the (view, Gaussian) entries
         uint32_t* scan_state = g.control + CTRL_SCAN_STATE;
         uint32_t* depth_lookback = scan_state + 2 * (blocks + 1);

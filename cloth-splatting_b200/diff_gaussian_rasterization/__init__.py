@@ -35,6 +35,8 @@ _pinned_counter = {}
 
 
 _RING = 64
+_COUNT_REFUSED = 0xFFFFFFFD  # per-tile binning refused: a tile list exceeds the per-tile sort's shared memory
+_small_bins = {}
 _ring_next = {}
 
 
@@ -129,6 +131,11 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
     hint = _capacity_hint.get(key, 0)
     capacity = max(int(hint * 1.25) + 4096 if hint else 0, _PER_GAUSSIAN * V * P, _MIN_CAPACITY) if P else 0
     stream = _abi.current_stream_ptr()
+    # short tile lists (cloth-sized scenes) are binned per tile (count / scan / fill / per-tile sort: flags bit2) instead
+    # of going through the two global radix sorts; the library refuses when a tile list is too long and the global
+    # path takes over for this problem size from then on
+    n_tiles = V * ((W + 15) // 16) * ((H + 15) // 16)
+    small = _small_bins.get(key, n_tiles <= (1 << 20) and V * P <= (1 << 19)) and P > 0
     while True:
         host_word.fill_(-1)
         nbytes = lib.csb_rasterize_binning_bytes(V, P, W, H, capacity)
@@ -140,15 +147,20 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
             _abi.ptr(scales), float(scale_modifier), _abi.ptr(rotations), _abi.ptr(cov3D_precomp), int(bool(prefiltered)),
             geom.data_ptr(), geom.numel(), img.data_ptr(), img.numel(), _abi.ptr(binning), binning.numel(), capacity,
             out_color.data_ptr(), out_depth.data_ptr(), radii.data_ptr() if P else None, counter.data_ptr(),
-            host_word.data_ptr(), flags | 2, stream)
+            host_word.data_ptr(), flags | 2 | (4 if small else 0), stream)
         _abi.check(rc, "csb_rasterize_forward")
         # no stream synchronisation: the instance count is polled from pinned memory as soon as the binning
         # kernel knows it (the reference blocks on a cudaMemcpy in the middle, rasterizer_impl.cu:282)
         rendered = _await_count(host_word, torch.cuda.current_stream())
+        if small and rendered == _COUNT_REFUSED:
+            small = _small_bins[key] = False
+            continue
         if rendered <= capacity:
             break
         capacity = rendered + 4096  # grow and render again
     _capacity_hint[key] = rendered
+    if small and rendered > 96 * n_tiles:
+        _small_bins[key] = False  # long lists: the global sorts are faster from here on
     del keep
     return rendered, out_color, out_depth, radii, geom, binning, img
 

@@ -102,7 +102,11 @@ size_t csb_rasterize_binning_capacity(int num_views, int P, int width, int heigh
  * binning kernel stores the count (clamped to 0xFFFFFFFE) into it as soon as it is known --
  * before the tile sort and the render kernel run -- and no copy is enqueued at the end.  A
  * caller that pre-sets the word to 0xFFFFFFFF can poll it instead of synchronising the stream,
- * and enqueue the backward pass while the forward is still rendering. */
+ * and enqueue the backward pass while the forward is still rendering;
+ * bit2 = per-tile binning for scenes with short tile lists: instead of the depth sort / emission /
+ * tile sort (7-8 launches) the entries are counted into their tiles, scanned, filled and sorted per tile
+ * in shared memory (4 launches, same resulting order bit for bit).  If a tile holds more than 2048
+ * instances nothing is rendered and the count word reads 0xFFFFFFFD: call again without bit2. */
 int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
                           const float* means3D, const float* shs, const float* colors_precomp,
                           const float* opacities, const float* scales, float scale_modifier,

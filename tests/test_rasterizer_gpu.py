@@ -142,7 +142,10 @@ def _compare_with_reference(g, cam, sh_degree=3, bg=(1.0, 1.0, 1.0)):
         a = got[k][0] if k == "means2D" else got[k]
         rel = Hh.rel_err(a.cpu().numpy(), g_ref[k].cpu().numpy())
         spread = Hh.rel_err(g_ref2[k].cpu().numpy(), g_ref[k].cpu().numpy())
-        assert spread < 3e-4, f"reference run-to-run spread of grad {k}: {spread}"
+        # two runs of the reference differ by up to ~5e-4 on the intermediate dL/dcov3D (float atomics over heavily
+        # cancelling terms; measured 1.0e-4 .. 4.8e-4 over repeated runs): the spread is budget, capped so that a
+        # broken reference build cannot hide a real error
+        assert spread < 1e-3, f"reference run-to-run spread of grad {k}: {spread}"
         assert rel < _grad_tol(k) + 2 * spread, f"grad {k}: rel {rel} (reference vs itself: {spread})"
 
 
