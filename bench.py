@@ -346,6 +346,8 @@ def run_b200(args, rank, world, dev):
         d = dict(zip(("means3D", "scales", "rotations", "opacities", "shs"), grads))
         bucket.copy_(d) if len(view_batches) == 1 else bucket.add_(d)
 
+    bucket_views = bucket.as_dict()
+
     def device_step():
         """Device-resident step through the C-ABI wrapper layer (no autograd)."""
         if len(view_batches) > 1:
@@ -357,10 +359,13 @@ def run_b200(args, rank, world, dev):
                                      gd["shs"], 3, False)
             R, color, depth, radii, geom, binning, img = fwd
             R_total += R
+            # one launch set covers all views of the batch: its gradients go straight into the flat bucket
             gb = dgr._backward_views(vs, gd["means3D"], radii, e, gd["scales"], gd["rotations"], 1.0, e, H, W,
-                                     dl[b[0]:b[-1] + 1], gd["shs"], 3, geom, binning, img)
-            dm2, dcol, dop, dm3, dcov, dsh, dsc, drot = gb
-            pack((dm3, dsc, drot, dop, dsh))
+                                     dl[b[0]:b[-1] + 1], gd["shs"], 3, geom, binning, img,
+                                     out=bucket_views if len(view_batches) == 1 else None)
+            if len(view_batches) > 1:
+                dm2, dcol, dop, dm3, dcov, dsh, dsc, drot = gb
+                pack((dm3, dsc, drot, dop, dsh))
         bucket.all_reduce()
         return R_total
 

@@ -166,7 +166,10 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
 
 
 def _backward_views(views, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, image_height,
-                    image_width, dL_dout_color, sh, degree, geom, binning, img):
+                    image_width, dL_dout_color, sh, degree, geom, binning, img, out=None):
+    """`out`: optional dict of preallocated contiguous fp32 CUDA tensors ("means3D" [P,3], "scales" [P,3], "rotations"
+    [P,4], "opacities" [P,1], "shs" [P,M,3]) the kernels write these gradients into -- e.g. views of the flat
+    all-reduce bucket (csb_dist.FlatGradBucket), which saves the pack copies."""
     lib = _abi.lib()
     V = len(views)
     P = means3D.size(0)
@@ -181,14 +184,24 @@ def _backward_views(views, means3D, radii, colors, scales, rotations, scale_modi
     M = sh.size(1) if sh is not None else 0
     dL_dpix = _f32c(dL_dout_color, "dL_dout_color")
 
+    def _buf(name, shape):
+        t = out.get(name) if out else None
+        if t is None:
+            return torch.empty(shape, dtype=torch.float32, device=dev)
+        if tuple(t.shape) != tuple(shape) or t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
+            raise ValueError(f"out['{name}'] must be a contiguous float32 tensor of shape {tuple(shape)} on {dev}")
+        if t.data_ptr() % 16:
+            raise ValueError(f"out['{name}'] must be 16-byte aligned (the kernels use vector stores)")
+        return t
+
     dL_dmeans2D = torch.empty((V, P, 3), dtype=torch.float32, device=dev)
-    dL_dmeans3D = torch.empty((P, 3), dtype=torch.float32, device=dev)
+    dL_dmeans3D = _buf("means3D", (P, 3))
     dL_dcolors = torch.empty((P, 3), dtype=torch.float32, device=dev)
-    dL_dopacity = torch.empty((P, 1), dtype=torch.float32, device=dev)
+    dL_dopacity = _buf("opacities", (P, 1))
     dL_dcov3D = torch.empty((P, 6), dtype=torch.float32, device=dev)
-    dL_dsh = torch.empty((P, M, 3), dtype=torch.float32, device=dev)
-    dL_dscales = torch.empty((P, 3), dtype=torch.float32, device=dev)
-    dL_drotations = torch.empty((P, 4), dtype=torch.float32, device=dev)
+    dL_dsh = _buf("shs", (P, M, 3))
+    dL_dscales = _buf("scales", (P, 3))
+    dL_drotations = _buf("rotations", (P, 4))
     if P:
         arr, keep = _views_array(views)
         capacity = lib.csb_rasterize_binning_capacity(V, P, W, H, binning.numel())
