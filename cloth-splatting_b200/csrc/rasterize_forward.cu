@@ -393,122 +393,152 @@ constexpr uint32_t TILE_SORT_MAX = 2048;
 constexpr uint32_t TILE_RANK_MAX = 256;  // lists up to here are rank-sorted (no barriers), longer ones bitonic
 constexpr uint32_t COUNT_REFUSED = 0xFFFFFFFDu;
 
-// Exclusive scan of the per-tile counts (ranges[t].y) by one block of 256 threads -> ranges[t] = (start, start); the
-// fill kernel then advances .y to the end of the run.  Publishes the instance count (device word, control word,
-// pinned host word).  Thread t owns a contiguous chunk; its loads are batched so that the chunk costs a few L2
-// round trips, not one per tile.
-__device__ void bin_scan_block(uint2* __restrict__ ranges, uint32_t n_tiles, size_t capacity,
-                               uint32_t* __restrict__ control, uint32_t* __restrict__ num_rendered_out,
-                               uint32_t* num_rendered_mapped, uint32_t* s_sum, uint32_t* s_max) {
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t per = (n_tiles + 255u) / 256u;
-    const uint32_t lo = min(tid * per, n_tiles), hi = min(lo + per, n_tiles);
-    uint32_t sum = 0, mx = 0;
-    for (uint32_t i = lo; i < hi; i += 8) {
-        uint32_t c[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) c[u] = (i + u < hi) ? __ldcg(&ranges[i + u].y) : 0u;
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            sum += c[u];
-            mx = max(mx, c[u]);
-        }
-    }
-    uint32_t incl = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (lane >= (uint32_t)o) incl += t;
-        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
-    }
-    if (lane == 31) { s_sum[warp] = incl; s_max[warp] = mx; }
-    __syncthreads();
-    uint32_t base = 0, total = 0, gmax = 0;
-#pragma unroll
-    for (uint32_t w = 0; w < 8; ++w) {
-        const uint32_t v = s_sum[w];
-        if (w < warp) base += v;
-        total += v;
-        gmax = max(gmax, s_max[w]);
-    }
-    const bool refused = gmax > TILE_SORT_MAX;
-    const bool overflow = (size_t)total > capacity;
-    if (tid == 0) {
-        control[CTRL_NUM_RENDERED] = (refused || overflow) ? 0u : total;
-        control[CTRL_OVERFLOW] = refused ? 2u : (overflow ? 1u : 0u);
-        const uint32_t word = refused ? COUNT_REFUSED : total;
-        num_rendered_out[0] = word;
-        if (num_rendered_mapped) {
-            asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(num_rendered_mapped), "r"(word) : "memory");
-            __threadfence_system();
-        }
-    }
-    uint32_t run = base + incl - sum;
-    const bool bad = refused || overflow;
-    for (uint32_t i = lo; i < hi; i += 8) {
-        uint32_t c[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) c[u] = (i + u < hi) ? __ldcg(&ranges[i + u].y) : 0u;
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            if (i + u < hi) ranges[i + u] = bad ? make_uint2(0u, 0u) : make_uint2(run, run);
-            run += c[u];
-        }
-    }
-}
+// Control words of this path (the depth sort's tickets are free here).
+constexpr int CTRL_BIN_MAX = CTRL_TICKET_DEPTH + 1;     // longest tile list
+constexpr int CTRL_BIN_TICKET = CTRL_TICKET_DEPTH + 2;  // block ticket of bin_ranges_kernel
 
-// FILL = false: every (view, Gaussian) entry counts itself into the tiles of its rectangle; the last block to finish
-// scans the counts.  FILL = true: the same walk claims a slot per tile and stores (depth bits, entry) there.
+// FILL = false: every (view, Gaussian) entry counts itself into the tiles of its rectangle.  FILL = true: the same walk claims a slot per tile and stores
+// (depth bits, entry) there.
 template <bool FILL>
 __global__ void __launch_bounds__(256)
-bin_entries_kernel(const ViewBatch vb, GeomState g, uint2* __restrict__ ranges, uint32_t* __restrict__ fill_depth,
-                   uint32_t* __restrict__ fill_vals, size_t capacity, uint32_t* __restrict__ num_rendered_out,
-                   uint32_t* num_rendered_mapped) {
-    __shared__ uint32_t s_sum[8], s_max[8];
-    __shared__ uint32_t s_last;
+bin_entries_kernel(const ViewBatch vb, GeomState g, uint2* __restrict__ ranges, uint32_t* __restrict__ groups,
+                   uint32_t* __restrict__ fill_depth, uint32_t* __restrict__ fill_vals) {
     grid_dep_wait();
     grid_dep_launch();
     if (FILL && g.control[CTRL_OVERFLOW]) return;
     const size_t n = (size_t)vb.V * vb.P;
     const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;
     const uint32_t cnt = j < n ? g.tiles_touched[j] : 0u;
-    if (cnt) {
-        const uint4 rect = g.rects[j];
-        const uint32_t view = (uint32_t)(j / (size_t)vb.P);
-        const uint32_t first = view * (uint32_t)vb.tiles + rect.y * (uint32_t)vb.gx + rect.x;
-        const float inv_w = 1.0f / (float)rect.z;
-        // tile k of the rectangle (row-major); four slot claims in flight per round trip
-        for (uint32_t k = 0; k < cnt; k += 4) {
-            uint32_t t[4], slot[4];
+    if (!cnt) return;
+    const uint4 rect = g.rects[j];
+    const uint32_t view = (uint32_t)(j / (size_t)vb.P);
+    const uint32_t first = view * (uint32_t)vb.tiles + rect.y * (uint32_t)vb.gx + rect.x;
+    const float inv_w = 1.0f / (float)rect.z;
+    // tile k of the rectangle (row-major); four slot claims in flight per round trip
+    for (uint32_t k = 0; k < cnt; k += 4) {
+        uint32_t t[4], slot[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const uint32_t kk = min(k + u, cnt - 1);
-                const uint32_t ry = (uint32_t)(((float)kk + 0.5f) * inv_w);
-                t[u] = first + ry * (uint32_t)vb.gx + (kk - ry * rect.z);
-            }
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t kk = min(k + u, cnt - 1);
+            const uint32_t ry = (uint32_t)(((float)kk + 0.5f) * inv_w);
+            t[u] = first + ry * (uint32_t)vb.gx + (kk - ry * rect.z);
+        }
+        if (FILL) {
 #pragma unroll
             for (int u = 0; u < 4; ++u)
                 if (k + u < cnt) slot[u] = atomicAdd(&ranges[t[u]].y, 1u);
-            if (FILL) {
 #pragma unroll
-                for (int u = 0; u < 4; ++u)
-                    if (k + u < cnt) {
-                        fill_depth[slot[u]] = rect.w;
-                        fill_vals[slot[u]] = (uint32_t)j;
-                    }
+            for (int u = 0; u < 4; ++u)
+                if (k + u < cnt) {
+                    fill_depth[slot[u]] = rect.w;
+                    fill_vals[slot[u]] = (uint32_t)j;
+                }
+        } else {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (k + u < cnt) atomicAdd(&ranges[t[u]].y, 1u);
+        }
+    }
+}
+
+// Single-pass exclusive scan of the per-tile counts (chained scan with decoupled look-back, 256 tiles per block):
+// ranges[t] = (start, start); the fill kernel then advances .y to the end of the run.  The block holding the last
+// ticket ends up with the instance count and publishes it (device word, control word, pinned host word) -- or the
+// refusal, when a tile list is too long for the per-tile sort.
+constexpr uint32_t BS_AGG = 1u << 30, BS_INC = 2u << 30, BS_VAL = (1u << 30) - 1;
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(256)
+bin_ranges_kernel(uint2* __restrict__ ranges, uint32_t* __restrict__ status, uint32_t n_tiles, size_t capacity,
+                  uint32_t* __restrict__ control, uint32_t* __restrict__ num_rendered_out,
+                  uint32_t* num_rendered_mapped) {
+    __shared__ uint32_t s_warp[8];
+    __shared__ uint32_t s_blk, s_excl;
+    grid_dep_wait();
+    grid_dep_launch();
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_blk = atomicAdd(&control[CTRL_BIN_TICKET], 1u);
+    __syncthreads();
+    const uint32_t blk = s_blk;
+    const uint32_t t = blk * 256u + tid;
+    const uint32_t c = t < n_tiles ? __ldcg(&ranges[t].y) : 0u;
+    uint32_t incl = c, mx = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= (uint32_t)o) incl += v;
+        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    if (lane == 0 && mx > TILE_SORT_MAX) atomicMax(&control[CTRL_BIN_MAX], mx);
+    __syncthreads();
+    uint32_t warp_off = 0, block_tot = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < 8; ++w) {
+        if (w < warp) warp_off += s_warp[w];
+        block_tot += s_warp[w];
+    }
+    if (warp == 0) {
+        uint32_t excl = 0;
+        __threadfence();  // this block's atomicMax is visible before its status is
+        if (blk == 0) {
+            if (lane == 0) st_volatile_u32(&status[0], BS_INC | block_tot);
+        } else {
+            if (lane == 0) st_volatile_u32(&status[blk], BS_AGG | block_tot);
+            int pos = (int)blk - 1;
+            while (true) {
+                const int q = pos - (int)lane;
+                const uint32_t sv = q >= 0 ? ld_volatile_u32(&status[q]) : BS_INC;
+                const uint32_t ready = __ballot_sync(0xFFFFFFFFu, (sv & ~BS_VAL) != 0);
+                const uint32_t inc = __ballot_sync(0xFFFFFFFFu, (sv & ~BS_VAL) == BS_INC);
+                if (inc) {
+                    const int fi = __ffs(inc) - 1;  // nearest predecessor holding an inclusive prefix
+                    const uint32_t need = fi == 31 ? 0xFFFFFFFFu : ((1u << (fi + 1)) - 1);
+                    if ((ready & need) != need) continue;
+                    uint32_t part = (int)lane <= fi ? (sv & BS_VAL) : 0u;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
+                    excl += part;
+                    break;
+                }
+                if (ready != 0xFFFFFFFFu) continue;
+                uint32_t part = sv & BS_VAL;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
+                excl += part;
+                pos -= 32;
+            }
+            if (lane == 0) st_volatile_u32(&status[blk], BS_INC | (excl + block_tot));
+        }
+        if (lane == 0) {
+            s_excl = excl;
+            if (blk == gridDim.x - 1) {
+                __threadfence();
+                const uint32_t total = excl + block_tot;
+                const bool refused = __ldcg(&control[CTRL_BIN_MAX]) > TILE_SORT_MAX;
+                const bool overflow = (size_t)total > capacity;
+                control[CTRL_NUM_RENDERED] = (refused || overflow) ? 0u : total;
+                control[CTRL_OVERFLOW] = refused ? 2u : (overflow ? 1u : 0u);
+                const uint32_t word = refused ? COUNT_REFUSED : total;
+                num_rendered_out[0] = word;
+                if (num_rendered_mapped) {
+                    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(num_rendered_mapped), "r"(word) : "memory");
+                    __threadfence_system();
+                }
             }
         }
     }
-    if (!FILL) {
-        __threadfence();
-        __syncthreads();
-        if (threadIdx.x == 0) s_last = atomicAdd(&g.control[CTRL_TICKET_SCAN], 1u) == gridDim.x - 1 ? 1u : 0u;
-        __syncthreads();
-        if (s_last) {
-            __threadfence();
-            bin_scan_block(ranges, (uint32_t)vb.V * (uint32_t)vb.tiles, capacity, g.control, num_rendered_out,
-                           num_rendered_mapped, s_sum, s_max);
-        }
+    __syncthreads();
+    if (t < n_tiles) {
+        const uint32_t start = s_excl + warp_off + incl - c;
+        ranges[t] = make_uint2(start, start);
     }
 }
 
@@ -794,8 +824,12 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
     CSB_CUDA_TRY(cudaMemsetAsync(g.control, 0, g.control_words * sizeof(uint32_t), stream));
     CSB_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, total_tiles * sizeof(uint2), stream));
     // all memsets first: the kernels behind them form one programmatic-dependent-launch chain
-    if (n > 0 && binning_capacity > 0 && !(flags & 4))
-        CSB_CUDA_TRY(cudaMemsetAsync(b.lookback, 0, b.lookback_words * sizeof(uint32_t), stream));
+    if (n > 0 && binning_capacity > 0) {
+        // global path: look-back words of the tile sort; per-tile path (flags bit2): the status words of its scan
+        const size_t words = (flags & 4) ? (total_tiles + 255) / 256 : b.lookback_words;
+        if (words > b.lookback_words) return CSB_ERR_UNSUPPORTED;
+        CSB_CUDA_TRY(cudaMemsetAsync(b.lookback, 0, words * sizeof(uint32_t), stream));
+    }
     dim3 tgrid(vb.gx, vb.gy, num_views);
     if (n > 0) {
         const unsigned blocks = (unsigned)((n + 255) / 256);
@@ -819,10 +853,12 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             uint32_t* st = side ? b.tiles_b : b.tiles_a;
             uint32_t* sv = side ? b.vals_b : b.vals_a;
             uint32_t* mapped = early_count ? num_rendered_host : nullptr;
-            CSB_LAUNCH("bin_count", stream, launch_pdl(bin_entries_kernel<false>, dim3(blocks), dim3(256), 0, stream, vb, g, im.ranges, fill_d, fill_v,
-                                                        binning_capacity, num_rendered_dev, mapped));
-            CSB_LAUNCH("bin_fill", stream, launch_pdl(bin_entries_kernel<true>, dim3(blocks), dim3(256), 0, stream, vb, g, im.ranges, fill_d, fill_v,
-                                                       binning_capacity, num_rendered_dev, mapped));
+            const uint32_t sblocks_scan = (uint32_t)((total_tiles + 255) / 256);
+            uint32_t* groups = b.lookback;  // status words of the chained scan: free in this path; zeroed above
+            CSB_LAUNCH("bin_count", stream, launch_pdl(bin_entries_kernel<false>, dim3(blocks), dim3(256), 0, stream, vb, g, im.ranges, groups, fill_d, fill_v));
+            CSB_LAUNCH("bin_ranges", stream, launch_pdl(bin_ranges_kernel, dim3(sblocks_scan), dim3(256), 0, stream, im.ranges, groups,
+                                                         (uint32_t)total_tiles, binning_capacity, g.control, num_rendered_dev, mapped));
+            CSB_LAUNCH("bin_fill", stream, launch_pdl(bin_entries_kernel<true>, dim3(blocks), dim3(256), 0, stream, vb, g, im.ranges, groups, fill_d, fill_v));
             const unsigned sblocks = (unsigned)std::min<size_t>(total_tiles, 148 * 8);
             CSB_LAUNCH("bin_sort", stream, launch_pdl(bin_sort_kernel, dim3(sblocks), dim3(256), 0, stream, im.ranges, (const uint32_t*)g.control,
                                                        (uint32_t)total_tiles, (const uint32_t*)fill_d, (const uint32_t*)fill_v, st, sv,
