@@ -296,16 +296,22 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float* __res
     return dnormvdv3(dir_orig, dL_ddir);
 }
 
-// One Gaussian: `sh_row` = its SH record, `my_dsh` = where its dL/dsh record goes (both may live in shared memory).
-__device__ __forceinline__ void
-gaussian_backward_one(const int idx, const ViewBatch& vb, int D, int M, const float* __restrict__ means3D,
-                      const float* sh_row, const float* __restrict__ scales, float scale_modifier,
-                      const float* __restrict__ rotations, const float* __restrict__ cov3D_in,
-                      const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
-                      const float* __restrict__ grad_acc, float* __restrict__ dL_dmeans2D,
-                      float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
-                      float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D, float* my_dsh,
-                      float* __restrict__ dL_dscales, float* __restrict__ dL_drots) {
+// What the views of one Gaussian add up to (the sums over views of backward.cu's per-view kernels).
+struct GaussPartial {
+    float3 dmean;
+    float dcov[6];
+    float3 dcolor;
+    float dop;
+    bool any_visible;
+};
+
+// Views v_begin, v_begin + v_step, ... of one Gaussian: `sh_row` = its SH record, `my_dsh` = where this walk's dL/dsh
+// record goes (both may live in shared memory; zero-filled if no view saw the Gaussian).
+__device__ __forceinline__ GaussPartial
+gaussian_backward_views(const int idx, const int v_begin, const int v_step, const ViewBatch& vb, int D, int M,
+                        const float* __restrict__ means3D, const float* sh_row, const float* __restrict__ cov3D_in,
+                        const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
+                        const float* __restrict__ grad_acc, float* __restrict__ dL_dmeans2D, float* my_dsh) {
     const float3 mean = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
 
     float3 dmean_tot = make_float3(0.f, 0.f, 0.f);
@@ -314,7 +320,7 @@ gaussian_backward_one(const int idx, const ViewBatch& vb, int D, int M, const fl
     float dop_tot = 0.f;
     bool first_sh = true, any_visible = false;
 
-    for (int v = 0; v < vb.V; ++v) {
+    for (int v = v_begin; v < vb.V; v += v_step) {
         const size_t e = (size_t)v * vb.P + idx;
         float* m2d = dL_dmeans2D + e * 3;
         if (!(radii[e] > 0)) {
@@ -423,19 +429,37 @@ gaussian_backward_one(const int idx, const ViewBatch& vb, int D, int M, const fl
         dmean_tot.x += dmean.x; dmean_tot.y += dmean.y; dmean_tot.z += dmean.z;
     }
 
-    dL_dmeans3D[3 * idx + 0] = dmean_tot.x;
-    dL_dmeans3D[3 * idx + 1] = dmean_tot.y;
-    dL_dmeans3D[3 * idx + 2] = dmean_tot.z;
-    dL_dcolors[3 * idx + 0] = dcolor_tot.x;
-    dL_dcolors[3 * idx + 1] = dcolor_tot.y;
-    dL_dcolors[3 * idx + 2] = dcolor_tot.z;
-    dL_dopacity[idx] = dop_tot;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) dL_dcov3D[6 * (size_t)idx + i] = dcov_tot[i];
     if (my_dsh && first_sh)
         for (int k = 0; k < M * 3; ++k) my_dsh[k] = 0.f;
+    GaussPartial r;
+    r.dmean = dmean_tot;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) r.dcov[i] = dcov_tot[i];
+    r.dcolor = dcolor_tot;
+    r.dop = dop_tot;
+    r.any_visible = any_visible;
+    return r;
+}
 
-    // ---- cov3D -> scale, rotation (backward.cu:278-341); linear in dL_dcov3D, so done once ----
+// Writes the per-Gaussian outputs from the sum over views, then cov3D -> scale, rotation (backward.cu:278-341;
+// linear in dL_dcov3D, so done once).
+__device__ __forceinline__ void
+gaussian_backward_finish(const int idx, const GaussPartial& tot, const float* __restrict__ scales, float scale_modifier,
+                         const float* __restrict__ rotations, float* __restrict__ dL_dcolors,
+                         float* __restrict__ dL_dopacity, float* __restrict__ dL_dmeans3D,
+                         float* __restrict__ dL_dcov3D, float* __restrict__ dL_dscales, float* __restrict__ dL_drots) {
+    const float* dcov_tot = tot.dcov;
+    const bool any_visible = tot.any_visible;
+    dL_dmeans3D[3 * idx + 0] = tot.dmean.x;
+    dL_dmeans3D[3 * idx + 1] = tot.dmean.y;
+    dL_dmeans3D[3 * idx + 2] = tot.dmean.z;
+    dL_dcolors[3 * idx + 0] = tot.dcolor.x;
+    dL_dcolors[3 * idx + 1] = tot.dcolor.y;
+    dL_dcolors[3 * idx + 2] = tot.dcolor.z;
+    dL_dopacity[idx] = tot.dop;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) dL_dcov3D[6 * (size_t)idx + i] = dcov_tot[i];
+
     float3 dscale = make_float3(0.f, 0.f, 0.f);
     float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
     if (scales != nullptr && any_visible) {
@@ -511,17 +535,108 @@ gaussian_backward_kernel(const ViewBatch vb, int D, int M, const float* __restri
         else stage_records_in<0>(shs + (size_t)first * rec, s_rec, count, rec, tid, nthr);
         __syncthreads();
     }
-    if (idx < vb.P)
-        gaussian_backward_one(idx, vb, D, M, means3D,
-                              staged ? s_rec + tid * pitch : (shs ? shs + (size_t)idx * rec : nullptr), scales,
-                              scale_modifier, rotations, cov3D_in, radii, clamped, grad_acc, dL_dmeans2D, dL_dcolors,
-                              dL_dopacity, dL_dmeans3D, dL_dcov3D,
-                              staged ? s_rec + (nthr + tid) * pitch : (dL_dsh ? dL_dsh + (size_t)idx * rec : nullptr),
-                              dL_dscales, dL_drots);
+    if (idx < vb.P) {
+        const GaussPartial tot = gaussian_backward_views(
+            idx, 0, 1, vb, D, M, means3D, staged ? s_rec + tid * pitch : (shs ? shs + (size_t)idx * rec : nullptr),
+            cov3D_in, radii, clamped, grad_acc, dL_dmeans2D,
+            staged ? s_rec + (nthr + tid) * pitch : (dL_dsh ? dL_dsh + (size_t)idx * rec : nullptr));
+        gaussian_backward_finish(idx, tot, scales, scale_modifier, rotations, dL_dcolors, dL_dopacity, dL_dmeans3D,
+                                 dL_dcov3D, dL_dscales, dL_drots);
+    }
     if (staged) {
         __syncthreads();
         if (rec == 48) stage_records_out<48>(dL_dsh + (size_t)first * rec, s_rec + nthr * pitch, count, rec, tid, nthr);
         else stage_records_out<0>(dL_dsh + (size_t)first * rec, s_rec + nthr * pitch, count, rec, tid, nthr);
+    }
+}
+
+// Few Gaussians, several views (the cloth: 10 k Gaussians x 4 views): one thread per Gaussian leaves the GPU at 3 %
+// occupancy and the kernel is one thread's serial latency.  Here a block is 32 Gaussians x S view lanes (warp s walks
+// views s, s + S, ...); the lanes' partial sums and dL/dsh records meet in shared memory and are added in lane order
+// (deterministic), then warp 0 finishes the Gaussian.
+constexpr int GB_SPLIT_G = 32;
+constexpr int GB_PART = 14;  // dmean 3, dcov 6, dcolor 3, dop 1, any_visible 1
+
+__global__ void __launch_bounds__(GB_SPLIT_G * 8)
+gaussian_backward_split_kernel(const ViewBatch vb, int S, int D, int M, const float* __restrict__ means3D,
+                               const float* __restrict__ shs, const float* __restrict__ scales, float scale_modifier,
+                               const float* __restrict__ rotations, const float* __restrict__ cov3D_in,
+                               const int* __restrict__ radii, const uint8_t* __restrict__ clamped,
+                               const float* __restrict__ grad_acc, float* __restrict__ dL_dmeans2D,
+                               float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
+                               float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dcov3D,
+                               float* __restrict__ dL_dsh, float* __restrict__ dL_dscales,
+                               float* __restrict__ dL_drots) {
+    extern __shared__ float s_rec[];  // SH in [G][pitch] | dL/dsh [S][G][pitch] | partials [S][G][GB_PART]
+    grid_dep_wait();
+    grid_dep_launch();
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int gl = tid & (GB_SPLIT_G - 1), vl = tid / GB_SPLIT_G;
+    const int first = blockIdx.x * GB_SPLIT_G;
+    const int idx = first + gl;
+    const int rec = M * 3, pitch = rec + 1;
+    const int count = min(GB_SPLIT_G, vb.P - first);
+    const bool has_sh = shs != nullptr && dL_dsh != nullptr;
+    float* s_in = s_rec;
+    float* s_dsh = s_rec + (has_sh ? GB_SPLIT_G * pitch : 0);
+    float* s_part = s_dsh + (has_sh ? S * GB_SPLIT_G * pitch : 0);
+    if (has_sh) {
+        if (rec == 48) stage_records_in<48>(shs + (size_t)first * rec, s_in, count, rec, tid, nthr);
+        else stage_records_in<0>(shs + (size_t)first * rec, s_in, count, rec, tid, nthr);
+        __syncthreads();
+    }
+    if (idx < vb.P) {
+        const GaussPartial p = gaussian_backward_views(
+            idx, vl, S, vb, D, M, means3D, has_sh ? s_in + gl * pitch : nullptr, cov3D_in, radii, clamped, grad_acc,
+            dL_dmeans2D, has_sh ? s_dsh + (vl * GB_SPLIT_G + gl) * pitch : nullptr);
+        float* q = s_part + (vl * GB_SPLIT_G + gl) * GB_PART;
+        q[0] = p.dmean.x; q[1] = p.dmean.y; q[2] = p.dmean.z;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) q[3 + i] = p.dcov[i];
+        q[9] = p.dcolor.x; q[10] = p.dcolor.y; q[11] = p.dcolor.z;
+        q[12] = p.dop;
+        q[13] = p.any_visible ? 1.f : 0.f;
+    }
+    __syncthreads();
+    if (vl == 0 && idx < vb.P) {
+        float a[GB_PART];
+#pragma unroll
+        for (int i = 0; i < GB_PART; ++i) a[i] = s_part[gl * GB_PART + i];
+        for (int s = 1; s < S; ++s)
+#pragma unroll
+            for (int i = 0; i < GB_PART; ++i) a[i] += s_part[(s * GB_SPLIT_G + gl) * GB_PART + i];
+        GaussPartial tot;
+        tot.dmean = make_float3(a[0], a[1], a[2]);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) tot.dcov[i] = a[3 + i];
+        tot.dcolor = make_float3(a[9], a[10], a[11]);
+        tot.dop = a[12];
+        tot.any_visible = a[13] > 0.f;
+        gaussian_backward_finish(idx, tot, scales, scale_modifier, rotations, dL_dcolors, dL_dopacity, dL_dmeans3D,
+                                 dL_dcov3D, dL_dscales, dL_drots);
+    }
+    if (has_sh) {
+        // dL/dsh = sum over the view lanes, in lane order; coalesced 16-byte stores
+        float* dst = dL_dsh + (size_t)first * rec;
+        const int total = count * rec;
+        const bool vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+        for (int i = tid * 4; i < total; i += nthr * 4) {
+            float v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int f = i + j;
+                float acc = 0.f;
+                if (f < total) {
+                    const int o = (f / rec) * pitch + (f % rec);
+                    acc = s_dsh[o];
+                    for (int s = 1; s < S; ++s) acc += s_dsh[s * GB_SPLIT_G * pitch + o];
+                }
+                v[j] = acc;
+            }
+            if (vec && i + 3 < total) *reinterpret_cast<float4*>(dst + i) = make_float4(v[0], v[1], v[2], v[3]);
+            else
+                for (int j = 0; j < 4 && i + j < total; ++j) dst[i + j] = v[j];
+        }
     }
 }
 
@@ -572,6 +687,21 @@ int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, i
         }
     }
     if (gsmem > 64 * 1024) return CSB_ERR_UNSUPPORTED;
+    const int S = num_views >= 8 ? 8 : (num_views >= 4 ? 4 : num_views);
+    const size_t pitch = (size_t)M * 3 + 1;
+    const size_t ssmem = ((shs && dL_dsh) ? (size_t)(1 + S) * GB_SPLIT_G * pitch : 0) * sizeof(float) +
+                         (size_t)S * GB_SPLIT_G * GB_PART * sizeof(float);
+    if (S >= 2 && P < 148 * 256 && ssmem <= 64 * 1024) {
+        static bool configured_split = false;
+        if (!configured_split) {
+            CSB_CUDA_TRY(cudaFuncSetAttribute(gaussian_backward_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+            configured_split = true;
+        }
+        CSB_LAUNCH("gaussian_backward", stream, launch_pdl(gaussian_backward_split_kernel, dim3((P + GB_SPLIT_G - 1) / GB_SPLIT_G), dim3(GB_SPLIT_G * S), ssmem, stream,
+            vb, S, D, M, means3D, shs, cov3D_precomp ? nullptr : scales, scale_modifier, rotations, cov3D, radii, g.clamped,
+            g.grad_acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations));
+        return 0;
+    }
     CSB_LAUNCH("gaussian_backward", stream, launch_pdl(gaussian_backward_kernel, dim3((P + gb - 1) / gb), dim3(gb), gsmem, stream, 
         vb, D, M, means3D, shs, cov3D_precomp ? nullptr : scales, scale_modifier, rotations, cov3D, radii, g.clamped,
         g.grad_acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations));
