@@ -182,11 +182,12 @@ def test_precomputed_colors_and_cov3d_vs_reference_cuda():
     _compare_with_reference(gg, cam)
 
 
-def test_multi_view_batch_equals_sequential():
-    g, cams = S.config_c2(4, 320)
+@pytest.mark.parametrize("n_views", [4, 3, 9])  # 9: view lanes of the split per-Gaussian backward walk two views
+def test_multi_view_batch_equals_sequential(n_views):
+    g, cams = S.config_c2(n_views, 320)
     gg = Hh.to_cuda({k: g[k] for k in ("means3D", "scales", "rotations", "opacities", "shs")})
     H = W = 320
-    dl = torch.from_numpy(S.pixel_grad(4, H, W)).cuda()
+    dl = torch.from_numpy(S.pixel_grad(n_views, H, W)).cuda()
     views, fwd = Hh.product_forward(gg, cams, 3)
     gb = Hh.product_backward(gg, cams, views, fwd, dl, 3)
     tot = None
