@@ -71,10 +71,11 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
     const float* __restrict__ bg = vb.background[v];
     const float bg0 = bg[0], bg1 = bg[1], bg2 = bg[2];
 
-    float accum0 = 0.f, accum1 = 0.f, accum2 = 0.f;
-    float last_alpha = 0.f, lastc0 = 0.f, lastc1 = 0.f, lastc2 = 0.f;
-    const float ddelx_dx = 0.5 * vb.W;
-    const float ddely_dy = 0.5 * vb.H;
+    float2 accum01 = make_float2(0.f, 0.f), lastc01 = make_float2(0.f, 0.f);
+    float accum2 = 0.f, lastc2 = 0.f, last_alpha = 0.f;
+    const float2 dpix01 = make_float2(dpix0, dpix1);
+    const float2 ddel = make_float2(0.5 * vb.W, 0.5 * vb.H);  // d(pixel coordinate) / d(ndc)
+    const float bg_dot_dpixel = bg0 * dpix0 + bg1 * dpix1 + bg2 * dpix2;
 
     // which of the 9 accumulator components (mx my cx cy cw op c0 c1 c2) this lane ends up holding, see XCH below
     const bool up16 = (lane & 16) != 0, up8 = (lane & 8) != 0, up4 = (lane & 4) != 0, up2 = (lane & 2) != 0;
@@ -149,38 +150,36 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
                 T = T * inv_1ma;
                 const float dchannel_dcolor = alpha * T;
                 const float4 cd = lds_f4(a_cd + (uint32_t)j * 16u);
-                float dL_dalpha = 0.0f;
-                accum0 = last_alpha * lastc0 + (1.f - last_alpha) * accum0;
-                lastc0 = cd.x;
-                dL_dalpha += (cd.x - accum0) * dpix0;
-                g_c0 = dchannel_dcolor * dpix0;
-                accum1 = last_alpha * lastc1 + (1.f - last_alpha) * accum1;
-                lastc1 = cd.y;
-                dL_dalpha += (cd.y - accum1) * dpix1;
-                g_c1 = dchannel_dcolor * dpix1;
-                accum2 = last_alpha * lastc2 + (1.f - last_alpha) * accum2;
+                // channel pairs on packed fp32x2 instructions (same roundings, half the issue slots)
+                const float oma = 1.f - last_alpha;
+                const float2 cd01 = make_float2(cd.x, cd.y);
+                accum01 = ffma2_bcast(last_alpha, lastc01, fmul2_bcast(oma, accum01));
+                accum2 = last_alpha * lastc2 + oma * accum2;
+                lastc01 = cd01;
                 lastc2 = cd.z;
-                dL_dalpha += (cd.z - accum2) * dpix2;
+                const float2 e01 = fmul2(ffma2_bcast(-1.f, accum01, cd01), dpix01);
+                float dL_dalpha = e01.x + e01.y + (cd.z - accum2) * dpix2;
+                const float2 gc01 = fmul2_bcast(dchannel_dcolor, dpix01);
+                g_c0 = gc01.x;
+                g_c1 = gc01.y;
                 g_c2 = dchannel_dcolor * dpix2;
                 dL_dalpha *= T;
                 last_alpha = alpha;
-
-                float bg_dot_dpixel = 0;
-                bg_dot_dpixel += bg0 * dpix0;
-                bg_dot_dpixel += bg1 * dpix1;
-                bg_dot_dpixel += bg2 * dpix2;
                 dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
 
                 const float dL_dG = con_o.w * dL_dalpha;
-                const float gdx = G * dx;
-                const float gdy = G * dy;
-                const float dG_ddelx = -gdx * con_o.x - gdy * con_o.y;
-                const float dG_ddely = -gdy * con_o.z - gdx * con_o.y;
-                g_mx = dL_dG * dG_ddelx * ddelx_dx;
-                g_my = dL_dG * dG_ddely * ddely_dy;
-                g_cx = -0.5f * gdx * dx * dL_dG;
-                g_cy = -0.5f * gdx * dy * dL_dG;
-                g_cw = -0.5f * gdy * dy * dL_dG;
+                const float2 dxy = make_float2(dx, dy);
+                const float2 gd = fmul2_bcast(G, dxy);  // (gdx, gdy)
+                const float dG_ddelx = -gd.x * con_o.x - gd.y * con_o.y;
+                const float dG_ddely = -gd.y * con_o.z - gd.x * con_o.y;
+                const float2 gm = fmul2(fmul2_bcast(dL_dG, make_float2(dG_ddelx, dG_ddely)), ddel);
+                g_mx = gm.x;
+                g_my = gm.y;
+                const float h = -0.5f * dL_dG;
+                const float2 gcxy = fmul2_bcast(h, fmul2_bcast(gd.x, dxy));  // -0.5 gdx (dx, dy) dL_dG
+                g_cx = gcxy.x;
+                g_cy = gcxy.y;
+                g_cw = h * gd.y * dy;
                 g_op = G * dL_dalpha;
             }
             // Transposed butterfly: at every step a lane hands one half of its remaining partial sums to its
