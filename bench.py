@@ -376,15 +376,17 @@ def run_b200(args, rank, world, dev):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        ms = []
-        for _ in range(steps):
+        # every step is bracketed by its own event pair on the launching stream; the host is not made to wait for
+        # the step (a training loop does not either): the ranks then stay in lockstep behind each all-reduce
+        # instead of re-starting every step with the skew of a host wake-up
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for a, b_ in ev:
             flush()
-            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
             step_fn()
             b_.record(stream)
-            b_.synchronize()
-            ms.append(a.elapsed_time(b_))
+        torch.cuda.synchronize()
+        ms = [a.elapsed_time(b_) for a, b_ in ev]
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -395,7 +397,15 @@ def run_b200(args, rank, world, dev):
 
     sampler = ClockSampler(dev.index) if rank == 0 else None
     launches0 = lib.csb_launch_count()
+    if bucket.peer:
+        bucket.peer.stats(reset=True)
     ms_step, ms_all = timed(device_step, args.steps, args.warmup)
+    allreduce = None
+    if world > 1:
+        allreduce = {"impl": "csb_peer_all_reduce (one kernel over NVLink peer memory)" if bucket.peer else "NCCL",
+                     "floats": bucket.numel}
+        if bucket.peer:  # the kernel's own clock, mean over warm-up + timed calls on rank 0
+            allreduce.update({k: round(v, 2) if isinstance(v, float) else v for k, v in bucket.peer.stats().items()})
     launches = (lib.csb_launch_count() - launches0) // (args.steps + args.warmup) * args.steps
     R_step = device_step()
     torch.cuda.synchronize()
@@ -434,13 +444,11 @@ def run_b200(args, rank, world, dev):
                 first = False
             color.backward(dl_dev[b[0]:b[-1] + 1])
         if world > 1:
-            flat = torch.cat([leaves[k].grad.reshape(-1) for k in PARAM_NAMES])
-            dist.all_reduce(flat)
-            o = 0
+            # the autograd gradients go into the peer-memory bucket, one NVLink all-reduce kernel sums it in place
+            bucket.copy_({k: leaves[k].grad for k in PARAM_NAMES})
+            bucket.all_reduce()
             for k in PARAM_NAMES:
-                n = leaves[k].grad.numel()
-                grads_host[k].copy_(flat[o:o + n].view_as(leaves[k].grad), non_blocking=True)
-                o += n
+                grads_host[k].copy_(bucket.view(k), non_blocking=True)
         else:
             for k in PARAM_NAMES:
                 grads_host[k].copy_(leaves[k].grad, non_blocking=True)
@@ -497,13 +505,19 @@ def run_b200(args, rank, world, dev):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "gaussians": P, "views_per_gpu": V, "width": W, "height": H,
                    "instances_per_step": int(R_step), "l2": "flushed between steps (256 MB write)",
-                   "parallelism": f"views x{world}" + (" + 1 flat NCCL all-reduce of gradients" if world > 1 else "")},
+                   "parallelism": f"views x{world}" + ((" + 1 flat gradient all-reduce (" + ("csb_peer_all_reduce over NVLink peer memory" if bucket.peer else "NCCL")
+                                                             + ")") if world > 1 else "")},
         "e2e": {"value": world * mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": "diff_gaussian_rasterization.rasterize_views + autograd backward"},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "impl": "b200",
+        # spread of the timed steps on rank 0 (device time): what a synchronous all-reduce turns into rank skew
+        "step_ms_spread": {"min": min(ms_all), "median": statistics.median(ms_all), "max": max(ms_all),
+                           "std": statistics.pstdev(ms_all)},
     }
+    if allreduce:
+        line["allreduce"] = allreduce
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(g_np, cams, dl_np)
     if not args.no_gnn:

@@ -84,6 +84,13 @@ _OPTIONAL = [
     ("csb_profile_enable", None, [c_int]),
     ("csb_profile_read", c_int, [c_char_p, POINTER(ctypes.c_double), POINTER(ctypes.c_ulonglong)]),
     ("csb_profile_names", c_int, [c_char_p, c_size_t]),
+    ("csb_peer_header_bytes", c_size_t, []),
+    ("csb_peer_alloc", c_int, [c_size_t, POINTER(c_void_p)]),
+    ("csb_peer_free", c_int, [c_void_p]),
+    ("csb_peer_export", c_int, [c_void_p, c_void_p]),
+    ("csb_peer_import", c_int, [c_char_p, POINTER(c_void_p)]),
+    ("csb_peer_close", c_int, [c_void_p]),
+    ("csb_peer_all_reduce", c_int, [c_int, c_int, POINTER(c_void_p), c_size_t, ctypes.c_uint, c_void_p]),
 ]
 
 _lib = None

@@ -289,6 +289,28 @@ int csb_adam_step(int n_tensors, float* const* params, float* const* grads, floa
                   float* const* exp_avg_sq, const int64_t* numel, const double* lr, double beta1, double beta2,
                   double eps, int step, int zero_grads, void* stream);
 
+/* ------------------------------------------------------------------------- *
+ * Gradient all-reduce over NVLink peer memory
+ * ------------------------------------------------------------------------- */
+
+/* The single collective of the data-parallel path: the sum over the GPUs of one node of the flat parameter
+ * gradient buffer (views sharded over GPUs: the reference loops them sequentially on one GPU,
+ * scene_reconstruction/train_utils.py:259; graphs of a GNN batch: train_meshnet_sim.py:491-532).
+ * A "peer buffer" is csb_peer_header_bytes() of flags followed by the fp32 payload.  Every rank allocates one
+ * (csb_peer_alloc: cudaMalloc, zero-filled), exports its 64-byte CUDA IPC handle (csb_peer_export), and opens the
+ * handles of the other ranks (csb_peer_import; csb_peer_close / csb_peer_free tear down).
+ * csb_peer_all_reduce enqueues ONE kernel on `stream`: bufs[r] = rank r's buffer as mapped in this process
+ * (bufs[rank] = the own allocation), n_floats (a multiple of 4) payload floats, seq = 1, 2, 3, ... incremented by
+ * the caller on every call (the same value on all ranks).  In place; the sum is formed in rank order on every
+ * element, so all ranks hold bit-identical results.  world <= 8.  Returns 0 or a CSB_ERR_* / cudaError_t code. */
+size_t csb_peer_header_bytes(void);
+int csb_peer_alloc(size_t bytes, void** ptr);
+int csb_peer_free(void* ptr);
+int csb_peer_export(void* ptr, void* handle64);
+int csb_peer_import(const void* handle64, void** ptr);
+int csb_peer_close(void* ptr);
+int csb_peer_all_reduce(int world, int rank, void* const* bufs, size_t n_floats, unsigned seq, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
