@@ -552,6 +552,281 @@ static int launch_role(const Args& a, int kin, int nout, cudaStream_t stream, co
     return 0;
 }
 
+// ---- EDGE role, two tiles in flight per CTA -------------------------------------------------------
+// The generic kernel above walks a tile as one serial chain (gather -> MMA -> epilogue -> ... -> scatter): the tensor
+// pipe idles during gathers and epilogues, the load/store units during the MMAs.  Here the CTA is two independent
+// groups of 128 threads that share the resident weight image (160 KB): each group owns its own tile, 2 K-blocks of A
+// operand (32 KB), 128 TMEM columns, an mbarrier and a named barrier, so one group's gathers / epilogues overlap the
+// other's MMAs -- two "virtual CTAs" per SM, which the weights' footprint forbids as real ones.  To fit 227 KB the
+// row indices live in registers (a warp gathers and scatters its own 32 rows: indices by shuffle), a thread owns a
+// whole row (LayerNorm without shared-memory partials; same summation order as the generic kernel) and the first
+// Linear's K = 384 is fed in three phases of two K-blocks whose loads are issued before the previous phase's MMAs are
+// waited for.  Arithmetic and roundings are those of gnn_mlp_kernel<EDGE>.
+constexpr int E2_A_CHUNKS = 2;
+constexpr size_t E2_SMEM = (size_t)10 * CHUNK_BYTES + 2 * E2_A_CHUNKS * CHUNK_BYTES + 5 * LAT * 4 + 64;
+static_assert(E2_SMEM <= 232448, "edge kernel shared memory");
+
+__device__ __forceinline__ void group_sync(int grp) { asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory"); }
+
+__global__ void __launch_bounds__(THREADS, 1) gnn_edge2_kernel(const __grid_constant__ Args a) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sW = smem;
+    uint8_t* sAall = sW + (size_t)10 * CHUNK_BYTES;
+    float* sF = reinterpret_cast<float*>(sAall + (size_t)2 * E2_A_CHUNKS * CHUNK_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sF + 5 * LAT);  // [0] weights, [1], [2] MMA of group 0 / 1
+    uint32_t* sTmem = reinterpret_cast<uint32_t*>(bars + 3);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int grp = tid >> 7, gt = tid & 127, wg = warp & 3;
+    const int row = gt;  // tile row == TMEM lane owned by this thread
+    uint8_t* sA = sAall + (size_t)grp * E2_A_CHUNKS * CHUNK_BYTES;
+    const uint32_t bar_w = smem_u32(&bars[0]), bar_mma = smem_u32(&bars[1 + grp]);
+
+    if (tid == 0) {
+        if (smem_u32(smem) & 1023u) __trap();  // swizzle-128B operands need the 1024-byte aligned base
+        mbar_init(bar_w, 1);
+        mbar_init(smem_u32(&bars[1]), 1);
+        mbar_init(smem_u32(&bars[2]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(smem_u32(sTmem), 2 * TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *sTmem + (uint32_t)(grp * TMEM_COLS);  // this group's accumulator columns
+    if (tid == 0) {
+        const uint32_t wbytes = 10u * CHUNK_BYTES, fbytes = 5u * LAT * 4u;
+        mbar_expect_tx(bar_w, wbytes + fbytes);
+        for (int c = 0; c < 10; ++c)
+            bulk_g2s(smem_u32(sW + (size_t)c * CHUNK_BYTES), a.unit + (size_t)c * CHUNK_BYTES, CHUNK_BYTES, bar_w);
+        bulk_g2s(smem_u32(sF), a.unit + wbytes, fbytes, bar_w);
+    }
+    grid_dep_trigger();
+    grid_dep_wait();
+    bool weights_ready = false;
+    uint32_t mma_parity = 0;
+    const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW);
+    const uint32_t taddr = tmem + ((uint32_t)(wg * 32) << 16);
+    const unsigned full = 0xffffffffu;
+
+    const int num_tiles = (a.rows + TILE_M - 1) / TILE_M;
+    const int stride = 2 * (int)gridDim.x;
+    int tile = (int)blockIdx.x + grp * (int)gridDim.x;
+    // row indices of the first tile
+    int d = -1, sidx = -1;
+    if (tile < num_tiles) {
+        const int p = tile * TILE_M + row;
+        if (p < a.rows) {
+            d = a.dst_sorted[p];
+            sidx = a.src_sorted[p];
+            if ((unsigned)d >= (unsigned)a.N || (unsigned)sidx >= (unsigned)a.N) d = sidx = -1;
+        }
+    }
+    for (; tile < num_tiles; tile += stride) {
+        const int row0 = tile * TILE_M;
+        // indices of this group's next tile: loaded now, used for the L2 prefetch below and as (d, sidx) next round
+        int dn = -1, sn = -1;
+        const int pn = (tile + stride) * TILE_M + row;
+        if (tile + stride < num_tiles && pn < a.rows) {
+            dn = a.dst_sorted[pn];
+            sn = a.src_sorted[pn];
+            if ((unsigned)dn >= (unsigned)a.N || (unsigned)sn >= (unsigned)a.N) dn = sn = -1;
+        }
+
+        // ---- first Linear, K = 384 as three phases of two K-blocks: x[dst] | x[src] | e0
+        // warp wg gathers its own 32 rows: item (it, lane) = 16-byte piece (lane & 7) of row 32 wg + 4 it + (lane >> 3)
+        uint4 v[16];
+        auto issue_loads = [&](int ph) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int rl = it * 4 + (lane >> 3);
+                const int dd = __shfl_sync(full, d, rl);
+                const int ss = __shfl_sync(full, sidx, rl);
+                const __nv_bfloat16* src;
+                if (ph == 0) src = a.x_bf16 + (size_t)(dd < 0 ? 0 : dd) * LAT;
+                else if (ph == 1) src = a.x_bf16 + (size_t)(ss < 0 ? 0 : ss) * LAT;
+                else src = a.e0 + (size_t)(row0 + wg * 32 + rl) * LAT;
+                v[2 * it] = v[2 * it + 1] = make_uint4(0, 0, 0, 0);
+                if (dd >= 0) {
+                    v[2 * it] = *reinterpret_cast<const uint4*>(src + (lane & 7) * 8);
+                    v[2 * it + 1] = *reinterpret_cast<const uint4*>(src + 64 + (lane & 7) * 8);
+                }
+            }
+        };
+        issue_loads(0);
+#pragma unroll
+        for (int ph = 0; ph < 3; ++ph) {
+            if (ph > 0) {  // the previous phase's MMAs have read the A blocks
+                mbar_wait(bar_mma, mma_parity);
+                mma_parity ^= 1;
+            }
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int r = wg * 32 + it * 4 + (lane >> 3);
+                *reinterpret_cast<uint4*>(sA + swz_off(r, lane & 7)) = v[2 * it];
+                *reinterpret_cast<uint4*>(sA + CHUNK_BYTES + swz_off(r, lane & 7)) = v[2 * it + 1];
+            }
+            if (!weights_ready) { mbar_wait(bar_w, 0); weights_ready = true; }
+            fence_proxy_async();
+            tc_fence_before();
+            group_sync(grp);
+            if (gt == 0) {
+                tc_fence_after();
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma(tmem, umma_desc(sA_u32 + (uint32_t)s * CHUNK_BYTES + k * 32),
+                             umma_desc(sW_u32 + (uint32_t)(2 * ph + s) * CHUNK_BYTES + k * 32),
+                             (ph > 0 || s > 0 || k > 0) ? 1u : 0u);
+                umma_commit(bar_mma);
+            }
+            if (ph < 2) issue_loads(ph + 1);  // in flight while the tensor core works
+        }
+        // next tile's rows towards L2 (each thread its own row: x[dst], x[src], e0 -- two 128-byte lines each)
+        if (dn >= 0) {
+            const char* pd = reinterpret_cast<const char*>(a.x_bf16 + (size_t)dn * LAT);
+            const char* ps = reinterpret_cast<const char*>(a.x_bf16 + (size_t)sn * LAT);
+            const char* pe = reinterpret_cast<const char*>(a.e0 + (size_t)pn * LAT);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pd));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pd + 128));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(ps));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(ps + 128));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pe));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pe + 128));
+        }
+        mbar_wait(bar_mma, mma_parity);
+        mma_parity ^= 1;
+        tc_fence_after();
+
+        // ---- layers 2 and 3: + bias, ReLU, bf16 -> A blocks -> MMA
+#pragma unroll 1
+        for (int layer = 0; layer < 2; ++layer) {
+            const float* bias = sF + layer * LAT;
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                float f[64];
+                tmem_ld32(taddr + h * 64, f);
+                tmem_ld32(taddr + h * 64 + 32, f + 32);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    float q[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) q[j] = fmaxf(f[c * 8 + j] + bias[h * 64 + c * 8 + j], 0.f);
+                    *reinterpret_cast<uint4*>(sA + (size_t)h * CHUNK_BYTES + swz_off(row, c)) =
+                        make_uint4(pack_bf16(q[0], q[1]), pack_bf16(q[2], q[3]), pack_bf16(q[4], q[5]), pack_bf16(q[6], q[7]));
+                }
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            group_sync(grp);
+            if (gt == 0) {
+                tc_fence_after();
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma(tmem, umma_desc(sA_u32 + (uint32_t)s * CHUNK_BYTES + k * 32),
+                             umma_desc(sW_u32 + (uint32_t)(6 + 2 * layer + s) * CHUNK_BYTES + k * 32), (s > 0 || k > 0) ? 1u : 0u);
+                umma_commit(bar_mma);
+            }
+            mbar_wait(bar_mma, mma_parity);
+            mma_parity ^= 1;
+            tc_fence_after();
+        }
+
+        // ---- + bias, LayerNorm over the thread's row (two passes over TMEM, 64-column halves summed like the
+        //      generic kernel: sequentially within a half, then half 0 + half 1)
+        const float* b2 = sF + 2 * LAT;
+        float s0 = 0.f, s1 = 0.f;
+        {
+            float f[64];
+            tmem_ld32(taddr, f);
+            tmem_ld32(taddr + 32, f + 32);
+#pragma unroll
+            for (int j = 0; j < 64; ++j) s0 += f[j] + b2[j];
+            tmem_ld32(taddr + 64, f);
+            tmem_ld32(taddr + 96, f + 32);
+#pragma unroll
+            for (int j = 0; j < 64; ++j) s1 += f[j] + b2[64 + j];
+        }
+        const float mean = (s0 + s1) * (1.0f / LAT);
+        float q0 = 0.f, q1 = 0.f;
+        {
+            float f[64];
+            tmem_ld32(taddr, f);
+            tmem_ld32(taddr + 32, f + 32);
+#pragma unroll
+            for (int j = 0; j < 64; ++j) { const float dl = (f[j] + b2[j]) - mean; q0 = fmaf(dl, dl, q0); }
+            tmem_ld32(taddr + 64, f);
+            tmem_ld32(taddr + 96, f + 32);
+#pragma unroll
+            for (int j = 0; j < 64; ++j) { const float dl = (f[j] + b2[64 + j]) - mean; q1 = fmaf(dl, dl, q1); }
+        }
+        const float var = (q0 + q1) * (1.0f / LAT);
+        const float rstd = 1.0f / sqrtf(var + 1e-5f);
+        const float* lg = sF + 3 * LAT;
+        const float* lb = sF + 4 * LAT;
+
+        // ---- segmented sum over the warp's 32 dst-sorted rows, 32 columns per round, staged in the warp's slice of
+        //      the (idle) A blocks; lane j owns a column and adds once per segment
+        float* st = reinterpret_cast<float*>(sA) + wg * (32 * 33);
+#pragma unroll 1
+        for (int rd = 0; rd < 4; ++rd) {
+            float f[32];
+            tmem_ld32(taddr + rd * 32, f);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int col = rd * 32 + j;
+                st[lane * 33 + j] = ((f[j] + b2[col]) - mean) * rstd * lg[col] + lb[col];
+            }
+            __syncwarp();
+            const int col = rd * 32 + lane;
+            int cur = __shfl_sync(full, d, 0);
+            float acc = 0.f;
+#pragma unroll 4
+            for (int i = 0; i < 32; ++i) {
+                const int dd = __shfl_sync(full, d, i);
+                if (dd != cur) {
+                    if (cur >= 0) atomicAdd(a.agg + (size_t)cur * LAT + col, acc);
+                    cur = dd;
+                    acc = 0.f;
+                }
+                acc += st[i * 33 + lane];
+            }
+            if (cur >= 0) atomicAdd(a.agg + (size_t)cur * LAT + col, acc);
+            __syncwarp();
+        }
+        d = dn;
+        sidx = sn;
+        // the next tile overwrites the A blocks / TMEM columns of this group
+        tc_fence_before();
+        group_sync(grp);
+    }
+    if (!weights_ready && tid == 0) mbar_wait(bar_w, 0);  // never leave a bulk copy in flight
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(*sTmem, 2 * TMEM_COLS);
+}
+
+static int launch_edge2(const Args& a, cudaStream_t stream) {
+    static bool configured = false;
+    if (!configured) {
+        CSB_CUDA_TRY(cudaFuncSetAttribute(gnn_edge2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E2_SMEM));
+        configured = true;
+    }
+    const int tiles = (a.rows + TILE_M - 1) / TILE_M;
+    if (tiles == 0) return 0;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // at most one tile per SM: nothing to overlap, the generic kernel's two-phase chain is shorter (C1: 18 tiles)
+    if (tiles <= sms) return launch_role<EDGE>(a, 0, LAT, stream, "gnn_edge");
+    const int grid = sms;
+    CSB_LAUNCH("gnn_edge", stream, launch_pdl(gnn_edge2_kernel, dim3(grid), dim3(THREADS), E2_SMEM, stream, a));
+    return 0;
+}
+
 }  // namespace gnn
 }  // namespace csb
 
@@ -645,7 +920,7 @@ static int forward_impl(const csb_gnn_dims* d, const void* packed, int N, int E,
         e.N = N; e.kin = 0; e.nout = LAT;
         e.unit = pk + t.u[2 + 2 * m].dst; e.rows = E;
         e.dst_sorted = dst_sorted; e.src_sorted = src_sorted; e.x_bf16 = xcur; e.e0 = e0; e.agg = agg;
-        rc = launch_role<EDGE>(e, 0, LAT, stream, "gnn_edge");
+        rc = launch_edge2(e, stream);
         if (rc) return rc;
         Args n{};
         n.N = N; n.kin = 0; n.nout = LAT;
