@@ -672,12 +672,16 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_edge2_kernel(const __grid_cons
             group_sync(grp);
             if (gt == 0) {
                 tc_fence_after();
+                // descriptors are rebuilt from the two base addresses at every issue (a few ALU ops): left to the
+                // compiler, all 40 of them become loop invariants held in registers and spill
+                uint32_t aw = sA_u32, ww = sW_u32;
+                asm volatile("" : "+r"(aw), "+r"(ww));
 #pragma unroll
                 for (int s = 0; s < 2; ++s)
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma(tmem, umma_desc(sA_u32 + (uint32_t)s * CHUNK_BYTES + k * 32),
-                             umma_desc(sW_u32 + (uint32_t)(2 * ph + s) * CHUNK_BYTES + k * 32),
+                        umma(tmem, umma_desc(aw + (uint32_t)s * CHUNK_BYTES + k * 32),
+                             umma_desc(ww + (uint32_t)(2 * ph + s) * CHUNK_BYTES + k * 32),
                              (ph > 0 || s > 0 || k > 0) ? 1u : 0u);
                 umma_commit(bar_mma);
             }
@@ -722,12 +726,14 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_edge2_kernel(const __grid_cons
             group_sync(grp);
             if (gt == 0) {
                 tc_fence_after();
+                uint32_t aw = sA_u32, ww = sW_u32 + (uint32_t)(6 + 2 * layer) * CHUNK_BYTES;
+                asm volatile("" : "+r"(aw), "+r"(ww));
 #pragma unroll
                 for (int s = 0; s < 2; ++s)
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma(tmem, umma_desc(sA_u32 + (uint32_t)s * CHUNK_BYTES + k * 32),
-                             umma_desc(sW_u32 + (uint32_t)(6 + 2 * layer + s) * CHUNK_BYTES + k * 32), (s > 0 || k > 0) ? 1u : 0u);
+                        umma(tmem, umma_desc(aw + (uint32_t)s * CHUNK_BYTES + k * 32),
+                             umma_desc(ww + (uint32_t)s * CHUNK_BYTES + k * 32), (s > 0 || k > 0) ? 1u : 0u);
                 umma_commit(bar_mma);
             }
             mbar_wait(bar_mma, mma_parity);
@@ -735,66 +741,51 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_edge2_kernel(const __grid_cons
             tc_fence_after();
         }
 
-        // ---- + bias, LayerNorm over the thread's row (two passes over TMEM, 64-column halves summed like the
-        //      generic kernel: sequentially within a half, then half 0 + half 1)
+        // ---- + bias, LayerNorm over the thread's row, all 128 values in registers.  Four interleaved partial sums per
+        //      statistic (a 128-long dependent FADD chain is ~0.25 us of pure latency with two warps per scheduler)
         const float* b2 = sF + 2 * LAT;
-        float s0 = 0.f, s1 = 0.f;
-        {
-            float f[64];
-            tmem_ld32(taddr, f);
-            tmem_ld32(taddr + 32, f + 32);
+        float f[LAT];
+        tmem_ld32(taddr, f);
+        tmem_ld32(taddr + 32, f + 32);
+        tmem_ld32(taddr + 64, f + 64);
+        tmem_ld32(taddr + 96, f + 96);
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int j = 0; j < 64; ++j) s0 += f[j] + b2[j];
-            tmem_ld32(taddr + 64, f);
-            tmem_ld32(taddr + 96, f + 32);
+        for (int j = 0; j < LAT; ++j) { f[j] += b2[j]; s4[j & 3] += f[j]; }
+        const float mean = ((s4[0] + s4[1]) + (s4[2] + s4[3])) * (1.0f / LAT);
+        float q4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int j = 0; j < 64; ++j) s1 += f[j] + b2[64 + j];
-        }
-        const float mean = (s0 + s1) * (1.0f / LAT);
-        float q0 = 0.f, q1 = 0.f;
-        {
-            float f[64];
-            tmem_ld32(taddr, f);
-            tmem_ld32(taddr + 32, f + 32);
-#pragma unroll
-            for (int j = 0; j < 64; ++j) { const float dl = (f[j] + b2[j]) - mean; q0 = fmaf(dl, dl, q0); }
-            tmem_ld32(taddr + 64, f);
-            tmem_ld32(taddr + 96, f + 32);
-#pragma unroll
-            for (int j = 0; j < 64; ++j) { const float dl = (f[j] + b2[64 + j]) - mean; q1 = fmaf(dl, dl, q1); }
-        }
-        const float var = (q0 + q1) * (1.0f / LAT);
+        for (int j = 0; j < LAT; ++j) { const float dl = f[j] - mean; q4[j & 3] = fmaf(dl, dl, q4[j & 3]); }
+        const float var = ((q4[0] + q4[1]) + (q4[2] + q4[3])) * (1.0f / LAT);
         const float rstd = 1.0f / sqrtf(var + 1e-5f);
         const float* lg = sF + 3 * LAT;
         const float* lb = sF + 4 * LAT;
 
         // ---- segmented sum over the warp's 32 dst-sorted rows, 32 columns per round, staged in the warp's slice of
-        //      the (idle) A blocks; lane j owns a column and adds once per segment
+        //      the (idle) A blocks; lane j owns a column and adds once per segment.  Bit i of `ends`: row i is the last
+        //      of its segment (warp-uniform, found once per tile).
+        const int dnext = __shfl_down_sync(full, d, 1);
+        const unsigned ends = __ballot_sync(full, lane == 31 || dnext != d);
         float* st = reinterpret_cast<float*>(sA) + wg * (32 * 33);
-#pragma unroll 1
+#pragma unroll
         for (int rd = 0; rd < 4; ++rd) {
-            float f[32];
-            tmem_ld32(taddr + rd * 32, f);
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
                 const int col = rd * 32 + j;
-                st[lane * 33 + j] = ((f[j] + b2[col]) - mean) * rstd * lg[col] + lb[col];
+                st[lane * 33 + j] = (f[col] - mean) * rstd * lg[col] + lb[col];
             }
             __syncwarp();
             const int col = rd * 32 + lane;
-            int cur = __shfl_sync(full, d, 0);
             float acc = 0.f;
-#pragma unroll 4
+#pragma unroll
             for (int i = 0; i < 32; ++i) {
-                const int dd = __shfl_sync(full, d, i);
-                if (dd != cur) {
-                    if (cur >= 0) atomicAdd(a.agg + (size_t)cur * LAT + col, acc);
-                    cur = dd;
+                acc += st[i * 33 + lane];
+                if ((ends >> i) & 1u) {
+                    const int dd = __shfl_sync(full, d, i);
+                    if (dd >= 0) atomicAdd(a.agg + (size_t)dd * LAT + col, acc);
                     acc = 0.f;
                 }
-                acc += st[i * 33 + lane];
             }
-            if (cur >= 0) atomicAdd(a.agg + (size_t)cur * LAT + col, acc);
             __syncwarp();
         }
         d = dn;
