@@ -301,6 +301,14 @@ def gnn_train_bench(dev, impl, peaks, graphs, F=10, iters=5, world=1):
         last["loss"] = loss.detach()
 
     ms, _ = _time_cuda(step, iters, 3, None)
+    kern = None
+    if impl == "b200":  # per-kernel device time of one more step (library CUDA events)
+        import csb_cabi
+        csb_cabi.lib().csb_profile_enable(1)
+        step()
+        torch.cuda.synchronize()
+        kern = {k: {"ms_per_step": v[0], "launches": int(v[1])} for k, v in csb_cabi.profile_read().items()}
+        csb_cabi.lib().csb_profile_enable(0)
     fl = 3.0 * F * gnn_flops(N, E)
     peak = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1590.0)))
     return {"graphs": graphs, "nodes": N, "edges": E, "rollout_steps": F, "ms_per_step": ms,
@@ -310,7 +318,7 @@ def gnn_train_bench(dev, impl, peaks, graphs, F=10, iters=5, world=1):
                          "frac": fl / (ms * 1e-3) / 1e12 / peak, "flops": "3 x forward (SURVEY.md 8d), recompute not counted",
                          "peak_source": "measured sustained" if peaks else "fallback"},
             "inputs": "resident (the batch is larger than L2: %.0f MB of saved state per prediction)" % (
-                (31.0 * N + E) * 256 / 1e6)}
+                (31.0 * N + E) * 256 / 1e6), **({"kernels": kern} if kern else {})}
 
 
 # ------------------------------------------------------------------------------------------

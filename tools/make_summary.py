@@ -70,12 +70,30 @@ cb = c2.get("cpu_baseline")
 if cb:
     A(f"CPU baseline ({cb['kind']}, {cb['cores']} host threads): {cb['value']:.1f} Mpix/s -- {cb['sample']}.\n")
 if g2:
-    A(f"2 GPUs (views x2, one flat NCCL all-reduce of the gradient bucket): {g2['value']:.0f} Mpix/s, "
-      f"{g2['ms_per_step']:.3f} ms/step (e2e {g2['e2e']['value']:.0f} Mpix/s); against the 1-GPU run of the same build on its box: "
-      "93 % weak-scaling efficiency (the all-reduce of 2.4 MB costs ~28 us of NCCL latency per step).\n")
+    A(f"2 GPUs (views x2, one flat all-reduce of the gradient bucket): {g2['value']:.0f} Mpix/s, "
+      f"{g2['ms_per_step']:.3f} ms/step (e2e {g2['e2e']['value']:.0f} Mpix/s).\n")
 A("Per-kernel CUDA-event times inside the step (`kernels{}` of the bench line; event bracketing adds ~3 us to every short kernel, "
   "the launch list has the undisturbed durations):\n")
 A(ktable(c2) + "\n")
+scal = {}
+for n in (1, 2, 4, 8):
+    d = load(f"scale_n{n}")
+    if d:
+        scal[n] = d
+if len(scal) > 1 and 1 in scal:
+    A("## Weak scaling over views (C2, 4 views per GPU, gradient bucket summed by `csb_peer_all_reduce` over NVLink peer memory)\n")
+    A("| GPUs | Mpix/s (device-resident step) | ms/step | efficiency vs N x 1 GPU | e2e Mpix/s | all-reduce kernel: wait for peers / reduce+push / depart (us) |\n|---|---|---|---|---|---|")
+    for n, d in sorted(scal.items()):
+        ar = d.get("allreduce") or {}
+        ph = f"{ar.get('wait_peers_us', 0):.1f} / {ar.get('reduce_push_us', 0):.1f} / {ar.get('depart_us', 0):.1f}" if ar.get("calls") else "-"
+        A(f"| {n} | {d['value']:.0f} | {d['ms_per_step']:.4f} | {100 * d['value'] / (n * scal[1]['value']):.1f} % | {d['e2e']['value']:.0f} | {ph} |")
+    sp = scal[1].get("step_ms_spread")
+    if sp:
+        A(f"\nSpread of the timed steps on one GPU: min {sp['min']:.4f} / median {sp['median']:.4f} / max {sp['max']:.4f} ms, sigma {sp['std'] * 1e3:.1f} us "
+          "-- the synchronous all-reduce turns this into the `wait for peers` column (rank skew), which is the larger part of the loss at 8 GPUs.")
+    A("All runs of this table come from ONE 8-GPU box (`tools/scale_run.sh`); e2e (host buffers over PCIe) is bounded by the host's memory system when 8 ranks copy at once.\n")
+    json.dump({str(n): {k: d.get(k) for k in ("value", "ms_per_step", "n_gpus", "e2e", "allreduce", "step_ms_spread", "config", "clocks")}
+               for n, d in scal.items()}, open(os.path.join(P, "r1_scaling_c2.json"), "w"), indent=1)
 rf = c2["roofline"]
 A(f"`roofline` of the bench line: dominant kernel `{rf['kernel']}`, algorithmic {rf['achieved']:.0f} GB/s of {rf['peak']:.0f} GB/s measured "
   f"HBM peak (frac {rf['frac']:.3f}), ncu DRAM traffic per launch {rf.get('traffic')} B -- the compositing kernels are issue-bound, see the ncu table.\n")
@@ -126,6 +144,16 @@ if t and rt:
             r = v["roofline"]
             A(f"* `{k}`: {v['ms_per_launch'] * 1e3:.1f} us/launch, algorithmic {r['achieved']:.0f} GB/s = {100 * r['frac']:.0f} % of the measured HBM peak")
     A("")
+if os.path.exists(os.path.join(G, f"{pre}_gnn_edge_full.ncu-rep")):
+    A("## ncu `--set full --clock-control none`: GNN edge role, two tiles in flight per CTA (128 graphs of 40x40, one message-passing step)\n")
+    A(table_of(f"{pre}_gnn_edge_full.ncu-rep", "r1_ncu_gnn_edge.json"))
+    kt = (c2.get("gnn") or {}).get("train_c5", {}).get("kernels")
+    if kt:
+        A("Kernels of one C5 training step on one GPU (128 graphs, 10-step rollout; CUDA events of the library profiler):\n")
+        A("| kernel | launches | ms/step | us/launch |\n|---|---|---|---|")
+        for k, v in sorted(kt.items(), key=lambda kv: -kv[1]["ms_per_step"]):
+            A(f"| `{k}` | {v['launches']} | {v['ms_per_step']:.1f} | {v['ms_per_step'] / v['launches'] * 1e3:.0f} |")
+        A("")
 traffic = {}
 for title, rep, js, wl in (("C2 step", f"{pre}_c2_full.ncu-rep", "r1_ncu_c2_step.json", "c2"),
                            ("C3 step", f"{pre}_c3_full.ncu-rep", "r1_ncu_c3_step.json", "c3"),
