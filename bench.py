@@ -357,16 +357,26 @@ def run_b200(args, rank, world, dev):
     bucket_views = bucket.as_dict()
 
     def device_step():
-        """Device-resident step through the C-ABI wrapper layer (no autograd)."""
+        """Device-resident step through the C-ABI wrapper layer (no autograd).  The instance count of a forward is
+        read (and its overflow check made) after the backward has been enqueued: the host never sits between two
+        kernels of the step."""
+        for attempt in range(3):
+            try:
+                return device_step_once()
+            except dgr.RenderAgain:  # binning workspace too small for this scene: hints are updated, do the step again
+                if attempt == 2:
+                    raise
+
+    def device_step_once():
         if len(view_batches) > 1:
             grad_flat.zero_()
-        R_total = 0
+        pending = []
         for b in view_batches:
             vs = views_of(b)
             fwd = dgr._forward_views(vs, gd["means3D"], e, gd["opacities"], gd["scales"], gd["rotations"], 1.0, e, H, W,
-                                     gd["shs"], 3, False)
+                                     gd["shs"], 3, False, defer_count=True)
             R, color, depth, radii, geom, binning, img = fwd
-            R_total += R
+            pending.append(R)
             # one launch set covers all views of the batch: its gradients go straight into the flat bucket
             gb = dgr._backward_views(vs, gd["means3D"], radii, e, gd["scales"], gd["rotations"], 1.0, e, H, W,
                                      dl[b[0]:b[-1] + 1], gd["shs"], 3, geom, binning, img,
@@ -375,7 +385,7 @@ def run_b200(args, rank, world, dev):
                 dm2, dcol, dop, dm3, dcov, dsh, dsc, drot = gb
                 pack((dm3, dsc, drot, dop, dsh))
         bucket.all_reduce()
-        return R_total
+        return sum(p.wait() for p in pending)
 
     def timed(step_fn, steps, warmup):
         for _ in range(warmup):

@@ -68,6 +68,39 @@ def _await_count(word, stream):
             return v & 0xFFFFFFFF
 
 
+class RenderAgain(RuntimeError):
+    """A deferred instance count turned out larger than the binning workspace (or the per-tile binning path refused the
+    scene): the images of that forward are incomplete.  The size hints have been updated; call the forward again."""
+
+
+class PendingCount:
+    """The instance count of a forward launched with `defer_count=True`: nothing has been read from the device yet.
+    `wait()` (or `int()`) polls the pinned word -- normally long after the binning kernel wrote it, i.e. without
+    waiting -- applies the overflow check the eager path does right after the launch, and returns the count."""
+
+    def __init__(self, word, stream, capacity, key, small, n_tiles):
+        self.word, self.stream, self.capacity, self.key, self.small, self.n_tiles = word, stream, capacity, key, small, n_tiles
+        self.value = None
+
+    def wait(self):
+        if self.value is None:
+            v = _await_count(self.word, self.stream)
+            if self.small and v == _COUNT_REFUSED:
+                _small_bins[self.key] = False
+                raise RenderAgain("the per-tile binning path refused this scene (tile list too long)")
+            if v > self.capacity:
+                _capacity_hint[self.key] = v
+                raise RenderAgain(f"{v} instances do not fit the binning workspace sized for {self.capacity}")
+            _capacity_hint[self.key] = v
+            if self.small and v > 96 * self.n_tiles:
+                _small_bins[self.key] = False
+            self.value = v
+        return self.value
+
+    __int__ = wait
+    __index__ = wait
+
+
 def _f32c(t, name):
     if t is None or t.numel() == 0:
         return None
@@ -94,8 +127,11 @@ def _views_array(views):
 
 
 def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
-                   image_height, image_width, sh, degree, prefiltered, flags=0):
-    """Shared implementation: returns (rendered, color[V,3,H,W], depth[V,1,H,W], radii[V,P], geom, binning, img)."""
+                   image_height, image_width, sh, degree, prefiltered, flags=0, defer_count=False):
+    """Shared implementation: returns (rendered, color[V,3,H,W], depth[V,1,H,W], radii[V,P], geom, binning, img).
+    `defer_count=True` returns a `PendingCount` instead of the int and does not touch the host word: the caller goes
+    on enqueueing (the backward pass does not need the count) and calls `.wait()` when convenient; an overflow of the
+    binning workspace then surfaces there as `RenderAgain` instead of being retried here."""
     lib = _abi.lib()
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise ValueError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:55-57
@@ -149,6 +185,10 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
             out_color.data_ptr(), out_depth.data_ptr(), radii.data_ptr() if P else None, counter.data_ptr(),
             host_word.data_ptr(), flags | 2 | (4 if small else 0), stream)
         _abi.check(rc, "csb_rasterize_forward")
+        if defer_count:
+            del keep
+            return (PendingCount(host_word, torch.cuda.current_stream(), capacity, key, small, n_tiles), out_color,
+                    out_depth, radii, geom, binning, img)
         # no stream synchronisation: the instance count is polled from pinned memory as soon as the binning
         # kernel knows it (the reference blocks on a cudaMemcpy in the middle, rasterizer_impl.cu:282)
         rendered = _await_count(host_word, torch.cuda.current_stream())

@@ -307,3 +307,35 @@ def test_api_surface_and_autograd():
     assert m2.grad is not None and float(m2.grad[:, 2].abs().max()) == 0
     vis = rast.markVisible(gc["means3D"])
     assert vis.dtype == torch.bool and torch.equal(vis, gc["means3D"][:, 2] > 0.2)
+
+
+def test_deferred_count_matches_eager_and_reports_overflow():
+    """defer_count=True: the forward returns without reading the instance count; .wait() gives the eager path's count,
+    the images are the same, and a workspace that is too small surfaces as RenderAgain (then fits on the next call)."""
+    import diff_gaussian_rasterization as dgr
+
+    g, cam = Hh.small_scene(P=4000, W=176, H=128, seed=21)
+    gc = Hh.to_cuda(g)
+    e = torch.Tensor([])
+    args = ([Hh.view_tuple(cam)], gc["means3D"], e, gc["opacities"], gc["scales"], gc["rotations"], 1.0, e,
+            cam.image_height, cam.image_width, gc["shs"], 3, False)
+    eager = dgr._forward_views(*args)
+    key = (gc["means3D"].device, 1, 4000, cam.image_width, cam.image_height)
+    deferred = dgr._forward_views(*args, defer_count=True)
+    assert isinstance(deferred[0], dgr.PendingCount)
+    assert deferred[0].wait() == eager[0] == int(deferred[0])
+    for a, b in zip(eager[1:4], deferred[1:4]):
+        assert torch.equal(a, b)
+    # force a workspace that is too small: pretend the previous frame had almost no instances
+    saved = (dgr._PER_GAUSSIAN, dgr._MIN_CAPACITY)
+    try:
+        dgr._PER_GAUSSIAN, dgr._MIN_CAPACITY = 0, 16
+        dgr._capacity_hint.pop(key, None)
+        small = dgr._forward_views(*args, defer_count=True)
+        with pytest.raises(dgr.RenderAgain):
+            small[0].wait()
+        again = dgr._forward_views(*args, defer_count=True)  # the hint now holds the real count
+        assert again[0].wait() == eager[0]
+        assert torch.equal(again[1], eager[1])
+    finally:
+        dgr._PER_GAUSSIAN, dgr._MIN_CAPACITY = saved
