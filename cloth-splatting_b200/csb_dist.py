@@ -76,13 +76,14 @@ class PeerBuffer:
         push, fence + departure barrier), as the kernel timed itself with %globaltimer."""
         torch.cuda.synchronize(self.device)
         words = torch.as_tensor(_CudaBlob(self.base, self.header // 4), device=self.device)
-        q = words[64:72].view(torch.int64)
-        t_arrive, t_reduce, t_depart, calls = (int(v) for v in q.cpu())
+        q = words[64:76].view(torch.int64)
+        t_arrive, t_reduce, t_depart, calls, t_fence, t_count = (int(v) for v in q.cpu())
         if reset:
             q.zero_()
         n = max(calls, 1)
         return {"calls": calls, "wait_peers_us": t_arrive / n / 1e3, "reduce_push_us": t_reduce / n / 1e3,
-                "depart_us": t_depart / n / 1e3}
+                "depart_us": t_depart / n / 1e3, "depart_fence_us": t_fence / n / 1e3,
+                "depart_count_us": t_count / n / 1e3}
 
     def close(self):
         """Unmaps the peers' buffers and frees the own one (call on every rank; collective)."""

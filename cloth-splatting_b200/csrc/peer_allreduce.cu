@@ -29,7 +29,7 @@ struct Header {
     uint32_t pad[31];
     // [64] self-timing of the calls so far (ns, %globaltimer; block 0 / the last block): waiting for the peers to
     // arrive (rank skew), reducing + pushing, fence + waiting for the peers' done flags; number of calls
-    unsigned long long t_arrive, t_reduce, t_depart, calls;
+    unsigned long long t_arrive, t_reduce, t_depart, calls, t_fence, t_count;
 };
 static_assert(sizeof(Header) <= HEADER_BYTES, "header");
 __device__ __forceinline__ unsigned long long now_ns() {
@@ -53,16 +53,11 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ float4 ld_peer(const float4* p) {
-    float4 v;
-    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_peer(float4* p, float4 v) {
-    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
-                 ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-}
+// Payload accesses are weak, L2-only vector accesses (a warp's 32 x 16 B coalesce into full NVLink packets); the
+// ordering comes from the flags: acquire before the loads, block barrier + system fence + release after the stores.
+// (.relaxed.sys stores went out as single 16-byte packets: the push phase then ran at ~120 GB/s.)
+__device__ __forceinline__ float4 ld_peer(const float4* p) { return __ldcg(p); }
+__device__ __forceinline__ void st_peer(float4* p, float4 v) { __stcg(p, v); }
 // spins until the flag has reached seq (flags only grow; compared modulo 2^32); traps instead of hanging the GPU
 __device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t seq) {
     const long long t0 = clock64();
@@ -80,7 +75,6 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_all_reduce_kernel(const __g
 
     // 0. arrive: everything this rank wrote into its bucket (earlier kernels of the stream) is ordered before the flag
     if (blockIdx.x == 0 && tid < W) {
-        __threadfence_system();
         st_release_sys(&reinterpret_cast<Header*>(a.buf[tid])->arrive[a.rank], a.seq);
     }
     if (tid < W) wait_flag(&mine->arrive[tid], a.seq);
@@ -104,20 +98,25 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_all_reduce_kernel(const __g
         for (int r = 0; r < W; ++r) st_peer(reinterpret_cast<float4*>(a.buf[r] + HEADER_BYTES) + i, s);
     }
 
-    // 2. depart
+    // 2. depart.  One system fence per block (thread 0, after the block barrier: the fence is cumulative over the
+    //    block's pushes it has synchronised with), then the grid counter.  Measured (t_fence): the fence waits ~8 us for
+    //    the remote stores to be acknowledged -- the largest part of the kernel that is not rank skew.
     const unsigned long long t2 = now_ns();
-    __threadfence_system();
     __syncthreads();
     __shared__ bool last;
+    __shared__ unsigned long long t_f;
     if (tid == 0) {
-        const unsigned prev = atomicAdd(&mine->blocks_done, 1u);
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+        t_f = now_ns();
+        unsigned prev;
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(prev) : "l"(&mine->blocks_done) : "memory");
         last = prev == gridDim.x - 1;
         if (last) mine->blocks_done = 0;  // every block has counted: ready for the next call
     }
     __syncthreads();
     if (!last) return;
+    const unsigned long long t3 = now_ns();
     if (tid < W) {
-        __threadfence_system();
         st_release_sys(&reinterpret_cast<Header*>(a.buf[tid])->done[a.rank], a.seq);
         wait_flag(&mine->done[tid], a.seq);
     }
@@ -127,6 +126,8 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_all_reduce_kernel(const __g
         mine->t_reduce += t2 - t1;
         mine->t_depart += now_ns() - t2;
         mine->calls += 1;
+        mine->t_fence += t_f - t2;   // block barrier + system fence of the last block
+        mine->t_count += t3 - t_f;   // grid counter
     }
 }
 
