@@ -440,23 +440,33 @@ def run_b200(args, rank, world, dev):
 
     copy_stream = torch.cuda.Stream(device=dev)
     dl_ready = torch.cuda.Event()
+    staged = dgr.StagedPixelGrads(dl_dev, copy_stream) if len(view_batches) == 1 else None
 
     def e2e_step():
-        # dL/dpixel (the large input) is only needed by the backward: its H2D copy runs on a side stream
-        # while the forward renders; the parameters go first on the compute stream
-        copy_stream.wait_stream(stream)
-        with torch.cuda.stream(copy_stream):
-            dl_dev.copy_(dl_host, non_blocking=True)
-            dl_ready.record(copy_stream)
+        # the parameters (2.4 MB) are enqueued FIRST: host-to-device copies of all streams go through the copy engine in
+        # submission order, and the forward only needs them.  dL/dpixel (30.7 MB, needed by the backward only) follows
+        # on a side stream while the forward renders
         with torch.no_grad():
             for k in PARAM_NAMES:
                 leaves[k].copy_(host[k], non_blocking=True)
                 leaves[k].grad = None
+        # ... and the side stream is held back until they are through (the L2 flush in front of the step would otherwise
+        # let the big copy slip ahead of them in the copy engine)
+        copy_stream.wait_stream(stream)
+        if staged:  # one copy + event per view: view v's compositing backward starts when ITS plane has arrived
+            staged.upload(dl_host)
+        else:
+            with torch.cuda.stream(copy_stream):
+                dl_dev.copy_(dl_host, non_blocking=True)
+                dl_ready.record(copy_stream)
         first = True
         for b in view_batches:
             color, radii, depth = dgr.rasterize_views([sl[v] for v in b], leaves["means3D"], leaves["opacities"],
                                                       shs=leaves["shs"], scales=leaves["scales"],
                                                       rotations=leaves["rotations"])
+            if staged:
+                dgr.backward_staged(color, staged)
+                continue
             if first:
                 stream.wait_event(dl_ready)
                 first = False
@@ -527,7 +537,8 @@ def run_b200(args, rank, world, dev):
                                                              + ")") if world > 1 else "")},
         "e2e": {"value": world * mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "api": "diff_gaussian_rasterization.rasterize_views + autograd backward"},
+                "api": "diff_gaussian_rasterization.rasterize_views + autograd backward"
+                       + (" (dL/dpixel uploaded and consumed view by view: StagedPixelGrads / backward_staged)" if staged else "")},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "impl": "b200",
         # spread of the timed steps on rank 0 (device time): what a synchronous all-reduce turns into rank skew

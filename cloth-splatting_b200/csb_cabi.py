@@ -84,6 +84,12 @@ _OPTIONAL = [
     ("csb_profile_enable", None, [c_int]),
     ("csb_profile_read", c_int, [c_char_p, POINTER(ctypes.c_double), POINTER(ctypes.c_ulonglong)]),
     ("csb_profile_names", c_int, [c_char_p, c_size_t]),
+    ("csb_rasterize_backward_staged", c_int, [
+        c_int, POINTER(CsbView), c_int, c_int, c_int, c_int, c_int,
+        c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p, c_void_p, c_void_p,
+        c_void_p, c_void_p, c_void_p, c_size_t,
+        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(c_void_p),
+        c_void_p]),
     ("csb_peer_header_bytes", c_size_t, []),
     ("csb_peer_alloc", c_int, [c_size_t, POINTER(c_void_p)]),
     ("csb_peer_free", c_int, [c_void_p]),

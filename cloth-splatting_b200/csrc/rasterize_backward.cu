@@ -20,7 +20,7 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
                        const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                        const float4* __restrict__ rgb_depth, const float* __restrict__ final_T,
                        const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
-                       float* __restrict__ grad_acc) {
+                       float* __restrict__ grad_acc, const int view0) {
     __shared__ uint32_t s_id[BW_BATCH];
     __shared__ float2 s_xy[BW_BATCH];
     __shared__ float4 s_co[BW_BATCH];
@@ -30,7 +30,7 @@ render_backward_kernel(const ViewBatch vb, const uint2* __restrict__ ranges, con
 
     grid_dep_wait();
     grid_dep_launch();
-    const int v = blockIdx.z;
+    const int v = view0 + blockIdx.z;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const int lx = (warp & 1) * 8 + (lane & 7);
@@ -645,14 +645,14 @@ using namespace csb;
 
 extern "C" {
 
-int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
-                           const float* means3D, const float* shs, const float* colors_precomp,
-                           const float* scales, float scale_modifier, const float* rotations,
-                           const float* cov3D_precomp, const int* radii, const void* geom_ws,
-                           const void* image_ws, const void* binning_ws, size_t binning_capacity,
-                           const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
-                           float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
-                           float* dL_drotations, void* stream_) {
+static int backward_impl(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
+                         const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* scales, float scale_modifier, const float* rotations,
+                         const float* cov3D_precomp, const int* radii, const void* geom_ws,
+                         const void* image_ws, const void* binning_ws, size_t binning_capacity,
+                         const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                         float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                         float* dL_drotations, void* const* view_ready, void* stream_) {
     (void)colors_precomp;
     cudaStream_t stream = (cudaStream_t)stream_;
     ViewBatch vb;
@@ -670,10 +670,21 @@ int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, i
     CSB_CUDA_TRY(cudaMemsetAsync(g.grad_acc, 0, n * ACC_STRIDE * sizeof(float), stream));
     if (binning_capacity > 0 && binning_ws) {
         const uint32_t* point_list = sorted_side(total_tiles) ? b.vals_b : b.vals_a;
-        dim3 tgrid(vb.gx, vb.gy, num_views);
-        CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, point_list, g.means2D,
-                                                                  g.conic_opacity, g.rgb_depth, im.final_T,
-                                                                  im.n_contrib, dL_dpix, g.grad_acc));
+        if (view_ready) {
+            // dL/dpixel arrives view by view (e.g. over PCIe on another stream): view v is composited backwards as soon as
+            // its event has fired, while the later views are still in flight
+            for (int v = 0; v < num_views; ++v) {
+                if (view_ready[v]) CSB_CUDA_TRY(cudaStreamWaitEvent(stream, (cudaEvent_t)view_ready[v], 0));
+                CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, dim3(vb.gx, vb.gy, 1), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, point_list, g.means2D,
+                                                                          g.conic_opacity, g.rgb_depth, im.final_T,
+                                                                          im.n_contrib, dL_dpix, g.grad_acc, v));
+            }
+        } else {
+            dim3 tgrid(vb.gx, vb.gy, num_views);
+            CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, point_list, g.means2D,
+                                                                      g.conic_opacity, g.rgb_depth, im.final_T,
+                                                                      im.n_contrib, dL_dpix, g.grad_acc, 0));
+        }
     }
     const float* cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
     const int gb = P < 148 * 256 ? 64 : 128;  // few Gaussians (C2: 10 k): smaller blocks reach every SM
@@ -705,6 +716,35 @@ int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, i
         vb, D, M, means3D, shs, cov3D_precomp ? nullptr : scales, scale_modifier, rotations, cov3D, radii, g.clamped,
         g.grad_acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations));
     return 0;
+}
+
+int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
+                           const float* means3D, const float* shs, const float* colors_precomp,
+                           const float* scales, float scale_modifier, const float* rotations,
+                           const float* cov3D_precomp, const int* radii, const void* geom_ws,
+                           const void* image_ws, const void* binning_ws, size_t binning_capacity,
+                           const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                           float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                           float* dL_drotations, void* stream_) {
+    return backward_impl(num_views, views, P, D, M, width, height, means3D, shs, colors_precomp, scales, scale_modifier,
+                         rotations, cov3D_precomp, radii, geom_ws, image_ws, binning_ws, binning_capacity, dL_dpix,
+                         dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations,
+                         nullptr, stream_);
+}
+
+int csb_rasterize_backward_staged(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
+                                  const float* means3D, const float* shs, const float* colors_precomp,
+                                  const float* scales, float scale_modifier, const float* rotations,
+                                  const float* cov3D_precomp, const int* radii, const void* geom_ws,
+                                  const void* image_ws, const void* binning_ws, size_t binning_capacity,
+                                  const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                                  float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                                  float* dL_drotations, void* const* view_ready, void* stream_) {
+    if (!view_ready) return CSB_ERR_BAD_ARG;
+    return backward_impl(num_views, views, P, D, M, width, height, means3D, shs, colors_precomp, scales, scale_modifier,
+                         rotations, cov3D_precomp, radii, geom_ws, image_ws, binning_ws, binning_capacity, dL_dpix,
+                         dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations,
+                         view_ready, stream_);
 }
 
 }  // extern "C"

@@ -206,10 +206,12 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
 
 
 def _backward_views(views, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, image_height,
-                    image_width, dL_dout_color, sh, degree, geom, binning, img, out=None):
+                    image_width, dL_dout_color, sh, degree, geom, binning, img, out=None, view_events=None):
     """`out`: optional dict of preallocated contiguous fp32 CUDA tensors ("means3D" [P,3], "scales" [P,3], "rotations"
     [P,4], "opacities" [P,1], "shs" [P,M,3]) the kernels write these gradients into -- e.g. views of the flat
-    all-reduce bucket (csb_dist.FlatGradBucket), which saves the pack copies."""
+    all-reduce bucket (csb_dist.FlatGradBucket), which saves the pack copies.
+    `view_events`: optional list of V torch.cuda.Event (or None entries): view v's plane of dL_dout_color is complete
+    once its event has fired (csb_rasterize_backward_staged)."""
     lib = _abi.lib()
     V = len(views)
     P = means3D.size(0)
@@ -245,12 +247,20 @@ def _backward_views(views, means3D, radii, colors, scales, rotations, scale_modi
     if P:
         arr, keep = _views_array(views)
         capacity = lib.csb_rasterize_binning_capacity(V, P, W, H, binning.numel())
-        rc = lib.csb_rasterize_backward(
-            V, arr, P, int(degree), M, W, H, _abi.ptr(means3D), _abi.ptr(sh), _abi.ptr(colors), _abi.ptr(scales),
-            float(scale_modifier), _abi.ptr(rotations), _abi.ptr(cov3D_precomp), radii.data_ptr(), geom.data_ptr(),
-            img.data_ptr(), _abi.ptr(binning), capacity, dL_dpix.data_ptr(), dL_dmeans2D.data_ptr(),
-            dL_dcolors.data_ptr(), dL_dopacity.data_ptr(), dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(),
-            _abi.ptr(dL_dsh), dL_dscales.data_ptr(), dL_drotations.data_ptr(), _abi.current_stream_ptr())
+        args = (V, arr, P, int(degree), M, W, H, _abi.ptr(means3D), _abi.ptr(sh), _abi.ptr(colors), _abi.ptr(scales),
+                float(scale_modifier), _abi.ptr(rotations), _abi.ptr(cov3D_precomp), radii.data_ptr(), geom.data_ptr(),
+                img.data_ptr(), _abi.ptr(binning), capacity, dL_dpix.data_ptr(), dL_dmeans2D.data_ptr(),
+                dL_dcolors.data_ptr(), dL_dopacity.data_ptr(), dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(),
+                _abi.ptr(dL_dsh), dL_dscales.data_ptr(), dL_drotations.data_ptr())
+        if view_events is not None:
+            if len(view_events) != V:
+                raise ValueError("view_events needs one entry per view")
+            import ctypes
+
+            evs = (ctypes.c_void_p * V)(*[None if ev is None else ev.cuda_event for ev in view_events])
+            rc = lib.csb_rasterize_backward_staged(*args, evs, _abi.current_stream_ptr())
+        else:
+            rc = lib.csb_rasterize_backward(*args, _abi.current_stream_ptr())
         _abi.check(rc, "csb_rasterize_backward")
         del keep
     return dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations
@@ -426,11 +436,52 @@ class _RasterizeViews(torch.autograd.Function):
         s0 = settings_list[0]
         colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img = ctx.saved_tensors
         views = [(s.viewmatrix, s.projmatrix, s.campos, s.bg, s.tanfovx, s.tanfovy) for s in settings_list]
+        staged = getattr(_staged, "grads", None)
+        events = None
+        if staged is not None and staged.dev.data_ptr() == grad_color.data_ptr() and len(staged.events) == len(views):
+            events = staged.events  # the upstream gradient is the staged upload itself: wait view by view
         g = _backward_views(views, means3D, radii, colors_precomp, scales, rotations, s0.scale_modifier, cov3Ds_precomp,
-                            s0.image_height, s0.image_width, grad_color, sh, s0.sh_degree, geom, binning, img)
+                            s0.image_height, s0.image_width, grad_color, sh, s0.sh_degree, geom, binning, img,
+                            view_events=events)
         dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations = g
         ctx.dL_dmeans2D = dL_dmeans2D
         return (dL_dmeans3D, dL_dsh, dL_dcolors, dL_dopacity, dL_dscales, dL_drotations, dL_dcov3D, None)
+
+
+class _Staged:  # a plain global: autograd runs CUDA nodes on its own device thread, a thread-local would not be seen
+    grads = None
+
+
+_staged = _Staged()
+
+
+class StagedPixelGrads:
+    """dL/dpixel of a view batch on its way to the device, view by view: `upload(host)` enqueues one copy per view on
+    `stream` (a side stream) and records an event behind each; `backward_staged(color, staged)` then runs the backward
+    of `rasterize_views` so that view v is composited as soon as ITS plane has arrived, while the planes of the later
+    views are still crossing PCIe."""
+
+    def __init__(self, dev_buffer, stream):
+        self.dev, self.stream = dev_buffer, stream
+        self.events = [torch.cuda.Event() for _ in range(dev_buffer.shape[0])]
+
+    def upload(self, host):
+        with torch.cuda.stream(self.stream):
+            for v, ev in enumerate(self.events):
+                self.dev[v].copy_(host[v], non_blocking=True)
+                ev.record(self.stream)
+        return self
+
+
+def backward_staged(color, staged):
+    """color.backward(staged.dev) with the per-view events of `staged` honoured by the rasterizer's backward (the
+    current stream never waits for the whole upload).  Only valid when `color` is the direct output of
+    `rasterize_views` and staged.dev is passed as its upstream gradient."""
+    _staged.grads = staged
+    try:
+        color.backward(staged.dev)
+    finally:
+        _staged.grads = None
 
 
 def rasterize_views(settings_list, means3D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,

@@ -135,6 +135,20 @@ int csb_rasterize_backward(int num_views, const csb_view* views, int P, int D, i
                            float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
                            float* dL_drotations, void* stream);
 
+/* The same backward when dL_dpix arrives view by view (uploaded over PCIe on another stream, or produced by a
+ * per-view loss): view_ready[v] is a cudaEvent_t (or NULL = already there) recorded after view v's plane
+ * dL_dpix[v] is complete.  View v is composited backwards as soon as its event has fired, the per-Gaussian stage
+ * runs after the last view -- the transfer of the later views overlaps the compositing of the earlier ones.
+ * Results are bit-identical to csb_rasterize_backward's up to the order of the atomic sums it already has. */
+int csb_rasterize_backward_staged(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
+                                  const float* means3D, const float* shs, const float* colors_precomp,
+                                  const float* scales, float scale_modifier, const float* rotations,
+                                  const float* cov3D_precomp, const int* radii, const void* geom_ws,
+                                  const void* image_ws, const void* binning_ws, size_t binning_capacity,
+                                  const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                                  float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                                  float* dL_drotations, void* const* view_ready, void* stream);
+
 /* present[i] = (viewmatrix * means3D[i]).z > 0.2   (auxiliary.h:139-164) */
 int csb_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      uint8_t* present, void* stream);

@@ -339,3 +339,37 @@ def test_deferred_count_matches_eager_and_reports_overflow():
         assert torch.equal(again[1], eager[1])
     finally:
         dgr._PER_GAUSSIAN, dgr._MIN_CAPACITY = saved
+
+
+def test_staged_pixel_grads_backward_matches_plain():
+    """dL/dpixel uploaded view by view on a side stream (StagedPixelGrads) and consumed by backward_staged: the same
+    gradients as color.backward(dl) with the whole tensor resident (the sums over pixels are atomic in both, hence the
+    tolerance of the unordered float sums)."""
+    import diff_gaussian_rasterization as dgr
+
+    g = S.mesh_gaussians(8, 14, 1)
+    center = g["verts"].mean(0)
+    cams = S.ring_cameras(3, 208, 176, 0.6911, center)
+    gc = Hh.to_cuda({k: g[k] for k in ("means3D", "scales", "rotations", "opacities", "shs")})
+    settings = [Hh.settings_for(c) for c in cams]
+    dl_host = torch.from_numpy(S.pixel_grad(3, 176, 208, seed=3)).pin_memory()
+
+    def run(staged_mode):
+        leaves = {k: gc[k].clone().requires_grad_(True) for k in gc}
+        color, radii, depth = dgr.rasterize_views(settings, leaves["means3D"], leaves["opacities"], shs=leaves["shs"],
+                                                  scales=leaves["scales"], rotations=leaves["rotations"])
+        if staged_mode:
+            dev = torch.empty_like(color)
+            staged = dgr.StagedPixelGrads(dev, torch.cuda.Stream()).upload(dl_host)
+            dgr.backward_staged(color, staged)
+        else:
+            color.backward(dl_host.cuda())
+        torch.cuda.synchronize()
+        return {k: t.grad.clone() for k, t in leaves.items()}
+
+    plain, staged = run(False), run(True)
+    assert dgr._staged.grads is None
+    for k in plain:
+        scale = float(plain[k].abs().max()) + 1e-20
+        assert float((plain[k] - staged[k]).abs().max()) <= 2e-5 * scale, k
+        assert float(plain[k].abs().max()) > 0
