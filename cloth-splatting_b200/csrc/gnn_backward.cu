@@ -557,17 +557,18 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_bwd_kernel(const __grid_consta
             if (rvalid) {
                 float4* o = reinterpret_cast<float4*>(a.dx + (size_t)grow * LAT + half * 64);
 #pragma unroll
-                for (int c = 0; c < 16; ++c) {
-                    float4 t = o[c];
-                    t.x += v[c * 4]; t.y += v[c * 4 + 1]; t.z += v[c * 4 + 2]; t.w += v[c * 4 + 3];
-                    o[c] = t;
-                }
+                for (int c = 0; c < 16; ++c)  // red.global.add.v4.f32: no load on the tile's critical path (one adder per element
+                    atomicAdd(&o[c], make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]));  // and kernel: same sum)
             }
         } else if (MODE == EDGE) {
-            float* st = reinterpret_cast<float*>(sA) + warp * (32 * 33);
+            float* st = reinterpret_cast<float*>(sA) + warp * (32 * 36);  // per-warp staging: pitch 33 here, 36 below
             const int* wd = sDst + (warp & 3) * 32;
             const int* wsrc = sSrc + (warp & 3) * 32;
-            // d x[dst]: segmented sum over the warp's dst-sorted rows, one red.add per (segment, column)
+            // d x[dst]: segmented sum over the warp's dst-sorted rows, one red.add per (segment, column).  Bit i of `ends`:
+            // row i is the last of its segment (one ballot per tile instead of a compare + branch per row and column)
+            const int my_d = wd[lane];
+            const int nx_d = __shfl_down_sync(0xffffffffu, my_d, 1);
+            const unsigned ends = __ballot_sync(0xffffffffu, lane == 31 || nx_d != my_d);
             load_acc(0);
 #pragma unroll
             for (int rd = 0; rd < 2; ++rd) {
@@ -575,33 +576,35 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_bwd_kernel(const __grid_consta
                 for (int j = 0; j < 32; ++j) st[lane * 33 + j] = v[rd * 32 + j];
                 __syncwarp();
                 const int col = half * 64 + rd * 32 + lane;
-                int cur = wd[0];
                 float s = 0.f;
-#pragma unroll 4
+#pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                    const int dd = wd[i];
-                    if (dd != cur) {
-                        if (cur >= 0) atomicAdd(a.dx + (size_t)cur * LAT + col, s);
-                        cur = dd;
+                    s += st[i * 33 + lane];
+                    if ((ends >> i) & 1u) {
+                        const int dd = __shfl_sync(0xffffffffu, my_d, i);
+                        if (dd >= 0) atomicAdd(a.dx + (size_t)dd * LAT + col, s);
                         s = 0.f;
                     }
-                    s += st[i * 33 + lane];
                 }
-                if (cur >= 0) atomicAdd(a.dx + (size_t)cur * LAT + col, s);
                 __syncwarp();
             }
-            // d x[src]: one coalesced 128-byte red.add per row and 32-column group
+            // d x[src]: rows go out as 16-byte vector red.adds (lane = 4 columns of one of 4 rows per step: 128 bytes per
+            // row and warp instruction), 8 steps per 32 columns instead of 32 scalar ones
             load_acc(128);
+            float* st4 = st;  // same per-warp region, pitch 36 floats: 16-byte aligned rows
 #pragma unroll
             for (int rd = 0; rd < 2; ++rd) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) st[lane * 33 + j] = v[rd * 32 + j];
+                for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<float4*>(st4 + lane * 36 + j) = make_float4(v[rd * 32 + j], v[rd * 32 + j + 1], v[rd * 32 + j + 2], v[rd * 32 + j + 3]);
                 __syncwarp();
-                const int col = half * 64 + rd * 32 + lane;
-#pragma unroll 4
-                for (int i = 0; i < 32; ++i) {
-                    const int sr = wsrc[i];
-                    if (sr >= 0) atomicAdd(a.dx + (size_t)sr * LAT + col, st[i * 33 + lane]);
+                const int col = half * 64 + rd * 32 + (lane & 7) * 4;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int r = i * 4 + (lane >> 3);
+                    const int sr = wsrc[r];
+                    const float4 t = *reinterpret_cast<const float4*>(st4 + r * 36 + (lane & 7) * 4);
+                    if (sr >= 0) atomicAdd(reinterpret_cast<float4*>(a.dx + (size_t)sr * LAT + col), t);
                 }
                 __syncwarp();
             }
@@ -610,11 +613,8 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_bwd_kernel(const __grid_consta
             if (rvalid && sDst[row] >= 0) {
                 float4* o = reinterpret_cast<float4*>(a.de0 + (size_t)grow * LAT + half * 64);
 #pragma unroll
-                for (int c = 0; c < 16; ++c) {
-                    float4 t = o[c];
-                    t.x += v[c * 4]; t.y += v[c * 4 + 1]; t.z += v[c * 4 + 2]; t.w += v[c * 4 + 3];
-                    o[c] = t;
-                }
+                for (int c = 0; c < 16; ++c)  // red.global.add.v4.f32: no load on the tile's critical path (one adder per element
+                    atomicAdd(&o[c], make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]));  // and kernel: same sum)
             }
         }
         tc_fence_before();
