@@ -202,6 +202,10 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_bwd_kernel(const __grid_consta
     };
 
     const int num_tiles = (a.rows + TILE_M - 1) / TILE_M;
+    // EDGE: row indices of the CTA's next tile, fetched one tile ahead (threads < 128) so that a tile does not start with
+    // two dependent global-memory latencies (indices, then the rows they point to)
+    int d_next = -1, s_next = -1;
+    bool have_next = false;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int row0 = tile * TILE_M;
         const int grow = row0 + row;
@@ -305,15 +309,25 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_bwd_kernel(const __grid_consta
         if (MODE == EDGE) {
             if (tid < TILE_M) {
                 const int p = row0 + tid;
-                int d = -1, s = -1;
-                if (p < a.rows) {
-                    d = a.dst_sorted[p];
-                    s = a.src_sorted[p];
-                    if ((unsigned)d >= (unsigned)a.N || (unsigned)s >= (unsigned)a.N) d = s = -1;
+                int d = d_next, s = s_next;
+                if (!have_next) {
+                    d = s = -1;
+                    if (p < a.rows) {
+                        d = a.dst_sorted[p];
+                        s = a.src_sorted[p];
+                        if ((unsigned)d >= (unsigned)a.N || (unsigned)s >= (unsigned)a.N) d = s = -1;
+                    }
                 }
                 sDst[tid] = d;
                 sSrc[tid] = s;
+                const int pn = p + (int)gridDim.x * TILE_M;
+                d_next = s_next = -1;
+                if (pn < a.rows) {  // consumed at the top of the next tile
+                    d_next = a.dst_sorted[pn];
+                    s_next = a.src_sorted[pn];
+                }
             }
+            have_next = true;
             __syncthreads();
 #pragma unroll 1
             for (int ph = 0; ph < 2; ++ph) {
@@ -564,6 +578,20 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_bwd_kernel(const __grid_consta
             float* st = reinterpret_cast<float*>(sA) + warp * (32 * 36);  // per-warp staging: pitch 33 here, 36 below
             const int* wd = sDst + (warp & 3) * 32;
             const int* wsrc = sSrc + (warp & 3) * 32;
+            if (tid < TILE_M) {  // the next tile's indices have long arrived: validate, pull its rows towards L2
+                if ((unsigned)d_next >= (unsigned)a.N || (unsigned)s_next >= (unsigned)a.N) d_next = s_next = -1;
+                if (d_next >= 0) {
+                    const char* pd = reinterpret_cast<const char*>(a.x_bf16 + (size_t)d_next * LAT);
+                    const char* ps = reinterpret_cast<const char*>(a.x_bf16 + (size_t)s_next * LAT);
+                    const char* pe = reinterpret_cast<const char*>(a.e0 + (size_t)(row0 + tid + (size_t)gridDim.x * TILE_M) * LAT);
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pd));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pd + 128));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(ps));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(ps + 128));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pe));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pe + 128));
+                }
+            }
             // d x[dst]: segmented sum over the warp's dst-sorted rows, one red.add per (segment, column).  Bit i of `ends`:
             // row i is the last of its segment (one ballot per tile instead of a compare + branch per row and column)
             const int my_d = wd[lane];
