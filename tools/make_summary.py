@@ -82,17 +82,20 @@ for n in (1, 2, 4, 8):
         scal[n] = d
 if len(scal) > 1 and 1 in scal:
     A("## Weak scaling over views (C2, 4 views per GPU, gradient bucket summed by `csb_peer_all_reduce` over NVLink peer memory)\n")
-    A("| GPUs | Mpix/s (device-resident step) | ms/step | efficiency vs N x 1 GPU | e2e Mpix/s | all-reduce kernel: wait for peers / reduce+push / depart (us) |\n|---|---|---|---|---|---|")
+    A("| GPUs | Mpix/s (device-resident step) | ms/step | efficiency vs N x 1 GPU | e2e Mpix/s | all-reduce kernel: wait for peers / reduce+push / depart (us) | GNN C5 training graphs/s (128 graphs per GPU) |\n|---|---|---|---|---|---|---|")
     for n, d in sorted(scal.items()):
         ar = d.get("allreduce") or {}
         ph = f"{ar.get('wait_peers_us', 0):.1f} / {ar.get('reduce_push_us', 0):.1f} / {ar.get('depart_us', 0):.1f}" if ar.get("calls") else "-"
-        A(f"| {n} | {d['value']:.0f} | {d['ms_per_step']:.4f} | {100 * d['value'] / (n * scal[1]['value']):.1f} % | {d['e2e']['value']:.0f} | {ph} |")
+        tr = (d.get("gnn") or {}).get("train_c5")
+        tr1 = (scal[1].get("gnn") or {}).get("train_c5")
+        gt = f"{tr['graphs_per_s']:.0f} ({100 * tr['graphs_per_s'] / (n * tr1['graphs_per_s']):.0f} %)" if tr and tr1 else "-"
+        A(f"| {n} | {d['value']:.0f} | {d['ms_per_step']:.4f} | {100 * d['value'] / (n * scal[1]['value']):.1f} % | {d['e2e']['value']:.0f} | {ph} | {gt} |")
     sp = scal[1].get("step_ms_spread")
     if sp:
         A(f"\nSpread of the timed steps on one GPU: min {sp['min']:.4f} / median {sp['median']:.4f} / max {sp['max']:.4f} ms, sigma {sp['std'] * 1e3:.1f} us "
           "-- the synchronous all-reduce turns this into the `wait for peers` column (rank skew), which is the larger part of the loss at 8 GPUs.")
-    A("All runs of this table come from ONE 8-GPU box (`tools/scale_run.sh`); e2e (host buffers over PCIe) is bounded by the host's memory system when 8 ranks copy at once.\n")
-    json.dump({str(n): {k: d.get(k) for k in ("value", "ms_per_step", "n_gpus", "e2e", "allreduce", "step_ms_spread", "config", "clocks")}
+    A("All runs of this table come from ONE 8-GPU box (`tools/scale_run_full.sh`: the default `bench.py` command at every N); e2e (host buffers over PCIe) is bounded by the host's memory system when 8 ranks copy at once.\n")
+    json.dump({str(n): {k: d.get(k) for k in ("value", "ms_per_step", "n_gpus", "e2e", "allreduce", "step_ms_spread", "config", "clocks")} | {"gnn_train_c5": (d.get("gnn") or {}).get("train_c5")}
                for n, d in scal.items()}, open(os.path.join(P, "r1_scaling_c2.json"), "w"), indent=1)
 rf = c2["roofline"]
 A(f"`roofline` of the bench line: dominant kernel `{rf['kernel']}`, algorithmic {rf['achieved']:.0f} GB/s of {rf['peak']:.0f} GB/s measured "
