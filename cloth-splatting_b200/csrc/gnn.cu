@@ -112,7 +112,7 @@ static size_t smem_bytes(int mode, int kin, int nout) {
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(THREADS, 1) gnn_mlp_kernel(const __grid_constant__ Args a) {
+__global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1) gnn_mlp_kernel(const __grid_constant__ Args a) {
     using C = Cfg<MODE>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -547,7 +547,9 @@ static int launch_role(const Args& a, int kin, int nout, cudaStream_t stream, co
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int grid = tiles < sms ? tiles : sms;
+    // ENC / DEC: ~108 KB of shared memory and 128 registers: two CTAs per SM overlap each other's serial tile chains
+    const int per_sm = (MODE == ENC || MODE == DEC) ? 2 : 1;
+    const int grid = tiles < sms * per_sm ? tiles : sms * per_sm;
     CSB_LAUNCH(name, stream, launch_pdl(gnn_mlp_kernel<MODE>, dim3(grid), dim3(THREADS), smem, stream, a));
     return 0;
 }
