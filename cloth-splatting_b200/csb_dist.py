@@ -6,6 +6,7 @@ Process-group plumbing (rendezvous, handle exchange, barriers): torch.distribute
 the CPU tests.  The gradient sum itself runs over NVLink peer memory with the library's own kernel
 (`PeerBuffer` -> csb_peer_all_reduce, csrc/peer_allreduce.cu) whenever the ranks are CUDA devices of one node."""
 import ctypes
+import os
 from typing import Dict, List, Sequence
 
 import torch
@@ -22,6 +23,21 @@ class _CudaBlob:
     def __init__(self, ptr, numel):
         self.__cuda_array_interface__ = {"shape": (numel,), "typestr": "<f4", "data": (ptr, False), "version": 3,
                                          "strides": None}
+
+
+class PeerUnavailable(RuntimeError):
+    """CUDA IPC between the ranks is not possible here (raised on every rank together)."""
+
+
+def _peer_or_none(numel, device):
+    """A PeerBuffer, or None (with one line on stderr) where the ranks cannot map each other's memory."""
+    try:
+        return PeerBuffer(numel, device)
+    except PeerUnavailable as ex:
+        if dist.get_rank() == 0:
+            import sys
+            print(f"csb_dist: {ex}; the gradient sum falls back to NCCL", file=sys.stderr)
+        return None
 
 
 class PeerBuffer:
@@ -41,27 +57,52 @@ class PeerBuffer:
         self.padded = (self.numel + 3) // 4 * 4
         self.header = int(self.lib.csb_peer_header_bytes())
         self.seq = 0
+        # Two collective stages, each followed by an agreement: a rank that cannot allocate / export / map raises
+        # PeerUnavailable on EVERY rank (nobody is left waiting in a collective), and the callers fall back to NCCL.
+        self.base, self.opened, err = None, [], None
+        handle = ctypes.create_string_buffer(64)
         with torch.cuda.device(self.device):
-            base = ctypes.c_void_p()
-            self.check(self.lib.csb_peer_alloc(self.header + self.padded * 4, ctypes.byref(base)), "csb_peer_alloc")
-            self.base = base.value
-            handle = ctypes.create_string_buffer(64)
-            self.check(self.lib.csb_peer_export(self.base, handle), "csb_peer_export")
+            try:
+                if os.environ.get("CSB_PEER_FAIL_RANK") == str(self.rank):  # test hook for the fallback path
+                    raise RuntimeError("CSB_PEER_FAIL_RANK")
+                base = ctypes.c_void_p()
+                self.check(self.lib.csb_peer_alloc(self.header + self.padded * 4, ctypes.byref(base)), "csb_peer_alloc")
+                self.base = base.value
+                self.check(self.lib.csb_peer_export(self.base, handle), "csb_peer_export")
+            except Exception as ex:  # noqa: BLE001
+                err = ex
             every = [None] * self.world
-            dist.all_gather_object(every, handle.raw)
+            dist.all_gather_object(every, (err is None, handle.raw))
+            if not all(ok for ok, _ in every):
+                self._abandon()
+                raise PeerUnavailable(f"peer buffer: allocation / export failed on a rank ({err})")
             self.ptrs = (ctypes.c_void_p * self.world)()
-            self.opened = []
-            for r in range(self.world):
-                if r == self.rank:
-                    self.ptrs[r] = self.base
-                    continue
-                p = ctypes.c_void_p()
-                self.check(self.lib.csb_peer_import(every[r], ctypes.byref(p)), "csb_peer_import")
-                self.ptrs[r] = p.value
-                self.opened.append(p.value)
+            try:
+                for r in range(self.world):
+                    if r == self.rank:
+                        self.ptrs[r] = self.base
+                        continue
+                    p = ctypes.c_void_p()
+                    self.check(self.lib.csb_peer_import(every[r][1], ctypes.byref(p)), "csb_peer_import")
+                    self.ptrs[r] = p.value
+                    self.opened.append(p.value)
+            except Exception as ex:  # noqa: BLE001
+                err = ex
+            oks = [None] * self.world
+            dist.all_gather_object(oks, err is None)  # also the barrier: every rank has mapped every buffer
+            if not all(oks):
+                self._abandon()
+                raise PeerUnavailable(f"peer buffer: a rank could not map its peers ({err})")
             self._blob = _CudaBlob(self.base + self.header, self.padded)
             self.flat = torch.as_tensor(self._blob, device=self.device)[: self.numel]
-        dist.barrier()  # nobody starts reducing before every rank has mapped every buffer
+
+    def _abandon(self):
+        for p in self.opened:
+            self.lib.csb_peer_close(p)
+        self.opened = []
+        if self.base:
+            self.lib.csb_peer_free(self.base)
+        self.base = None
 
     def all_reduce(self):
         import csb_cabi
@@ -128,7 +169,11 @@ class FlatGradBucket:
             n += m
         self.numel = n
         # several CUDA ranks on one node: the bucket lives in peer memory and is summed by csb_peer_all_reduce
-        self.peer = PeerBuffer(n, device) if (peer is None and peer_capable(device)) or peer else None
+        self.peer = None
+        if peer is None and peer_capable(device):
+            self.peer = _peer_or_none(n, device)
+        elif peer:
+            self.peer = PeerBuffer(n, device)
         self.flat = self.peer.flat if self.peer else torch.zeros(n, dtype=torch.float32, device=device)
 
     def view(self, name):
@@ -170,8 +215,8 @@ def attach_flat_grads(params) -> torch.Tensor:
     (`all_reduce_flat`).  Use `flat.zero_()` (or optimizer.zero_grad(set_to_none=False)) between steps."""
     params = [p for p in params if p.requires_grad]
     n = sum(p.numel() for p in params)
-    if peer_capable(params[0].device):
-        pb = PeerBuffer(n, params[0].device)
+    pb = _peer_or_none(n, params[0].device) if peer_capable(params[0].device) else None
+    if pb is not None:
         flat = pb.flat
         _PEER_OF[flat.data_ptr()] = pb
     else:
