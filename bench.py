@@ -439,8 +439,8 @@ def run_b200(args, rank, world, dev):
     d2h = sum(t.numel() * 4 for t in grads_host.values())
 
     copy_stream = torch.cuda.Stream(device=dev)
-    dl_ready = torch.cuda.Event()
-    staged = dgr.StagedPixelGrads(dl_dev, copy_stream) if len(view_batches) == 1 else None
+    # one staged upload per launch set (C4: 4 sets of 16 views): a set's backward waits for ITS views only
+    staged = [dgr.StagedPixelGrads(dl_dev[b[0]:b[-1] + 1], copy_stream) for b in view_batches]
 
     def e2e_step():
         # the parameters (2.4 MB) are enqueued FIRST: host-to-device copies of all streams go through the copy engine in
@@ -453,24 +453,14 @@ def run_b200(args, rank, world, dev):
         # ... and the side stream is held back until they are through (the L2 flush in front of the step would otherwise
         # let the big copy slip ahead of them in the copy engine)
         copy_stream.wait_stream(stream)
-        if staged:  # one copy + event per view: view v's compositing backward starts when ITS plane has arrived
-            staged.upload(dl_host)
-        else:
-            with torch.cuda.stream(copy_stream):
-                dl_dev.copy_(dl_host, non_blocking=True)
-                dl_ready.record(copy_stream)
-        first = True
-        for b in view_batches:
+        # one copy + event per view: view v's compositing backward starts when ITS plane has arrived
+        for st, b in zip(staged, view_batches):
+            st.upload(dl_host[b[0]:b[-1] + 1])
+        for st, b in zip(staged, view_batches):
             color, radii, depth = dgr.rasterize_views([sl[v] for v in b], leaves["means3D"], leaves["opacities"],
                                                       shs=leaves["shs"], scales=leaves["scales"],
                                                       rotations=leaves["rotations"])
-            if staged:
-                dgr.backward_staged(color, staged)
-                continue
-            if first:
-                stream.wait_event(dl_ready)
-                first = False
-            color.backward(dl_dev[b[0]:b[-1] + 1])
+            dgr.backward_staged(color, st)
         if world > 1:
             # the autograd gradients go into the peer-memory bucket, one NVLink all-reduce kernel sums it in place
             bucket.copy_({k: leaves[k].grad for k in PARAM_NAMES})
@@ -538,7 +528,7 @@ def run_b200(args, rank, world, dev):
         "e2e": {"value": world * mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": "diff_gaussian_rasterization.rasterize_views + autograd backward"
-                       + (" (dL/dpixel uploaded and consumed view by view: StagedPixelGrads / backward_staged)" if staged else "")},
+                       + " (dL/dpixel uploaded and consumed view by view: StagedPixelGrads / backward_staged)"},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "impl": "b200",
         # spread of the timed steps on rank 0 (device time): what a synchronous all-reduce turns into rank skew
