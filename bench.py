@@ -516,6 +516,14 @@ def run_b200(args, rank, world, dev):
     roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": traffic, "peak_source": "measured" if peaks else "fallback",
                 "note": "compositing kernels are FP32/SFU-issue bound, not HBM bound; see kernels{} and DESIGN.md"}
+    # what does bound it: issue-slot and pipe utilisation of the same kernel from the committed ncu --set full capture
+    try:
+        for r in json.load(open(os.path.join(ROOT, "profiles", f"r1_ncu_{args.workload}_step.json"))):
+            if r["kernel"].startswith(top):
+                roofline["ncu"] = {"issue_slots_busy_pct": r["issue %"], "fma_pipe_pct": r["fma %"], "alu_pipe_pct": r["alu %"],
+                                   "xu_pipe_pct": r["xu %"], "dram_pct": r["dram %"], "source": f"profiles/r1_ncu_{args.workload}_step.json"}
+    except Exception:
+        pass
 
     line = {
         "metric": "rasterizer fwd+bwd Mpix/s", "value": world * mpix / (ms_step * 1e-3), "unit": "Mpix/s",
