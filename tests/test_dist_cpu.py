@@ -31,7 +31,9 @@ def _worker(rank, world, port, n_views, out):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     shapes = {"means3D": (37, 3), "scales": (37, 3), "rotations": (37, 4), "opacities": (37, 1), "shs": (37, 16, 3)}
+    assert not csb_dist.peer_capable("cpu")  # CPU ranks never take the peer-memory path
     bucket = csb_dist.FlatGradBucket(shapes, "cpu")
+    assert bucket.peer is None
     mine = csb_dist.shard_units(n_views, rank, world)
     for v in mine:
         bucket.add_(_fake_view_grads(v, shapes))
