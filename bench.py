@@ -384,8 +384,11 @@ def run_b200(args, rank, world, dev):
             if len(view_batches) > 1:
                 dm2, dcol, dop, dm3, dcov, dsh, dsc, drot = gb
                 pack((dm3, dsc, drot, dop, dsh))
+        # the counts (long since written) are checked BEFORE the collective is enqueued: a rank that has to render again
+        # must not have issued an all-reduce its peers will not match
+        R = sum(p.wait() for p in pending)
         bucket.all_reduce()
-        return sum(p.wait() for p in pending)
+        return R
 
     def timed(step_fn, steps, warmup):
         for _ in range(warmup):

@@ -257,6 +257,9 @@ def _backward_views(views, means3D, radii, colors, scales, rotations, scale_modi
                 raise ValueError("view_events needs one entry per view")
             import ctypes
 
+            for ev in view_events:
+                if ev is not None and not ev.cuda_event:  # torch creates the handle on the first record()
+                    raise ValueError("view_events: every event must have been recorded before the backward is enqueued")
             evs = (ctypes.c_void_p * V)(*[None if ev is None else ev.cuda_event for ev in view_events])
             rc = lib.csb_rasterize_backward_staged(*args, evs, _abi.current_stream_ptr())
         else:
