@@ -712,8 +712,7 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_edge2_kernel(const __grid_cons
 #pragma unroll 1
             for (int h = 0; h < 2; ++h) {
                 float f[64];
-                tmem_ld32(taddr + h * 64, f);
-                tmem_ld32(taddr + h * 64 + 32, f + 32);
+                tmem_ld_cols<2>(taddr + h * 64, f);
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     float q[8];
@@ -747,10 +746,7 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_edge2_kernel(const __grid_cons
         //      statistic (a 128-long dependent FADD chain is ~0.25 us of pure latency with two warps per scheduler)
         const float* b2 = sF + 2 * LAT;
         float f[LAT];
-        tmem_ld32(taddr, f);
-        tmem_ld32(taddr + 32, f + 32);
-        tmem_ld32(taddr + 64, f + 64);
-        tmem_ld32(taddr + 96, f + 96);
+        tmem_ld_cols<4>(taddr, f);
         float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
         for (int j = 0; j < LAT; ++j) { f[j] += b2[j]; s4[j & 3] += f[j]; }
