@@ -124,8 +124,8 @@ class MultiGaussianMesh(torch.nn.Module):
     """What `render()` reads from the reference class (scene_reconstruction/gaussian_mesh.py:105-262 and the
     GaussianModel accessors, gaussian_model.py:96-118): `mesh.pos`, `mesh.face`, `face_ids`, `face_bary`,
     `_features_dc/_features_rest/_scaling/_rotation/_opacity`, `get_xyz`, `get_rotation`, `get_scaling`,
-    `get_opacity`, `get_features`, `active_sh_degree`.  Optimiser set-up, densification and PLY / hdf5 IO of the
-    reference class are bookkeeping outside the hot path."""
+    `get_opacity`, `get_features`, `active_sh_degree`, `training_setup`, `save_ply` / `load_ply` (the reference's PLY
+    columns).  Densification of the reference class is bookkeeping outside the hot path."""
 
     def __init__(self, pos, face, face_ids, face_bary, sh_degree: int = 3):
         super().__init__()
@@ -216,6 +216,74 @@ class MultiGaussianMesh(torch.nn.Module):
             assert deformed_vertices.shape[0] == self.mesh.pos.shape[0]
         verts = self.mesh.pos if deformed_vertices is None else deformed_vertices
         return barycentric_xyz(verts, self.mesh.face, self.face_ids, self.face_bary)
+
+    # ---- on-disk format of the reference --------------------------------------------------
+    def save_ply(self, path):
+        """`<path>/point_cloud.ply` with the reference's columns (gaussian_mesh.py:438-460): positions, zero normals,
+        f_dc / f_rest channel-major, opacity, log-scales, quaternion, barycentric coordinates, face offset, face id.
+        The mesh goes to `<path>/mesh.hdf5` (datasets `pos`, `face`; :462-465) when h5py is importable, otherwise to
+        `<path>/mesh.npz` with the same names (h5py is not in this image)."""
+        import os
+
+        import numpy as np
+
+        from . import ply_io
+
+        n = lambda t: t.detach().cpu().numpy()  # noqa: E731
+        face_offset = getattr(self, "face_offset", None)
+        face_offset = n(face_offset) if face_offset is not None else np.zeros((self.num_gaussians, 1), np.float32)
+        f_dc = n(self._features_dc.detach().transpose(1, 2).flatten(start_dim=1).contiguous())
+        f_rest = n(self._features_rest.detach().transpose(1, 2).flatten(start_dim=1).contiguous())
+        xyz = n(self.get_xyz())
+        table = np.concatenate((xyz, np.zeros_like(xyz), f_dc, f_rest, n(self._opacity), n(self._scaling), n(self._rotation),
+                                n(self.face_bary), face_offset, n(self.face_ids).astype(np.float32)[:, None]), axis=1)
+        names = ply_io.gaussian_attribute_names(f_dc.shape[1], f_rest.shape[1], self._scaling.shape[1], self._rotation.shape[1])
+        ply_io.write_vertex_ply(os.path.join(path, "point_cloud.ply"), names, table)
+        mesh = {"pos": n(self.mesh.pos), "face": n(self.mesh.face)}
+        try:
+            import h5py
+
+            with h5py.File(os.path.join(path, "mesh.hdf5"), "w") as f:
+                for k, v in mesh.items():
+                    f.create_dataset(k, data=v)
+        except ImportError:
+            np.savez(os.path.join(path, "mesh.npz"), **mesh)
+
+    @classmethod
+    def load_ply(cls, path, sh_degree=3, device="cuda"):
+        """The inverse (gaussian_model.py:215-262 + gaussian_mesh.py:467-480): reads `point_cloud.ply` and the mesh
+        next to it; SH columns are sorted by their index and reshaped channel-major like the reference does."""
+        import os
+
+        import numpy as np
+
+        from . import ply_io
+
+        col = ply_io.read_vertex_ply(os.path.join(path, "point_cloud.ply"))
+        if os.path.exists(os.path.join(path, "mesh.hdf5")):
+            import h5py
+
+            with h5py.File(os.path.join(path, "mesh.hdf5"), "r") as f:
+                mesh = {k: np.asarray(f[k]) for k in ("pos", "face")}
+        else:
+            mesh = dict(np.load(os.path.join(path, "mesh.npz")))
+        T = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a), dtype=dt, device=device)  # noqa: E731
+
+        def stack(prefix):
+            names = sorted((k for k in col if k.startswith(prefix)), key=lambda k: int(k.split("_")[-1]))
+            return np.stack([col[k] for k in names], axis=1)
+
+        rest = stack("f_rest_")
+        if rest.shape[1] != 3 * (sh_degree + 1) ** 2 - 3:
+            raise ValueError("f_rest columns do not match sh_degree")
+        self = cls(T(mesh["pos"]), T(mesh["face"], torch.long), T(col["id"], torch.long),
+                   T(np.stack((col["b1"], col["b2"], col["b3"]), axis=1)), sh_degree)
+        self.set_gaussians(T(stack("f_dc_").reshape(-1, 3, 1)).transpose(1, 2).contiguous(),
+                           T(rest.reshape(rest.shape[0], 3, -1)).transpose(1, 2).contiguous(),
+                           T(stack("scale_")), T(stack("rot_")), T(col["opacity"][:, None]))
+        self.face_offset = torch.nn.Parameter(T(col["o"][:, None]))
+        self.active_sh_degree = sh_degree
+        return self
 
     def get_rotation(self, deformed_vertices=None):
         """normalize(_rotation), composed with each face's rest -> deformed rotation when a deformed mesh is given
