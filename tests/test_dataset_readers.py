@@ -63,3 +63,28 @@ def test_ids_from_matrices_when_names_carry_none(tmp_path):
     assert cams[3].image_path.endswith("img3.jpg")
     # frames that share a transform share a view id
     assert cams[0].view_id == cams[1].view_id != cams[2].view_id
+
+
+def test_raster_settings_agree_with_the_synthetic_cameras(tmp_path):
+    """A csb_synth ring camera written out as a Blender-style transform and read back gives the settings the bench and the
+    parity tests render with (same transposed matrices, same tan(fov/2), same camera centre)."""
+    import csb_synth as S
+    from scene_reconstruction import dataset_readers as dr
+
+    cams = S.ring_cameras(3, 96, 64, 0.6911, np.array([0.1, 0.0, 0.05], np.float32), fovy=0.5)
+    frames = []
+    for v, c in enumerate(cams):
+        w2c = c.world_view_transform.T.astype(np.float64)
+        c2w = np.linalg.inv(w2c)
+        c2w[:3, 1:3] *= -1  # COLMAP axes -> the OpenGL axes the file format uses
+        frames.append({"file_path": f"./train/r_{v}_0", "time": 0.0, "transform_matrix": c2w.tolist()})
+    (tmp_path / "t.json").write_text(json.dumps({"camera_angle_x": 0.6911, "camera_angle_y": 0.5, "frames": frames}))
+    got = dr.read_cameras_from_transforms(str(tmp_path), "t.json")
+    for c, g in zip(cams, got):
+        s = dr.raster_settings(g, c.image_width, c.image_height, (1.0, 1.0, 1.0), 3, device="cpu")
+        assert s._fields[:4] == ("image_height", "image_width", "tanfovx", "tanfovy")
+        assert (s.image_height, s.image_width, s.sh_degree) == (64, 96, 3)
+        assert abs(s.tanfovx - c.tanfovx) < 1e-12 and abs(s.tanfovy - c.tanfovy) < 1e-12
+        assert np.allclose(s.viewmatrix.numpy(), c.world_view_transform, atol=2e-6)
+        assert np.allclose(s.projmatrix.numpy(), c.full_proj_transform, atol=5e-6)
+        assert np.allclose(s.campos.numpy(), c.camera_center, atol=2e-6)
