@@ -217,6 +217,113 @@ class MultiGaussianMesh(torch.nn.Module):
         verts = self.mesh.pos if deformed_vertices is None else deformed_vertices
         return barycentric_xyz(verts, self.mesh.face, self.face_ids, self.face_bary)
 
+    # ---- densification / pruning bookkeeping (gaussian_model.py:266-430, gaussian_mesh.py:336-431) ----
+    # Host-side tensor surgery on the parameters and on the Adam state (csb_optim.Adam keeps torch's state keys, so
+    # the moments move with the rows).  Pinned on the reference's own methods: tests/make_golden_densify.py.
+    _GROUP_ATTR = {"face_bary": "face_bary", "face_offset": "face_offset", "f_dc": "_features_dc", "f_rest": "_features_rest",
+                   "opacity": "_opacity", "scaling": "_scaling", "rotation": "_rotation"}
+
+    def init_densification_stats(self, percent_dense=0.01):
+        """The statistics `training_setup` zeroes (gaussian_mesh.py:122-124) + `max_radii2D`."""
+        dev, P = self.face_bary.device, self.num_gaussians
+        self.percent_dense = percent_dense
+        self.pos_gradient_accum = torch.zeros((P, 1), device=dev)
+        self.denom = torch.zeros((P, 1), device=dev)
+        self.max_radii2D = torch.zeros((P,), device=dev)
+
+    def _adopt(self, tensors):
+        for name, t in tensors.items():
+            setattr(self, self._GROUP_ATTR[name], t)
+
+    def replace_tensor_to_optimizer(self, tensor, name):
+        out = {}
+        for group in self.optimizer.param_groups:
+            if group["name"] == name:
+                state = self.optimizer.state.get(group["params"][0], None)
+                state["exp_avg"] = torch.zeros_like(tensor)
+                state["exp_avg_sq"] = torch.zeros_like(tensor)
+                del self.optimizer.state[group["params"][0]]
+                group["params"][0] = torch.nn.Parameter(tensor.requires_grad_(True))
+                self.optimizer.state[group["params"][0]] = state
+                out[name] = group["params"][0]
+        return out
+
+    def _prune_optimizer(self, mask):
+        out = {}
+        for group in self.optimizer.param_groups:
+            if len(group["params"]) > 1:
+                continue
+            old = group["params"][0]
+            state = self.optimizer.state.get(old, None)
+            if state is not None:
+                state["exp_avg"] = state["exp_avg"][mask]
+                state["exp_avg_sq"] = state["exp_avg_sq"][mask]
+                del self.optimizer.state[old]
+            group["params"][0] = torch.nn.Parameter(old[mask].requires_grad_(True))
+            if state is not None:
+                self.optimizer.state[group["params"][0]] = state
+            out[group["name"]] = group["params"][0]
+        return out
+
+    def cat_tensors_to_optimizer(self, tensors_dict):
+        out = {}
+        for group in self.optimizer.param_groups:
+            assert len(group["params"]) == 1
+            ext = tensors_dict[group["name"]]
+            old = group["params"][0]
+            state = self.optimizer.state.get(old, None)
+            if state is not None:
+                state["exp_avg"] = torch.cat((state["exp_avg"], torch.zeros_like(ext)), dim=0)
+                state["exp_avg_sq"] = torch.cat((state["exp_avg_sq"], torch.zeros_like(ext)), dim=0)
+                del self.optimizer.state[old]
+            group["params"][0] = torch.nn.Parameter(torch.cat((old, ext), dim=0).requires_grad_(True))
+            if state is not None:
+                self.optimizer.state[group["params"][0]] = state
+            out[group["name"]] = group["params"][0]
+        return out
+
+    def prune_points(self, mask):
+        keep = ~mask
+        self._adopt(self._prune_optimizer(keep))
+        self.face_ids = self.face_ids[keep]
+        self.denom = self.denom[keep]
+        self.max_radii2D = self.max_radii2D[keep]
+        self.pos_gradient_accum = self.pos_gradient_accum[keep]
+
+    def densification_postfix(self, new_face_bary, new_face_offset, new_face_ids, new_features_dc, new_features_rest,
+                              new_opacities, new_scaling, new_rotation):
+        self._adopt(self.cat_tensors_to_optimizer({
+            "face_bary": new_face_bary, "face_offset": new_face_offset, "f_dc": new_features_dc, "f_rest": new_features_rest,
+            "opacity": new_opacities, "scaling": new_scaling, "rotation": new_rotation}))
+        self.face_ids = torch.cat((self.face_ids, new_face_ids), dim=0)
+        dev, P = self.face_bary.device, self.face_bary.shape[0]
+        self.pos_gradient_accum = torch.zeros((P, 1), device=dev)
+        self.denom = torch.zeros((P, 1), device=dev)
+        self.max_radii2D = torch.zeros((P,), device=dev)
+
+    def densify_and_clone(self, grads, grad_threshold, scene_extent):
+        sel = torch.where(torch.norm(grads, dim=-1) >= grad_threshold, True, False)
+        sel = torch.logical_and(sel, torch.max(self.get_scaling, dim=1).values <= self.percent_dense * scene_extent)
+        self.densification_postfix(self.face_bary[sel], self.face_offset[sel], self.face_ids[sel], self._features_dc[sel],
+                                   self._features_rest[sel], self._opacity[sel], self._scaling[sel], self._rotation[sel])
+
+    def add_densification_stats(self, viewspace_point_tensor, update_filter):
+        self.pos_gradient_accum[update_filter] += torch.norm(viewspace_point_tensor[update_filter, :2], dim=-1, keepdim=True)
+        self.denom[update_filter] += 1
+
+    def reset_opacity(self):
+        op = self.get_opacity
+        new = torch.min(op, torch.ones_like(op) * 0.01)
+        self._adopt(self.replace_tensor_to_optimizer(torch.log(new / (1 - new)), "opacity"))
+
+    def prune(self, max_grad, min_opacity, extent, max_screen_size):
+        mask = (self.get_opacity < min_opacity).squeeze()
+        if max_screen_size:
+            big_vs = self.max_radii2D > max_screen_size
+            big_ws = self.get_scaling.max(dim=1).values > 0.1 * extent
+            mask = torch.logical_or(torch.logical_or(mask, big_vs), big_ws)
+        self.prune_points(mask)
+
     # ---- on-disk format of the reference (SURVEY.md 8(f) #4) --------------------------------------------------
     def save_ply(self, path):
         """`<path>/point_cloud.ply` with the reference's columns (gaussian_mesh.py:438-460): positions, zero normals,

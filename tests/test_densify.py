@@ -1,0 +1,76 @@
+"""Densification / pruning bookkeeping of the mesh-anchored Gaussians: parameters, Adam moments and
+the per-Gaussian statistics after `add_densification_stats`, `densify_and_clone`, `reset_opacity`, `prune`, against what
+the reference's own methods produced for the same seeded state (tests/make_golden_densify.py lifts them from the reference
+source; tests/golden/densify_seed9.npz).  Host-side tensor surgery: runs on the CPU with torch.optim.Adam standing in for
+csb_optim.Adam (same state keys)."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+import conftest  # noqa: F401
+
+sys.path.insert(0, conftest.PKG)
+G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "densify_seed9.npz"))
+NAMES = ["face_bary", "face_offset", "f_dc", "f_rest", "opacity", "scaling", "rotation"]
+
+
+def fresh():
+    from scene_reconstruction.gaussian_mesh import MultiGaussianMesh
+
+    T = lambda k: torch.from_numpy(G[k].copy())  # noqa: E731
+    m = MultiGaussianMesh(torch.zeros((9, 3)), torch.zeros((3, 4), dtype=torch.long), T("in/face_ids"), T("in/face_bary"))
+    m.set_gaussians(T("in/f_dc"), T("in/f_rest"), T("in/scaling"), T("in/rotation"), T("in/opacity"))
+    m.face_offset = torch.nn.Parameter(T("in/face_offset"))
+    m.init_densification_stats(0.01)
+    m.max_radii2D = T("in/radii")
+    params = [getattr(m, m._GROUP_ATTR[n]) for n in NAMES]
+    m.optimizer = torch.optim.Adam([{"params": [p], "lr": 1e-3, "name": n} for p, n in zip(params, NAMES)], lr=0.0, eps=1e-15)
+    for p, n in zip(params, NAMES):
+        m.optimizer.state[p] = {"step": torch.tensor(5.0), "exp_avg": T(f"in/m1/{n}"), "exp_avg_sq": T(f"in/m2/{n}")}
+    return m
+
+
+def check(m, tag):
+    groups = {g["name"]: g["params"][0] for g in m.optimizer.param_groups}
+    for n in NAMES:
+        p = groups[n]
+        assert p is getattr(m, m._GROUP_ATTR[n]), n          # the attribute IS the optimiser's parameter
+        assert p.requires_grad and isinstance(p, torch.nn.Parameter)
+        st = m.optimizer.state[p]
+        assert np.array_equal(p.detach().numpy(), G[f"{tag}/{n}"]), (tag, n)
+        assert np.array_equal(st["exp_avg"].numpy(), G[f"{tag}/{n}/exp_avg"]), (tag, n)
+        assert np.array_equal(st["exp_avg_sq"].numpy(), G[f"{tag}/{n}/exp_avg_sq"]), (tag, n)
+        assert float(st["step"]) == 5.0
+    assert len(m.optimizer.state) == len(NAMES)              # no stale entries of replaced parameters
+    for a in ("face_ids", "pos_gradient_accum", "denom", "max_radii2D"):
+        assert np.array_equal(getattr(m, a).numpy(), G[f"{tag}/{a}"]), (tag, a)
+
+
+def test_stats_then_clone():
+    m = fresh()
+    m.add_densification_stats(torch.from_numpy(G["in/view_grad"]), torch.from_numpy(G["in/update_filter"]))
+    check(m, "stats")
+    grads = m.pos_gradient_accum / m.denom
+    grads[grads.isnan()] = 0.0
+    m.densify_and_clone(grads, 1.2, 20.0)
+    assert m.num_gaussians == G["clone/opacity"].shape[0] > G["in/opacity"].shape[0]
+    check(m, "clone")
+
+
+def test_reset_opacity():
+    m = fresh()
+    m.reset_opacity()
+    check(m, "reset_opacity")
+    assert float(m.get_opacity.detach().max()) <= 0.01 + 1e-7
+
+
+def test_prune_with_and_without_screen_size():
+    m = fresh()
+    m.prune(0.0, 0.45, 1.0, 25.0)
+    assert m.num_gaussians == G["prune/opacity"].shape[0]
+    check(m, "prune")
+    m = fresh()
+    m.prune(0.0, 0.45, 1.0, None)
+    check(m, "prune_opacity_only")
