@@ -115,6 +115,40 @@ def barycentric_xyz(vertices, face, face_ids, face_bary):
     return _MeshXYZ.apply(vertices, face, face_ids, face_bary)
 
 
+def _build_rotation(r):
+    """utils/general_utils.py:81-102 (quaternion r, x, y, z -> rotation matrix)."""
+    norm = torch.sqrt(r[:, 0] * r[:, 0] + r[:, 1] * r[:, 1] + r[:, 2] * r[:, 2] + r[:, 3] * r[:, 3])
+    q = r / norm[:, None]
+    R = torch.zeros((q.size(0), 3, 3), device=r.device)
+    r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    R[:, 0, 0] = 1 - 2 * (y * y + z * z)
+    R[:, 0, 1] = 2 * (x * y - r * z)
+    R[:, 0, 2] = 2 * (x * z + r * y)
+    R[:, 1, 0] = 2 * (x * y + r * z)
+    R[:, 1, 1] = 1 - 2 * (x * x + z * z)
+    R[:, 1, 2] = 2 * (y * z - r * x)
+    R[:, 2, 0] = 2 * (x * z - r * y)
+    R[:, 2, 1] = 2 * (y * z + r * x)
+    R[:, 2, 2] = 1 - 2 * (x * x + y * y)
+    return R
+
+
+def _barycentric_coordinates(points, triangles):
+    """meshnet/data_utils.py:494-530, including its component order (u for A, then the AC weight, then the AB weight)."""
+    A, B, C = triangles[:, 0, :], triangles[:, 1, :], triangles[:, 2, :]
+    AB, AC, AP = B - A, C - A, points - A
+    dot00 = torch.sum(AC * AC, dim=1)
+    dot01 = torch.sum(AC * AB, dim=1)
+    dot02 = torch.sum(AC * AP, dim=1)
+    dot11 = torch.sum(AB * AB, dim=1)
+    dot12 = torch.sum(AB * AP, dim=1)
+    denom = dot00 * dot11 - dot01 * dot01
+    v = (dot11 * dot02 - dot01 * dot12) / denom
+    w = (dot00 * dot12 - dot01 * dot02) / denom
+    u = 1.0 - v - w
+    return torch.stack([u, v, w], dim=1)
+
+
 class _Mesh:
     def __init__(self, pos, face):
         self.pos, self.face = pos, face
@@ -306,6 +340,35 @@ class MultiGaussianMesh(torch.nn.Module):
         sel = torch.logical_and(sel, torch.max(self.get_scaling, dim=1).values <= self.percent_dense * scene_extent)
         self.densification_postfix(self.face_bary[sel], self.face_offset[sel], self.face_ids[sel], self._features_dc[sel],
                                    self._features_rest[sel], self._opacity[sel], self._scaling[sel], self._rotation[sel])
+
+    def densify_and_split(self, grads, grad_threshold, scene_extent, N=2):
+        """gaussian_mesh.py:379-412: large Gaussians with a large view-space gradient are replaced by N samples drawn from
+        them (torch.normal on the global generator), re-anchored to their face by barycentric coordinates (in the
+        reference's [A, C, B] component order, meshnet/data_utils.py:494-530) and shrunk by 0.8 N."""
+        n_init = self.face_bary.shape[0]
+        dev = self.face_bary.device
+        padded = torch.zeros((n_init,), device=dev)
+        padded[:grads.shape[0]] = grads.squeeze()
+        sel = torch.where(padded >= grad_threshold, True, False)
+        sel = torch.logical_and(sel, torch.max(self.get_scaling, dim=1).values > self.percent_dense * scene_extent)
+        stds = self.get_scaling[sel].repeat(N, 1)
+        samples = torch.normal(mean=torch.zeros((stds.size(0), 3), device=dev), std=stds)
+        rots = _build_rotation(self._rotation[sel]).repeat(N, 1, 1)
+        new_xyz = self.get_xyz()[sel].repeat(N, 1) + torch.bmm(rots, samples.unsqueeze(-1)).squeeze(-1)
+        triangles = self.mesh.pos[self.mesh.face[:, self.face_ids[sel]]].transpose(0, 1).repeat(N, 1, 1)
+        new_bary = _barycentric_coordinates(new_xyz, triangles)
+        self.densification_postfix(
+            new_bary, self.face_offset[sel].repeat(N, 1), self.face_ids[sel].repeat(N),
+            self._features_dc[sel].repeat(N, 1, 1), self._features_rest[sel].repeat(N, 1, 1), self._opacity[sel].repeat(N, 1),
+            torch.log(self.get_scaling[sel].repeat(N, 1) / (0.8 * N)), self._rotation[sel].repeat(N, 1))
+        self.prune_points(torch.cat((sel, torch.zeros(N * int(sel.sum()), device=dev, dtype=bool))))
+
+    def densify(self, max_grad, min_opacity, extent, max_screen_size):
+        """gaussian_model.py:420-425."""
+        grads = self.pos_gradient_accum / self.denom
+        grads[grads.isnan()] = 0.0
+        self.densify_and_clone(grads, max_grad, extent)
+        self.densify_and_split(grads, max_grad, extent)
 
     def add_densification_stats(self, viewspace_point_tensor, update_filter):
         self.pos_gradient_accum[update_filter] += torch.norm(viewspace_point_tensor[update_filter, :2], dim=-1, keepdim=True)

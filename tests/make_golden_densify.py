@@ -3,7 +3,8 @@
 The reference modules cannot be imported here (roma, h5py, plyfile, simple_knn ... are missing), so the METHODS are lifted
 from the reference's source files at run time (ast) and bound to a stub object: `replace_tensor_to_optimizer`,
 `_prune_optimizer`, `cat_tensors_to_optimizer`, `reset_opacity`, `add_densification_stats`, `prune` of
-scene_reconstruction/gaussian_model.py and `prune_points`, `densification_postfix`, `densify_and_clone` of
+scene_reconstruction/gaussian_model.py and `prune_points`, `densification_postfix`, `densify_and_clone`, `densify_and_split` (+ `get_xyz`, `build_rotation`,
+`compute_barycentric_coordinates`) of
 MultiGaussianMesh (scene_reconstruction/gaussian_mesh.py:336-431).  They run on the CPU with torch.optim.Adam exactly as
 written (only `device="cuda"` in the two `torch.zeros` calls of densification_postfix is rewritten to "cpu").
 Run: python tests/make_golden_densify.py -> tests/golden/densify_seed9.npz"""
@@ -29,7 +30,7 @@ def lift(path, cls, names):
                 if isinstance(f, ast.FunctionDef) and f.name in names:
                     f.decorator_list = []
                     mod = ast.Module(body=[f], type_ignores=[])
-                    ns = {"torch": torch, "nn": nn, "np": np,
+                    ns = {"torch": torch, "nn": nn, "np": np, "Optional": __import__("typing").Optional,
                           "inverse_sigmoid": lambda x: torch.log(x / (1 - x))}  # utils/general_utils.py:20-21
                     exec(compile(mod, path, "exec"), ns)
                     out[f.name] = ns[f.name]
@@ -41,7 +42,24 @@ base = lift("scene_reconstruction/gaussian_model.py", "GaussianModel",
             ["replace_tensor_to_optimizer", "_prune_optimizer", "cat_tensors_to_optimizer", "reset_opacity",
              "add_densification_stats", "prune"])
 mesh = lift("scene_reconstruction/gaussian_mesh.py", "MultiGaussianMesh",
-            ["prune_points", "densification_postfix", "densify_and_clone"])
+            ["prune_points", "densification_postfix", "densify_and_clone", "densify_and_split", "get_xyz"])
+
+
+def lift_function(path, name):
+    tree = ast.parse(open(os.path.join(REF, path)).read().replace("device='cuda'", "device='cpu'"))
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name == name:
+            ns = {"torch": torch, "np": np}
+            exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), ns)
+            return ns[name]
+    raise KeyError(name)
+
+
+# helpers densify_and_split calls: utils/general_utils.py:81-102, meshnet/data_utils.py:494-530
+for f in mesh.values():
+    f.__globals__["build_rotation"] = lift_function("utils/general_utils.py", "build_rotation")
+    f.__globals__["compute_barycentric_coordinates"] = lift_function("meshnet/data_utils.py", "compute_barycentric_coordinates")
+    f.__globals__["Optional"] = __import__("typing").Optional
 
 
 class Stub:
@@ -62,6 +80,8 @@ init = {"face_bary": torch.rand((P, 3), generator=g), "face_offset": torch.randn
 face_ids = torch.randint(0, 7, (P,), generator=g)
 m1 = {k: torch.randn(v.shape, generator=g) for k, v in init.items()}       # Adam state as after some steps
 m2 = {k: torch.rand(v.shape, generator=g) for k, v in init.items()}
+mesh_pos = torch.rand((9, 3), generator=g)
+mesh_face = torch.tensor([[0, 1, 3, 4, 1, 2, 4], [1, 2, 4, 5, 4, 5, 7], [3, 4, 6, 7, 3, 4, 6]])
 view_grad = torch.randn((P, 3), generator=g)
 update_filter = torch.rand(P, generator=g) > 0.3
 radii = torch.rand(P, generator=g) * 40
@@ -73,6 +93,8 @@ def fresh():
     s._features_dc, s._features_rest = nn.Parameter(init["f_dc"].clone()), nn.Parameter(init["f_rest"].clone())
     s._opacity, s._scaling, s._rotation = (nn.Parameter(init[k].clone()) for k in ("opacity", "scaling", "rotation"))
     s.face_ids = face_ids.clone()
+    s.mesh = types.SimpleNamespace(pos=mesh_pos.clone(), face=mesh_face.clone())
+    s.scaling_inverse_activation = torch.log
     s.percent_dense = 0.01
     s.pos_gradient_accum, s.denom, s.max_radii2D = torch.zeros((P, 1)), torch.zeros((P, 1)), radii.clone()
     names = ["face_bary", "face_offset", "f_dc", "f_rest", "opacity", "scaling", "rotation"]
@@ -105,6 +127,13 @@ grads[grads.isnan()] = 0.0
 s.densify_and_clone(grads, 1.2, 20.0)
 snapshot(s, "clone", out)
 s = fresh()
+s.add_densification_stats(view_grad, update_filter)
+grads = s.pos_gradient_accum / s.denom
+grads[grads.isnan()] = 0.0
+torch.manual_seed(1234)  # torch.normal inside draws from the global CPU generator
+s.densify_and_split(grads, 1.2, 0.5)
+snapshot(s, "split", out)
+s = fresh()
 s.reset_opacity()
 snapshot(s, "reset_opacity", out)
 s = fresh()
@@ -119,7 +148,7 @@ commit = json.load(open(os.path.join(REF, ".SUBMODULES.json")))["commit"][:7]
 inputs = {f"in/{k}": v.numpy() for k, v in init.items()}
 inputs.update({f"in/m1/{k}": v.numpy() for k, v in m1.items()})
 inputs.update({f"in/m2/{k}": v.numpy() for k, v in m2.items()})
-inputs.update({"in/face_ids": face_ids.numpy(), "in/view_grad": view_grad.numpy(), "in/update_filter": update_filter.numpy(),
+inputs.update({"in/mesh_pos": mesh_pos.numpy(), "in/mesh_face": mesh_face.numpy(), "in/face_ids": face_ids.numpy(), "in/view_grad": view_grad.numpy(), "in/update_filter": update_filter.numpy(),
                "in/radii": radii.numpy()})
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "densify_seed9.npz")
 np.savez_compressed(path, ref_commit=f"KTH-RPL/cloth-splatting {commit}", **inputs, **out)

@@ -20,7 +20,13 @@ def fresh():
     from scene_reconstruction.gaussian_mesh import MultiGaussianMesh
 
     T = lambda k: torch.from_numpy(G[k].copy())  # noqa: E731
-    m = MultiGaussianMesh(torch.zeros((9, 3)), torch.zeros((3, 4), dtype=torch.long), T("in/face_ids"), T("in/face_bary"))
+    class CpuMesh(MultiGaussianMesh):  # get_xyz of the reference in torch (gaussian_mesh.py:151-169): no GPU here
+        def get_xyz(self, deformed_vertices=None):
+            vid = self.mesh.face[:, self.face_ids].transpose(0, 1)
+            nb = self.face_bary / self.face_bary.sum(dim=1, keepdim=True)
+            return (nb.unsqueeze(1) @ self.mesh.pos[vid, :]).squeeze(1)
+
+    m = CpuMesh(T("in/mesh_pos"), T("in/mesh_face"), T("in/face_ids"), T("in/face_bary"))
     m.set_gaussians(T("in/f_dc"), T("in/f_rest"), T("in/scaling"), T("in/rotation"), T("in/opacity"))
     m.face_offset = torch.nn.Parameter(T("in/face_offset"))
     m.init_densification_stats(0.01)
@@ -74,3 +80,14 @@ def test_prune_with_and_without_screen_size():
     m = fresh()
     m.prune(0.0, 0.45, 1.0, None)
     check(m, "prune_opacity_only")
+
+
+def test_split_replaces_large_gaussians_by_samples():
+    m = fresh()
+    m.add_densification_stats(torch.from_numpy(G["in/view_grad"]), torch.from_numpy(G["in/update_filter"]))
+    grads = m.pos_gradient_accum / m.denom
+    grads[grads.isnan()] = 0.0
+    torch.manual_seed(1234)  # the same global-generator state the golden run drew its samples from
+    m.densify_and_split(grads, 1.2, 0.5)
+    assert m.num_gaussians == G["split/opacity"].shape[0] != G["in/opacity"].shape[0]
+    check(m, "split")
