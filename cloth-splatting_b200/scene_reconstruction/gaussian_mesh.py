@@ -370,6 +370,32 @@ class MultiGaussianMesh(torch.nn.Module):
         self.densify_and_clone(grads, max_grad, extent)
         self.densify_and_split(grads, max_grad, extent)
 
+    @torch.no_grad()
+    def cleanup_barycentric_coordinates(self):
+        """gaussian_mesh.py:267-322 (called from the training loop, train_utils.py:307): a negative barycentric
+        coordinate means the Gaussian has left its face through the edge opposite to that vertex; it is handed to the
+        face on the other side of that edge, with the reference's re-anchoring weights (distances to the new face's
+        vertices, normalised) -- or, on a mesh border, the coordinate is reset the way the reference does it (0.005
+        divided by itself: 1.0).  Host-side loop over the few affected Gaussians, in the reference's order."""
+        face = self.mesh.face
+        faces_of_vertex = [torch.nonzero(torch.eq(face, i), as_tuple=False)[:, 1].tolist() for i in range(self.mesh.pos.shape[0])]
+        rows, comps = torch.where(self.face_bary < 0)
+        old_ids = self.face_ids[rows]
+        old_faces = face[:, old_ids].transpose(0, 1)
+        xyz = self.get_xyz()
+        for row, comp, tri, fid in zip(rows, comps, old_faces, old_ids):
+            keep = tri[tri != tri[comp]]  # the two vertices of the edge that was crossed
+            across = set(faces_of_vertex[keep[0]]).intersection(set(faces_of_vertex[keep[1]]))
+            across.discard(fid.item())
+            if not across:
+                self.face_bary[row, comp] = 0.005
+                self.face_bary[row, comp] = self.face_bary[row, comp] / self.face_bary[row, comp].sum()
+            else:
+                new_face = list(across)[0]
+                self.face_ids[row] = new_face
+                d = torch.linalg.norm(xyz[row].unsqueeze(0) - self.mesh.pos[face[:, new_face]], dim=1)
+                self.face_bary[row] = d / d.sum()
+
     def add_densification_stats(self, viewspace_point_tensor, update_filter):
         self.pos_gradient_accum[update_filter] += torch.norm(viewspace_point_tensor[update_filter, :2], dim=-1, keepdim=True)
         self.denom[update_filter] += 1

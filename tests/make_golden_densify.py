@@ -42,7 +42,8 @@ base = lift("scene_reconstruction/gaussian_model.py", "GaussianModel",
             ["replace_tensor_to_optimizer", "_prune_optimizer", "cat_tensors_to_optimizer", "reset_opacity",
              "add_densification_stats", "prune"])
 mesh = lift("scene_reconstruction/gaussian_mesh.py", "MultiGaussianMesh",
-            ["prune_points", "densification_postfix", "densify_and_clone", "densify_and_split", "get_xyz"])
+            ["prune_points", "densification_postfix", "densify_and_clone", "densify_and_split", "get_xyz",
+             "cleanup_barycentric_coordinates"])
 
 
 def lift_function(path, name):
@@ -144,6 +145,13 @@ s = fresh()
 s.prune(0.0, 0.45, 1.0, None)
 snapshot(s, "prune_opacity_only", out)
 
+# cleanup_barycentric_coordinates (gaussian_mesh.py:267-322): Gaussians that left their face are re-anchored
+s = fresh()
+bary = init["face_bary"].clone()
+bary[[2, 5, 5, 11, 17], [0, 1, 2, 2, 1]] = torch.tensor([-0.2, -0.05, -0.3, -0.4, -0.01])
+s.face_bary = bary                      # a plain tensor: the method writes into it in place
+s.cleanup_barycentric_coordinates()
+out["cleanup/face_bary"], out["cleanup/face_ids"] = s.face_bary.numpy().copy(), s.face_ids.numpy().copy()
 commit = json.load(open(os.path.join(REF, ".SUBMODULES.json")))["commit"][:7]
 inputs = {f"in/{k}": v.numpy() for k, v in init.items()}
 inputs.update({f"in/m1/{k}": v.numpy() for k, v in m1.items()})

@@ -91,3 +91,14 @@ def test_split_replaces_large_gaussians_by_samples():
     m.densify_and_split(grads, 1.2, 0.5)
     assert m.num_gaussians == G["split/opacity"].shape[0] != G["in/opacity"].shape[0]
     check(m, "split")
+
+
+def test_cleanup_reanchors_gaussians_that_left_their_face():
+    m = fresh()
+    with torch.no_grad():
+        m.face_bary[[2, 5, 5, 11, 17], [0, 1, 2, 2, 1]] = torch.tensor([-0.2, -0.05, -0.3, -0.4, -0.01])
+    before = m.face_ids.clone()
+    m.cleanup_barycentric_coordinates()
+    assert np.array_equal(m.face_bary.detach().numpy(), G["cleanup/face_bary"])
+    assert np.array_equal(m.face_ids.numpy(), G["cleanup/face_ids"])
+    assert int((m.face_ids != before).sum()) == 3 and float(m.face_bary.detach().min()) > 0   # both branches were taken
