@@ -50,7 +50,7 @@ def lift_function(path, name):
     tree = ast.parse(open(os.path.join(REF, path)).read().replace("device='cuda'", "device='cpu'"))
     for node in tree.body:
         if isinstance(node, ast.FunctionDef) and node.name == name:
-            ns = {"torch": torch, "np": np}
+            ns = {"torch": torch, "np": np, "OptimizationParams": object}
             exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), ns)
             return ns[name]
     raise KeyError(name)
@@ -152,12 +152,28 @@ bary[[2, 5, 5, 11, 17], [0, 1, 2, 2, 1]] = torch.tensor([-0.2, -0.05, -0.3, -0.4
 s.face_bary = bary                      # a plain tensor: the method writes into it in place
 s.cleanup_barycentric_coordinates()
 out["cleanup/face_bary"], out["cleanup/face_ids"] = s.face_bary.numpy().copy(), s.face_ids.numpy().copy()
+# densification() of the training loop (scene_reconstruction/train_utils.py:324-345) over the methods above
+densification = lift_function("scene_reconstruction/train_utils.py", "densification")
+Stub.densify = lift("scene_reconstruction/gaussian_model.py", "GaussianModel", ["densify"])["densify"]
+OPT = dict(opacity_threshold_fine_init=0.5, opacity_threshold_fine_after=0.3, densify_until_iter=1000,
+           densify_grad_threshold_fine_init=1.4, densify_grad_threshold_after=0.8, densify_from_iter=100,
+           densification_interval=100, opacity_reset_interval=300, pruning_from_iter=100, pruning_interval=200)
+vis = torch.rand(P, generator=g) > 0.2
+new_radii = (torch.rand(P, generator=g) * 60)
+for it in (50, 300, 400):   # statistics only / densify (no size threshold) / densify + prune with size threshold
+    s = fresh()
+    s.pos_gradient_accum += 3.0 * torch.rand((P, 1), generator=torch.Generator().manual_seed(it))
+    s.denom += 2
+    torch.manual_seed(77 + it)
+    densification(s, it, vis, new_radii, view_grad, types.SimpleNamespace(**OPT), 0.5)
+    snapshot(s, f"loop{it}", out)
 commit = json.load(open(os.path.join(REF, ".SUBMODULES.json")))["commit"][:7]
 inputs = {f"in/{k}": v.numpy() for k, v in init.items()}
 inputs.update({f"in/m1/{k}": v.numpy() for k, v in m1.items()})
 inputs.update({f"in/m2/{k}": v.numpy() for k, v in m2.items()})
 inputs.update({"in/mesh_pos": mesh_pos.numpy(), "in/mesh_face": mesh_face.numpy(), "in/face_ids": face_ids.numpy(), "in/view_grad": view_grad.numpy(), "in/update_filter": update_filter.numpy(),
-               "in/radii": radii.numpy()})
+               "in/radii": radii.numpy(), "in/vis": vis.numpy(), "in/new_radii": new_radii.numpy(),
+               "in/opt": json.dumps(OPT)})
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "densify_seed9.npz")
 np.savez_compressed(path, ref_commit=f"KTH-RPL/cloth-splatting {commit}", **inputs, **out)
 print("wrote", path, len(out), "arrays; clone ->", out["clone/opacity"].shape[0], "prune ->", out["prune/opacity"].shape[0],

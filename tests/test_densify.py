@@ -102,3 +102,24 @@ def test_cleanup_reanchors_gaussians_that_left_their_face():
     assert np.array_equal(m.face_bary.detach().numpy(), G["cleanup/face_bary"])
     assert np.array_equal(m.face_ids.numpy(), G["cleanup/face_ids"])
     assert int((m.face_ids != before).sum()) == 3 and float(m.face_bary.detach().min()) > 0   # both branches were taken
+
+
+def test_densification_schedule_of_the_training_loop():
+    """train_utils.densification at three iterations: statistics only (50), clone + split without the screen-size
+    criterion (300), clone + split + prune with it (400) -- the same final state as the reference's function."""
+    import json
+    import types
+
+    from scene_reconstruction.train_utils import densification
+
+    opt = types.SimpleNamespace(**json.loads(str(G["in/opt"])))
+    for it in (50, 300, 400):
+        m = fresh()
+        m.pos_gradient_accum += 3.0 * torch.rand((m.num_gaussians, 1), generator=torch.Generator().manual_seed(it))
+        m.denom += 2
+        torch.manual_seed(77 + it)
+        with torch.no_grad():
+            densification(m, it, torch.from_numpy(G["in/vis"]), torch.from_numpy(G["in/new_radii"]),
+                          torch.from_numpy(G["in/view_grad"]), opt, 0.5)
+        assert m.num_gaussians == G[f"loop{it}/opacity"].shape[0]
+        check(m, f"loop{it}")
