@@ -223,7 +223,22 @@ class MultiGaussianMesh(torch.nn.Module):
             {"params": [self._rotation], "lr": training_args.rotation_lr, "name": "rotation"},
         ]
         self.optimizer = Adam(groups, lr=0.0, eps=1e-15)
+        if hasattr(training_args, "position_lr_final"):
+            from .train_utils import get_expon_lr_func
+
+            self.xyz_scheduler_args = get_expon_lr_func(
+                lr_init=training_args.position_lr_init * scale, lr_final=training_args.position_lr_final * scale,
+                lr_delay_mult=training_args.position_lr_delay_mult, max_steps=training_args.position_lr_max_steps)
         return self.optimizer
+
+    def update_learning_rate(self, iteration):
+        """gaussian_model.py:173-179, kept as it is: the schedule is applied to a group named "xyz" -- which the
+        mesh-anchored model does not have (its position groups are `face_bary` / `face_offset`), so this returns None
+        and the learning rates of `training_setup` stay constant, exactly like in the reference."""
+        for group in self.optimizer.param_groups:
+            if group["name"] == "xyz":
+                group["lr"] = self.xyz_scheduler_args(iteration)
+                return group["lr"]
 
     @property
     def num_gaussians(self):

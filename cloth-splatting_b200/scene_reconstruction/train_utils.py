@@ -35,3 +35,43 @@ def densification(gaussians, iteration, visibility_filter, radii, viewspace_poin
         gaussians.densify(densify_threshold, opacity_threshold, cameras_extent, size_threshold)
     if iteration > opt.pruning_from_iter and iteration % opt.pruning_interval == 0:
         gaussians.prune(densify_threshold, opacity_threshold, cameras_extent, size_threshold)
+
+
+def regularization(all_vertice_deform, gaussians, opt, static=False):
+    """The mesh regularisers added to the photometric loss (scene_reconstruction/train_utils.py:77-102, 238), over the
+    deformed vertices of the views of a step `[n_cams, N, 3]` (consecutive time steps): mean deformation magnitude
+    between neighbouring views, L1 between rest and deformed edge lengths, and an L1 second-difference (momentum)
+    term.  The first and the last need at least three views."""
+    n_cams = all_vertice_deform.shape[0]
+    loss = torch.zeros([], device=all_vertice_deform.device)
+    if static:
+        return loss
+    if opt.lambda_deform_mag > 0. and n_cams >= 3:
+        mag0 = torch.linalg.norm(all_vertice_deform[1] - all_vertice_deform[0], dim=-1).mean()
+        mag1 = torch.linalg.norm(all_vertice_deform[2] - all_vertice_deform[1], dim=-1).mean()
+        loss += opt.lambda_deform_mag * (0.5 * (mag0 + mag1))
+    if opt.lambda_rigid > 0:
+        ei = gaussians.mesh.edge_index
+        deformed_norm = torch.linalg.norm(all_vertice_deform[:, ei[1]] - all_vertice_deform[:, ei[0]], dim=-1, keepdim=True)
+        static_norm = gaussians.edge_norm.unsqueeze(0).expand(n_cams, -1, -1)
+        loss += opt.lambda_rigid * torch.nn.functional.l1_loss(static_norm, deformed_norm)
+    if opt.lambda_momentum > 0 and n_cams >= 3:
+        second = all_vertice_deform[2] - 2 * all_vertice_deform[1] + all_vertice_deform[0]
+        loss += opt.lambda_momentum * torch.linalg.norm(second, dim=-1, ord=1).mean().mean()
+    return loss
+
+
+def get_expon_lr_func(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):
+    """Log-linear learning-rate decay with an optional eased-in start (utils/general_utils.py:32-65)."""
+    import numpy as np
+
+    def helper(step):
+        if step < 0 or (lr_init == 0.0 and lr_final == 0.0):
+            return 0.0
+        delay = 1.0
+        if lr_delay_steps > 0:
+            delay = lr_delay_mult + (1 - lr_delay_mult) * np.sin(0.5 * np.pi * np.clip(step / lr_delay_steps, 0, 1))
+        t = np.clip(step / max_steps, 0, 1)
+        return delay * np.exp(np.log(lr_init) * (1 - t) + np.log(lr_final) * t)
+
+    return helper
