@@ -154,6 +154,12 @@ class _Mesh:
         self.pos, self.face = pos, face
 
 
+def compute_edge_features(points, edge_index):
+    """Receiver - sender displacement of every edge and its length [E,1] (meshnet/data_utils.py:443-448)."""
+    displacement = points[edge_index[1]] - points[edge_index[0]]
+    return displacement, torch.norm(displacement, dim=1, keepdim=True)
+
+
 class MultiGaussianMesh(torch.nn.Module):
     """What `render()` reads from the reference class (scene_reconstruction/gaussian_mesh.py:105-262 and the
     GaussianModel accessors, gaussian_model.py:96-118): `mesh.pos`, `mesh.face`, `face_ids`, `face_bary`,
@@ -196,6 +202,15 @@ class MultiGaussianMesh(torch.nn.Module):
         op = torch.full((P, 1), 0.1, device=dev)
         self.set_gaussians(feats[:, :, 0:1].transpose(1, 2).contiguous(), feats[:, :, 1:].transpose(1, 2).contiguous(),
                            torch.log(torch.sqrt(dist2))[..., None].repeat(1, 3), rots, torch.log(op / (1 - op)))
+        return self
+
+    def set_edges(self, edge_index):
+        """The rest-pose edge features `_setup_callback` derives from the mesh graph (gaussian_mesh.py:214-218):
+        `edge_displacement`, `edge_norm` (read by `train_utils.regularization`) and `mesh.edge_attr` [E,4]."""
+        self.mesh.edge_index = edge_index
+        self.edge_displacement, self.edge_norm = compute_edge_features(self.mesh.pos, edge_index)
+        self.mesh.edge_attr = torch.hstack((self.edge_displacement.clone().detach().to(torch.float32).contiguous(),
+                                            self.edge_norm.clone().detach().to(torch.float32).contiguous()))
         return self
 
     def set_gaussians(self, features_dc, features_rest, scaling, rotation, opacity):

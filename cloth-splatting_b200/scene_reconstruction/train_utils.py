@@ -5,6 +5,7 @@ same keys ('l1', 'ssim_loss').  The reference reads both entries with `.item()` 
 step); `sync=False` keeps them as device scalars instead."""
 import torch
 
+from utils.image_utils import psnr
 from utils.loss_utils import image_loss
 
 
@@ -75,3 +76,54 @@ def get_expon_lr_func(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, ma
         return delay * np.exp(np.log(lr_init) * (1 - t) + np.log(lr_final) * t)
 
     return helper
+
+
+def train_step(iteration, viewpoint_cams, gaussians, simulator, meshnet_optimizer, pipeline_params, opt_params,
+               cameras_extent, background, static=False, white_background=False, user_args=None):
+    """One iteration of the refinement loop (scene_reconstruction/train_utils.py:240-321), same arguments and the same
+    `(psnr, loss, loss_dict)` return: render every view of the step at its time (`gaussian_renderer.render`: simulator ->
+    mesh-anchored Gaussians -> rasterizer), image losses over the stacked views + the mesh regularisers, one backward, the
+    densification / opacity-reset / barycentric-cleanup schedule on the summed screen-space gradients, then the Adam
+    steps of the Gaussians and (unless `static`) of the simulator."""
+    from gaussian_renderer import render
+
+    gaussians.update_learning_rate(iteration)
+    if iteration % 1000 == 0:
+        gaussians.oneupSHdegree()
+    dev = background.device
+    no_shadow = getattr(user_args, "no_shadow", False)
+    pkgs = [render(cam, gaussians, simulator, pipeline_params, background, no_shadow=no_shadow, render_static=static)
+            for cam in viewpoint_cams]
+    image_tensor = torch.stack([p.render for p in pkgs])
+    gt_image_tensor = torch.stack([cam.original_image.to(dev, non_blocking=True) for cam in viewpoint_cams])
+    mask_tensor = None
+    if viewpoint_cams[0].mask is not None:
+        mask_tensor = torch.stack([cam.mask.to(dev, non_blocking=True) for cam in viewpoint_cams])
+    all_vertice_deform = torch.stack([p.vertice_deform for p in pkgs])
+    radii = torch.stack([p.radii for p in pkgs]).max(dim=0).values
+    visibility_filter = torch.stack([p.visibility_filter for p in pkgs]).any(dim=0)
+
+    psnr_ = psnr(image_tensor, gt_image_tensor).mean().double()
+    loss, loss_dict = image_losses(image_tensor, gt_image_tensor, opt_params, mask_tensor)
+    loss = loss + regularization(all_vertice_deform, gaussians, opt_params, static)
+    loss.backward()
+
+    viewspace_point_tensor_grad = torch.zeros_like(pkgs[0].viewspace_points)
+    for p in pkgs:
+        viewspace_point_tensor_grad = viewspace_point_tensor_grad + p.viewspace_points.grad
+    with torch.no_grad():
+        if iteration < opt_params.densify_until_iter:
+            densification(gaussians, iteration, visibility_filter, radii, viewspace_point_tensor_grad, opt_params,
+                          cameras_extent)
+            if iteration % opt_params.opacity_reset_interval == 0 or (
+                    white_background and iteration == opt_params.densify_from_iter):
+                gaussians.reset_opacity()
+        if iteration % opt_params.bary_cleanup == 0:
+            gaussians.cleanup_barycentric_coordinates()
+        if iteration < opt_params.iterations:
+            gaussians.optimizer.step()
+            if not static:
+                meshnet_optimizer.step()
+            gaussians.optimizer.zero_grad(set_to_none=True)
+            meshnet_optimizer.zero_grad()
+    return psnr_, loss, loss_dict

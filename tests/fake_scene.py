@@ -1,0 +1,143 @@
+"""A CPU stand-in scene for the GLUE of `train_step` (tests/make_golden_train_step.py, tests/test_train_step_cpu.py): the
+mirror's MultiGaussianMesh / ResidualMeshSimulator on the CPU, a differentiable toy `render` with the fields train_step
+reads, and the image loss of oracle/loss_oracle.py.  The kernels are not involved -- their parity is tested elsewhere;
+this pins the order of operations of the step (losses, schedule, optimiser calls) on the reference's own function."""
+import os
+import sys
+import types
+
+import torch
+
+import conftest  # noqa: F401
+
+sys.path.insert(0, conftest.PKG)
+H, W = 24, 32
+
+
+class Img:
+    """`cam.original_image`: the reference calls `.cuda()`, the mirror `.to(device)`."""
+    def __init__(self, t):
+        self.t = t
+
+    def cuda(self):
+        return self.t
+
+    def to(self, *a, **k):
+        return self.t
+
+
+def options(**over):
+    o = dict(lambda_dssim=0.2, lambda_deform_mag=0.1, lambda_rigid=0.5, lambda_momentum=0.05, densify_until_iter=15000,
+             densify_from_iter=500, densification_interval=100, pruning_from_iter=500, pruning_interval=300,
+             opacity_reset_interval=3000, bary_cleanup=700, iterations=30000, opacity_threshold_fine_init=0.5,
+             opacity_threshold_fine_after=0.4, densify_grad_threshold_fine_init=1e-4, densify_grad_threshold_after=5e-5,
+             position_lr_init=1.6e-4, feature_lr=2.5e-3, opacity_lr=0.05, scaling_lr=5e-3, rotation_lr=1e-3)
+    o.update(over)
+    return types.SimpleNamespace(**o)
+
+
+def build(seed=3, masks=False):
+    from meshnet.meshnet_network import ResidualMeshSimulator
+    from scene_reconstruction.gaussian_mesh import MultiGaussianMesh
+
+    class CpuMesh(MultiGaussianMesh):  # get_xyz of the reference in torch (gaussian_mesh.py:151-169): no GPU here
+        def get_xyz(self, deformed_vertices=None):
+            verts = self.mesh.pos if deformed_vertices is None else deformed_vertices
+            vid = self.mesh.face[:, self.face_ids].transpose(0, 1)
+            nb = self.face_bary / self.face_bary.sum(dim=1, keepdim=True)
+            return (nb.unsqueeze(1) @ verts[vid, :]).squeeze(1)
+
+    g = torch.Generator().manual_seed(seed)
+    pos = torch.rand((9, 3), generator=g)
+    face = torch.tensor([[0, 1, 3, 4, 1, 2, 4, 5], [1, 2, 4, 5, 4, 5, 7, 8], [3, 4, 6, 7, 3, 4, 6, 7]])
+    P = 3 * face.shape[1]
+    bary = torch.rand((P, 3), generator=g) + 0.05
+    bary[5, 1] = -0.02                                        # one Gaussian has left its face (cleanup branch)
+    m = CpuMesh(pos, face, torch.arange(face.shape[1]).repeat(3).sort().values, bary, sh_degree=3)
+    m.set_gaussians(torch.randn((P, 1, 3), generator=g), torch.randn((P, 15, 3), generator=g) * 0.1,
+                    torch.randn((P, 3), generator=g) * 0.5 - 3.0, torch.randn((P, 4), generator=g),
+                    torch.randn((P, 1), generator=g))
+    ei = torch.cat([face[[0, 1]], face[[1, 2]], face[[2, 0]]], dim=1)
+    m.set_edges(torch.cat([ei, ei.flip(0)], dim=1))
+    m.face_offset = torch.nn.Parameter(torch.zeros((P, 1)))
+    m.init_densification_stats(0.01)
+    names = ["face_bary", "face_offset", "f_dc", "f_rest", "opacity", "scaling", "rotation"]
+    m.optimizer = torch.optim.Adam([{"params": [getattr(m, m._GROUP_ATTR[n])], "lr": 1e-2, "name": n} for n in names],
+                                   lr=0.0, eps=1e-15)
+    sim = ResidualMeshSimulator(torch.stack([pos, pos + 0.02 * torch.randn(pos.shape, generator=g),
+                                             pos + 0.04 * torch.randn(pos.shape, generator=g)]), device="cpu")
+    with torch.no_grad():
+        for p in sim.parameters():
+            p.copy_(torch.randn(p.shape, generator=g) * (1e-3 if p.shape[0] == 27 else 0.2))
+    mesh_opt = torch.optim.Adam(sim.parameters(), lr=1e-3)
+    cams = []
+    for i, t in enumerate((0.0, 0.5, 1.0)):
+        cams.append(types.SimpleNamespace(
+            time=t, idx=i, original_image=Img(torch.rand((3, H, W), generator=g)),
+            mask=Img((torch.rand((1, H, W), generator=g) > 0.2).float()) if masks else None,
+            pattern=torch.rand((3, H, W), generator=g), axis=torch.randn(3, generator=g)))
+    return m, sim, mesh_opt, cams, torch.ones(3)
+
+
+def render(cam, pc, simulator, pipe, bg, no_shadow=False, render_static=False):
+    base = pc.get_xyz()
+    screen = torch.zeros_like(base, requires_grad=True) + 0
+    screen.retain_grad()
+    if render_static:
+        verts = pc.mesh.pos
+        xyz = base
+    else:
+        verts = simulator(time_vector=torch.tensor(cam.time).repeat(pc.mesh.pos.shape[0], 1))
+        xyz = pc.get_xyz(verts)
+    rot = torch.nn.functional.normalize(pc._rotation)
+    weight = pc.get_opacity * (1 + xyz @ cam.axis[:, None] + (screen * 0.3).sum(1, keepdim=True)
+                               + 0.1 * pc.get_scaling.sum(1, keepdim=True) + 0.05 * rot[:, :1])
+    colour = (weight * torch.sigmoid(pc.get_features[:, 0, :] + pc.get_features[:, 1:pc.active_sh_degree + 2, :].sum(1))).mean(0)
+    image = torch.sigmoid(colour[:, None, None] * cam.pattern + 0.1 * bg[:, None, None])
+    radii = ((xyz[:, 0].detach() * 37 + cam.idx * 3).abs() - 4).clamp_min(0).to(torch.int32)
+    return types.SimpleNamespace(render=image, viewspace_points=screen, visibility_filter=radii > 0, radii=radii,
+                                 vertice_deform=verts)
+
+
+def image_losses(image, gt, opt, mask=None):
+    from oracle import loss_oracle
+
+    loss, l1, ssim_loss = loss_oracle.image_losses(image, gt, opt.lambda_dssim, mask)
+    return loss, {"l1": l1.item(), "ssim_loss": ssim_loss.item()}
+
+
+CASES = {  # iteration, static, white_background, masks -- each takes a different set of branches of the step
+    "plain": (1, False, False, False), "masked": (7, False, False, True), "static": (3, True, False, False),
+    "densify": (600, False, False, False), "prune_cleanup": (2100, False, False, False),
+    "sh_up_reset": (3000, False, False, False), "white_bg_reset": (500, False, True, False),
+    "past_densify": (16100, False, False, False), "past_end": (30000, False, False, False)}
+
+
+def run_case(train_step, name):
+    """Two iterations (the first fills the Adam state and the statistics at iteration-1, no schedule hit by construction
+    of CASES) -> everything the step returns and leaves behind."""
+    it, static, white, masks = CASES[name]
+    m, sim, mesh_opt, cams, bg = build(masks=masks)
+    opt = options()
+    out = {}
+    for k, i in enumerate((it - 1 if it > 1 else 1, it)):
+        torch.manual_seed(11 + k)                              # densify_and_split draws from the global generator
+        ps, loss, d = train_step(i, cams, m, sim, mesh_opt, types.SimpleNamespace(), opt, 5.0, bg, static=static,
+                                 white_background=white, user_args=types.SimpleNamespace(no_shadow=True))
+        out[f"{k}/psnr"], out[f"{k}/loss"] = ps.detach().numpy(), loss.detach().numpy()
+        out[f"{k}/l1"], out[f"{k}/ssim_loss"] = d["l1"], d["ssim_loss"]
+    for n, a in m._GROUP_ATTR.items():
+        p = getattr(m, a)
+        out[f"p/{n}"] = p.detach().numpy().copy()
+        st = m.optimizer.state.get(p)
+        if st:
+            out[f"m1/{n}"], out[f"m2/{n}"] = st["exp_avg"].numpy().copy(), st["exp_avg_sq"].numpy().copy()
+    for a in ("face_ids", "pos_gradient_accum", "denom", "max_radii2D"):
+        out[a] = getattr(m, a).numpy().copy()
+    out["sh"] = m.active_sh_degree
+    for n, p in sim.named_parameters():                        # the large layers as float64 sums (golden file size)
+        v = p.detach().double()
+        out[f"sim/{n}"] = (p.detach().numpy().copy() if p.numel() <= 1024
+                           else torch.stack([v.sum(), v.abs().sum(), (v * v).sum()]).numpy())
+        out[f"sim_grad_none/{n}"] = p.grad is None
+    return out

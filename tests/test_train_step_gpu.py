@@ -1,0 +1,109 @@
+"""`train_step` on the real kernels (simulator -> mesh-anchored Gaussians -> rasterizer -> fused loss -> backward ->
+multi-tensor Adam): the value it returns equals the pieces composed by hand, the first Adam step moves every parameter by
+at most its learning rate, the statistics it leaves are those of the views, and a densifying iteration leaves a model the
+next iteration can render.  The order of operations itself is pinned on the reference's function in
+tests/test_train_step_cpu.py."""
+import types
+
+import numpy as np
+import pytest
+import torch
+
+import csb_synth as S
+import fake_scene
+
+
+def scene(views=3, W=160, H=120):
+    from meshnet.meshnet_network import ResidualMeshSimulator
+    from scene_reconstruction.gaussian_mesh import MultiGaussianMesh
+
+    verts, faces, ei = S.cloth_mesh(8)
+    pos = torch.from_numpy(verts).cuda()
+    g = torch.Generator(device="cuda").manual_seed(0)
+    pc = MultiGaussianMesh.from_mesh(pos, torch.from_numpy(np.ascontiguousarray(faces.T)).cuda(), gaussian_init_factor=3, generator=g)
+    pc.set_edges(torch.from_numpy(ei).cuda())
+    with torch.no_grad():
+        pc._opacity.add_(2.0)
+        pc._features_dc.add_(torch.randn(pc._features_dc.shape, device="cuda", generator=g))
+    opt = fake_scene.options(densify_grad_threshold_fine_init=1e-7, densify_grad_threshold_after=1e-7,
+                             opacity_threshold_fine_init=0.05, opacity_threshold_fine_after=0.05)
+    pc.training_setup(opt)
+    pc.init_densification_stats(0.01)
+    sim = ResidualMeshSimulator(torch.stack([pos, pos + 0.01, pos + 0.02]), device="cuda")
+    with torch.no_grad():
+        sim.output.weight.normal_(0, 1e-3, generator=g)
+    cams = S.ring_cameras(views, W, H, 0.69, verts.mean(0), fovy=0.55)
+    for i, cam in enumerate(cams):
+        for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+            setattr(cam, k, torch.from_numpy(getattr(cam, k)))
+        cam.time = i / (views - 1)
+        cam.original_image = torch.rand((3, H, W), generator=torch.Generator().manual_seed(i)).pin_memory()
+        cam.mask = None
+    return pc, sim, torch.optim.Adam(sim.parameters(), lr=1e-4), cams, opt, torch.ones(3, device="cuda")
+
+
+PIPE = types.SimpleNamespace(compute_cov3D_python=False)
+ARGS = types.SimpleNamespace(no_shadow=True)
+
+
+@pytest.mark.gpu
+def test_train_step_equals_the_pieces_and_steps_every_parameter():
+    from gaussian_renderer import render
+    from scene_reconstruction.train_utils import image_losses, regularization, train_step
+    from utils.image_utils import psnr
+
+    pc, sim, mesh_opt, cams, opt, bg = scene()
+    with torch.no_grad():                                       # by hand, before the step changes anything
+        pk = [render(c, pc, sim, PIPE, bg) for c in cams]
+        img = torch.stack([p.render for p in pk])
+        gt = torch.stack([c.original_image.cuda() for c in cams])
+        want, want_d = image_losses(img, gt, opt)
+        want = want + regularization(torch.stack([p.vertice_deform for p in pk]), pc, opt)
+        want_psnr = psnr(img, gt).mean().double()
+        seen = torch.stack([p.radii > 0 for p in pk]).any(0)
+        max_r = torch.stack([p.radii for p in pk]).max(0).values
+    names = ["face_bary", "f_dc", "f_rest", "opacity", "scaling", "rotation"]
+    before = {n: getattr(pc, pc._GROUP_ATTR[n]).detach().clone() for n in names}
+    sim_before = sim.output.weight.detach().clone()
+
+    ps, loss, d = train_step(1, cams, pc, sim, mesh_opt, PIPE, opt, 5.0, bg, user_args=ARGS)
+    assert torch.allclose(loss.detach(), want, rtol=1e-6, atol=0) and torch.allclose(ps, want_psnr, rtol=1e-6, atol=0)
+    assert d.keys() == want_d.keys() and all(abs(d[k] - want_d[k]) <= 1e-6 * abs(want_d[k]) for k in d)
+    assert int(seen.sum()) > pc.num_gaussians // 2
+    assert torch.equal(pc.denom.squeeze(1) > 0, seen) and torch.equal(pc.max_radii2D, max_r.float())
+    assert float(pc.pos_gradient_accum[seen].min()) >= 0 and float(pc.pos_gradient_accum.max()) > 0
+    lrs = {gr["name"]: gr["lr"] for gr in pc.optimizer.param_groups}
+    for n in names:
+        step = (getattr(pc, pc._GROUP_ATTR[n]).detach() - before[n]).abs()
+        assert float(step.max()) <= lrs[n] * 1.001 + 1e-6, n    # first Adam step: |m / sqrt(v)| <= 1
+        assert float(step.max()) > 0 or n == "f_rest", n        # SH degree 0 is active: the higher bands get no gradient
+    assert float((sim.output.weight.detach() - sim_before).abs().max()) > 0
+    assert all(p.grad is None for gr in pc.optimizer.param_groups for p in gr["params"])
+    assert all(p.grad is None or float(p.grad.abs().max()) == 0 for p in sim.parameters())
+
+
+@pytest.mark.gpu
+def test_densifying_iteration_leaves_a_model_the_next_one_renders():
+    from scene_reconstruction.train_utils import train_step
+
+    pc, sim, mesh_opt, cams, opt, bg = scene()
+    P0 = pc.num_gaussians
+    losses = [float(train_step(599, cams, pc, sim, mesh_opt, PIPE, opt, 2.0, bg, user_args=ARGS)[1].detach())]
+    torch.manual_seed(5)
+    losses.append(float(train_step(600, cams, pc, sim, mesh_opt, PIPE, opt, 2.0, bg, user_args=ARGS)[1].detach()))   # clone / split
+    P1 = pc.num_gaussians
+    assert P1 > P0
+    for gr in pc.optimizer.param_groups:
+        p = gr["params"][0]
+        assert p is getattr(pc, pc._GROUP_ATTR[gr["name"]]) and p.shape[0] == P1 and p.is_cuda
+        st = pc.optimizer.state.get(p)
+        assert st is None or (st["exp_avg"].shape == p.shape and st["exp_avg_sq"].shape == p.shape)
+    assert pc.face_ids.shape[0] == P1 and pc.denom.shape == (P1, 1) and float(pc.denom.max()) == 0
+    for it in (601, 602):
+        losses.append(float(train_step(it, cams, pc, sim, mesh_opt, PIPE, opt, 5.0, bg, user_args=ARGS)[1].detach()))
+    assert pc.num_gaussians == P1 and float(pc.denom.max()) == 2
+    assert all(np.isfinite(losses)), losses
+    # static: the mesh is not deformed, the simulator is not stepped
+    w = sim.output.weight.detach().clone()
+    train_step(603, cams, pc, sim, mesh_opt, PIPE, opt, 5.0, bg, static=True, user_args=ARGS)
+    assert torch.equal(sim.output.weight.detach(), w)
