@@ -69,7 +69,7 @@ def render(viewpoint_camera, pc, simulator, pipe, bg_color: torch.Tensor, scalin
         means3D_deform = base_xyz
         rotations_deform = pc.get_rotation()
     else:
-        time = torch.tensor(viewpoint_camera.time).to(dev).repeat(pc.mesh.pos.shape[0], 1)
+        time = torch.full((pc.mesh.pos.shape[0], 1), float(viewpoint_camera.time), device=dev)  # no host-to-device copy
         vertice_deform = simulator(time_vector=time)
         means3D_deform = pc.get_xyz(vertice_deform)
         rotations_deform = pc.get_rotation(vertice_deform)

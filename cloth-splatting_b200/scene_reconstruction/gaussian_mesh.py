@@ -427,8 +427,12 @@ class MultiGaussianMesh(torch.nn.Module):
                 self.face_bary[row] = d / d.sum()
 
     def add_densification_stats(self, viewspace_point_tensor, update_filter):
-        self.pos_gradient_accum[update_filter] += torch.norm(viewspace_point_tensor[update_filter, :2], dim=-1, keepdim=True)
-        self.denom[update_filter] += 1
+        """gaussian_model.py:427-430, written without boolean-mask indexing (no host synchronisation; adding 0 to the rows
+        that are not updated leaves them bit-identical)."""
+        seen = update_filter.unsqueeze(1)
+        norms = torch.norm(viewspace_point_tensor[:, :2], dim=-1, keepdim=True)
+        self.pos_gradient_accum += torch.where(seen, norms, torch.zeros_like(norms))
+        self.denom += seen.to(self.denom.dtype)
 
     def reset_opacity(self):
         op = self.get_opacity

@@ -23,7 +23,8 @@ def densification(gaussians, iteration, visibility_filter, radii, viewspace_poin
     statistics every iteration; clone / split every `densification_interval` and prune every `pruning_interval`
     iterations with thresholds that fall linearly from their `*_init` to their `*_after` value over
     `densify_until_iter` iterations; the screen-size criterion (20 px) only after the first opacity reset."""
-    gaussians.max_radii2D[visibility_filter] = torch.max(gaussians.max_radii2D[visibility_filter], radii[visibility_filter])
+    # same values as the reference's boolean-mask assignment, without the host synchronisation of mask indexing
+    gaussians.max_radii2D = torch.where(visibility_filter, torch.max(gaussians.max_radii2D, radii), gaussians.max_radii2D)
     gaussians.add_densification_stats(viewspace_point_tensor_grad, visibility_filter)
 
     def ramp(init, after):
