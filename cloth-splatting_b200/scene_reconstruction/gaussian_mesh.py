@@ -165,7 +165,8 @@ class MultiGaussianMesh(torch.nn.Module):
     GaussianModel accessors, gaussian_model.py:96-118): `mesh.pos`, `mesh.face`, `face_ids`, `face_bary`,
     `_features_dc/_features_rest/_scaling/_rotation/_opacity`, `get_xyz`, `get_rotation`, `get_scaling`,
     `get_opacity`, `get_features`, `active_sh_degree`, `training_setup`, `save_ply` / `load_ply` (the reference's PLY
-    columns).  Densification of the reference class is bookkeeping outside the hot path."""
+    columns), and the densification / pruning bookkeeping `train_step` drives (host-side tensor
+    surgery further down, pinned on the reference's own methods)."""
 
     def __init__(self, pos, face, face_ids, face_bary, sh_degree: int = 3):
         super().__init__()
@@ -222,9 +223,17 @@ class MultiGaussianMesh(torch.nn.Module):
     def training_setup(self, training_args):
         """The seven Adam groups of MultiGaussianMesh.training_setup (gaussian_mesh.py:121-135), same names, learning
         rates and `torch.optim.Adam(l, lr=0.0, eps=1e-15)` settings, stepped by ONE multi-tensor launch
-        (csb_optim.Adam -> csb_adam_step).  Densification statistics and the xyz scheduler stay with the caller."""
+        (csb_optim.Adam -> csb_adam_step).  Like the reference it also zeroes the densification statistics (when
+        `training_args.percent_dense` is given) and builds the position schedule (when `position_lr_final` is)."""
         from csb_optim import Adam
 
+        if hasattr(training_args, "percent_dense"):
+            dev, P = self.face_bary.device, self.num_gaussians
+            self.percent_dense = training_args.percent_dense
+            self.pos_gradient_accum = torch.zeros((P, 1), device=dev)
+            self.denom = torch.zeros((P, 1), device=dev)
+            if not hasattr(self, "max_radii2D"):
+                self.max_radii2D = torch.zeros((P,), device=dev)
         if not hasattr(self, "face_offset"):
             self.face_offset = torch.nn.Parameter(torch.zeros((self.num_gaussians, 1), device=self.face_bary.device))
         scale = getattr(self, "spatial_lr_scale", 1.0)
