@@ -88,6 +88,15 @@ def world_to_view(R, t, translate=(0.0, 0.0, 0.0), scale=1.0):
     return np.float32(np.linalg.inv(C2W))
 
 
+def nerf_normalization(cam_infos):
+    """getNerfppNorm (dataset_readers.py:58-79): `translate` = minus the mean camera centre, `radius` = 1.1 x the largest
+    distance of a camera from it -- the `cameras_extent` the densification thresholds scale with (scene.py:120)."""
+    centers = np.hstack([np.linalg.inv(world_to_view(c.R, c.T))[:3, 3:4] for c in cam_infos])
+    center = np.mean(centers, axis=1, keepdims=True)
+    diagonal = np.max(np.linalg.norm(centers - center, axis=0, keepdims=True))
+    return {"translate": -center.flatten(), "radius": diagonal * 1.1}
+
+
 def projection_matrix(znear, zfar, fovX, fovY):
     """getProjectionMatrix (utils/graphics_utils.py:51-71), fp32 like the torch original."""
     f = np.float32

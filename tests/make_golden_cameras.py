@@ -2,10 +2,12 @@
 container) for a small synthetic transforms file; the three numpy lines that turn `transform_matrix` into (R, T) are
 quoted from scene_reconstruction/dataset_readers.py:352-359 (that module itself needs PIL / plyfile / h5py and cannot be
 imported here).  Run: python tests/make_golden_cameras.py  ->  tests/golden/cameras_transforms.npz"""
+import ast
 import json
 import math
 import os
 import sys
+import types
 
 import numpy as np
 import torch
@@ -38,6 +40,7 @@ for v in range(3):
 contents = {"camera_angle_x": 0.6911, "camera_angle_y": 0.55, "frames": frames}
 
 exp = {"wvt": [], "full": [], "center": []}
+rts = []
 for fr in frames:
     c2w = np.array(fr["transform_matrix"])
     c2w[:3, 1:3] *= -1                       # dataset_readers.py:352-354
@@ -50,7 +53,16 @@ for fr in frames:
     full = (wvt.unsqueeze(0).bmm(proj.unsqueeze(0))).squeeze(0)
     center = wvt.inverse()[3, :3]
     exp["wvt"].append(wvt.numpy()); exp["full"].append(full.numpy()); exp["center"].append(center.numpy())
+    rts.append(types.SimpleNamespace(R=R, T=T))
+
+# getNerfppNorm (scene_reconstruction/dataset_readers.py:58-79), lifted from the source: -> Scene.cameras_extent (scene.py:120)
+tree = ast.parse(open(os.path.join(REF, "scene_reconstruction/dataset_readers.py")).read())
+node = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "getNerfppNorm")
+ns = {"np": np, "getWorld2View2": getWorld2View2}
+exec(compile(ast.Module(body=[node], type_ignores=[]), "dataset_readers.py", "exec"), ns)
+norm = ns["getNerfppNorm"](rts)
 commit = json.load(open(os.path.join(REF, ".SUBMODULES.json")))["commit"][:7]  # the checkout carries no .git
 out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cameras_transforms.npz")
-np.savez(out, transforms=json.dumps(contents), ref_commit=f"KTH-RPL/cloth-splatting {commit}", **{k: np.stack(v) for k, v in exp.items()})
+np.savez(out, transforms=json.dumps(contents), ref_commit=f"KTH-RPL/cloth-splatting {commit}", nerf_translate=norm["translate"],
+         nerf_radius=np.float64(norm["radius"]), **{k: np.stack(v) for k, v in exp.items()})
 print("wrote", out)

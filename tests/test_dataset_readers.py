@@ -88,3 +88,11 @@ def test_raster_settings_agree_with_the_synthetic_cameras(tmp_path):
         assert np.allclose(s.viewmatrix.numpy(), c.world_view_transform, atol=2e-6)
         assert np.allclose(s.projmatrix.numpy(), c.full_proj_transform, atol=5e-6)
         assert np.allclose(s.campos.numpy(), c.camera_center, atol=2e-6)
+
+
+def test_nerf_normalization_is_the_reference_cameras_extent(tmp_path):
+    from scene_reconstruction import dataset_readers as dr
+
+    g, _ = _scene(tmp_path)
+    norm = dr.nerf_normalization(dr.read_cameras_from_transforms(str(tmp_path), "transforms_train.json"))
+    assert np.array_equal(norm["translate"], g["nerf_translate"]) and norm["radius"] == float(g["nerf_radius"])
