@@ -6,6 +6,7 @@ import os
 import sys
 import types
 
+import numpy as np
 import torch
 
 import conftest  # noqa: F401
@@ -141,3 +142,18 @@ def run_case(train_step, name):
                            else torch.stack([v.sum(), v.abs().sum(), (v * v).sum()]).numpy())
         out[f"sim_grad_none/{n}"] = p.grad is None
     return out
+
+
+def camera_infos(n_views, n_times, seed=2, H=6, W=8):
+    """Camera infos of a complete view x time grid, in shuffled order, with non-contiguous ids."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for v in range(n_views):
+        q, _ = np.linalg.qr(rng.standard_normal((3, 3)))
+        R, T = q * np.sign(np.linalg.det(q)), rng.standard_normal(3)
+        for t in range(n_times):
+            out.append(types.SimpleNamespace(
+                R=R, T=T, FovX=0.6 + 0.05 * v, FovY=0.5 + 0.03 * v, time=t / max(n_times - 1, 1), view_id=3 * v + 1, time_id=2 * t,
+                image=torch.from_numpy(rng.uniform(-0.2, 1.2, (3, H, W)).astype(np.float32)), flow=None,
+                mask=torch.from_numpy((rng.uniform(size=(1, H, W)) > 0.3).astype(np.float32))))
+    return [out[i] for i in rng.permutation(len(out))]
