@@ -456,6 +456,24 @@ class MultiGaussianMesh(torch.nn.Module):
             mask = torch.logical_or(torch.logical_or(mask, big_vs), big_ws)
         self.prune_points(mask)
 
+    # ---- checkpoint tuple of the training CLI (train.py:106,220) ------------------------------------------------
+    def capture(self):
+        """gaussian_model.py:62-76, same 12 slots in the same order.  Slot 1 is `_xyz`, which for the mesh-anchored model is
+        the base class's empty tensor: the reference's checkpoint does not carry `face_bary` / `face_ids` / the mesh (those
+        travel in `save_ply`); kept as it is so that the tuples are interchangeable."""
+        return (self.active_sh_degree, getattr(self, "_xyz", torch.empty(0)), self._features_dc, self._features_rest,
+                self._scaling, self._rotation, self._opacity, self.max_radii2D, self.pos_gradient_accum, self.denom,
+                self.optimizer.state_dict(), getattr(self, "spatial_lr_scale", 1.0))
+
+    def restore(self, model_args, training_args):
+        """gaussian_model.py:78-94: adopt the tensors, rebuild the optimiser, then put the statistics and its state back."""
+        (self.active_sh_degree, self._xyz, self._features_dc, self._features_rest, self._scaling, self._rotation,
+         self._opacity, self.max_radii2D, pos_gradient_accum, denom, opt_dict, self.spatial_lr_scale) = model_args
+        self.training_setup(training_args)
+        self.pos_gradient_accum = pos_gradient_accum
+        self.denom = denom
+        self.optimizer.load_state_dict(opt_dict)
+
     # ---- on-disk format of the reference (SURVEY.md 8(f) #4) --------------------------------------------------
     def save_ply(self, path):
         """`<path>/point_cloud.ply` with the reference's columns (gaussian_mesh.py:438-460): positions, zero normals,

@@ -157,3 +157,27 @@ def camera_infos(n_views, n_times, seed=2, H=6, W=8):
                 image=torch.from_numpy(rng.uniform(-0.2, 1.2, (3, H, W)).astype(np.float32)), flow=None,
                 mask=torch.from_numpy((rng.uniform(size=(1, H, W)) > 0.3).astype(np.float32))))
     return [out[i] for i in rng.permutation(len(out))]
+
+
+# ---- checkpoint tuple (tests/make_golden_checkpoint.py, tests/test_checkpoint_cpu.py) ----
+SLOTS = ["active_sh_degree", "_xyz", "_features_dc", "_features_rest", "_scaling", "_rotation", "_opacity", "max_radii2D",
+         "pos_gradient_accum", "denom", "spatial_lr_scale"]
+
+
+class Named:
+    """every attribute holds its own name; the optimiser reports what was asked of it"""
+    def __init__(self):
+        self.log = []
+        for a in SLOTS:
+            setattr(self, a, a)
+        self.optimizer = self
+
+    def state_dict(self):
+        return "optimizer.state_dict()"
+
+    def load_state_dict(self, d):
+        self.log.append(f"load_state_dict({d})")
+
+    def training_setup(self, args):
+        self.log.append(f"training_setup({args})")
+        self.pos_gradient_accum, self.denom = "zeroed", "zeroed"
