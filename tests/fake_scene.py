@@ -181,3 +181,16 @@ class Named:
     def training_setup(self, args):
         self.log.append(f"training_setup({args})")
         self.pos_gradient_accum, self.denom = "zeroed", "zeroed"
+
+
+# ---- planner graphs (tests/make_golden_graph_data.py, tests/test_graph_data_cpu.py) ----
+def graph_case(as_numpy, N=7, F=4, L=2, seed=6):
+    """(action, grasped_particle, velocity, node_type, faces, velocity_target, position_target, positions) of one sample"""
+    g = torch.Generator().manual_seed(seed)
+    r = lambda *s: torch.randn(s, generator=g)  # noqa: E731
+    action, velocity, vt, pt, pos = r(F, 3) * 0.1, r(N, 3 * L), r(F, N, 3), r(F, N, 3), r(N, 3)
+    node_type = torch.zeros((N, 1))
+    node_type[3] = 1.0
+    faces = torch.randint(0, N, (3, 5), generator=g)
+    c = (lambda t: t.numpy().copy()) if as_numpy else (lambda t: t.clone())
+    return (c(action), 3, c(velocity), c(node_type), faces, c(vt), c(pt), c(pos))
