@@ -1,0 +1,89 @@
+"""The mesh files between the GNN rollout and the Gaussian refinement: `init_mesh.hdf5` and
+`mesh_predictions/mesh_XXX.hdf5` with the datasets `pos`, `face`, `edge_index`, `norm`, as
+meshnet/generate_mesh_predictions.py:34-46,94-119 writes them and meshnet/data_utils.py:450-457 reads them.
+
+The reference builds them with torch_geometric transforms (`FaceToEdge(remove_faces=False)`, `GenerateMeshNormals`,
+`Cartesian(norm=False)`, `Distance(norm=False)`); torch_geometric (2.x) is not in this image, so their published rules are
+restated here in torch -- parity of this file is UNPINNED and tested by properties (tests/test_mesh_data_cpu.py).  h5py is
+absent too: the files are written as `.hdf5` when h5py is importable and as `.npz` with the same dataset names otherwise."""
+import os
+
+import numpy as np
+import torch
+
+from .graph_data import Data
+
+
+def face_to_edge(face, num_nodes):
+    """FaceToEdge: the three sides of every triangle in both directions, duplicates removed, sorted by (source, target)."""
+    e = torch.cat([face[:2], face[1:], face[::2]], dim=1)
+    e = torch.cat([e, e.flip(0)], dim=1)
+    key = torch.unique(e[0] * num_nodes + e[1])                    # sorted
+    return torch.stack([key // num_nodes, key % num_nodes])
+
+
+def mesh_normals(pos, face):
+    """GenerateMeshNormals: unit face normals (v1 - v0) x (v2 - v0) summed at the three corners, normalised."""
+    n = torch.nn.functional.normalize(torch.linalg.cross(pos[face[1]] - pos[face[0]], pos[face[2]] - pos[face[0]], dim=1), dim=-1)
+    out = torch.zeros_like(pos).index_add_(0, face.reshape(-1), n.repeat(3, 1))
+    return torch.nn.functional.normalize(out, dim=-1)
+
+
+def cartesian_distance(pos, edge_index):
+    """Cartesian(norm=False) ++ Distance(norm=False): [pos[src] - pos[dst], |pos[dst] - pos[src]|] per edge, [E,4]."""
+    src, dst = edge_index
+    return torch.cat([pos[src] - pos[dst], (pos[dst] - pos[src]).norm(dim=-1, keepdim=True)], dim=-1)
+
+
+def get_mesh_data(points, faces):
+    """generate_mesh_predictions.py:40-45: Data(pos, face [3,F], edge_index, norm)."""
+    return Data(pos=points, face=faces, edge_index=face_to_edge(faces, points.shape[0]), norm=mesh_normals(points, faces))
+
+
+def predicted_positions(initial_pos, predicted_rollout):
+    """Positions after every rollout step (generate_mesh_predictions.py:106): the initial positions plus the running sum of
+    the predicted displacements -> [T+1, N, 3], entry 0 being the start."""
+    steps = np.cumsum(np.asarray(predicted_rollout), axis=0)
+    return np.concatenate([np.asarray(initial_pos)[None], np.asarray(initial_pos)[None] + steps], axis=0)
+
+
+def save_mesh(mesh, path, name="mesh.hdf5"):
+    """generate_mesh_predictions.py:34-38.  Returns the path written (`.npz` instead of `.hdf5` without h5py)."""
+    arrays = {k: getattr(mesh, k).detach().cpu().numpy() for k in mesh.keys() if isinstance(getattr(mesh, k), torch.Tensor)}
+    try:
+        import h5py
+    except ImportError:
+        out = os.path.join(path, os.path.splitext(name)[0] + ".npz")
+        np.savez(out, **arrays)
+        return out
+    out = os.path.join(path, name)
+    with h5py.File(out, "w") as f:
+        for k, v in arrays.items():
+            f.create_dataset(k, data=v)
+    return out
+
+
+def load_mesh(path, device="cuda"):
+    """load_mesh_from_h5py (meshnet/data_utils.py:450-457): Data(pos, norm, face, edge_index) on `device`."""
+    if path.endswith(".npz") or not os.path.exists(path):
+        with np.load(os.path.splitext(path)[0] + ".npz") as f:
+            arrays = {k: f[k] for k in ("pos", "norm", "face", "edge_index")}
+    else:
+        import h5py
+        with h5py.File(path, "r") as f:
+            arrays = {k: f[k][:] for k in ("pos", "norm", "face", "edge_index")}
+    return Data(**{k: torch.tensor(v, device=device) for k, v in arrays.items()})
+
+
+def write_mesh_predictions(root, initial_pos, predicted_rollout, faces):
+    """The files one rollout leaves (generate_mesh_predictions.py:94-119): `<root>/init_mesh.*`, and
+    `<root>/mesh_predictions/mesh_000.*` (the start) ... `mesh_TTT.*`.  Returns the paths."""
+    pred = os.path.join(root, "mesh_predictions")
+    os.makedirs(pred, exist_ok=True)
+    faces = torch.as_tensor(np.asarray(faces)).long()
+    positions = predicted_positions(initial_pos, predicted_rollout)
+    start = get_mesh_data(torch.from_numpy(positions[0]), faces)
+    out = [save_mesh(start, root, name="init_mesh.hdf5")]
+    for i, p in enumerate(positions):
+        out.append(save_mesh(get_mesh_data(torch.from_numpy(p), faces), pred, name=f"mesh_{i:03}.hdf5"))
+    return out
