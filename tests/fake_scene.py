@@ -194,3 +194,26 @@ def graph_case(as_numpy, N=7, F=4, L=2, seed=6):
     faces = torch.randint(0, N, (3, 5), generator=g)
     c = (lambda t: t.numpy().copy()) if as_numpy else (lambda t: t.clone())
     return (c(action), 3, c(velocity), c(node_type), faces, c(vt), c(pt), c(pos))
+
+
+# ---- open-loop rollout (tests/make_golden_rollout.py, tests/test_rollout_cpu.py) ----
+class ToySimulator:
+    """deterministic stand-in for ClothMeshSimulator.predict_velocity: sensitive to edge order, direction and features"""
+    def predict_velocity(self, velocities, node_type, edge_index, edge_features):
+        agg = torch.zeros((velocities.shape[0], 3)).index_add_(0, edge_index[1], edge_features[:, :3] * edge_features[:, 3:])
+        w = torch.linspace(0.5, 1.5, velocities.shape[1])
+        return (0.3 * velocities[:, -3:] + 0.05 * (velocities * w).sum(1, keepdim=True) + 0.2 * agg) * (1 - 0.5 * node_type)
+
+
+def rollout_features(T=6, n=4, seed=12):
+    import csb_synth as S
+
+    verts, faces, ei = S.cloth_mesh(n)
+    g = torch.Generator().manual_seed(seed)
+    N = verts.shape[0]
+    vel = torch.randn((T, N, 3), generator=g) * 0.01
+    pos = torch.from_numpy(verts).float()[None] + torch.cumsum(vel, 0)
+    node_type = torch.zeros((N, 1))
+    node_type[5] = 1.0
+    return {"pos": pos, "vel": vel, "actions": torch.randn((T, 3), generator=g) * 0.02, "node_type": node_type,
+            "edge_index": torch.from_numpy(ei), "faces": torch.from_numpy(np.ascontiguousarray(faces.T)), "grasped_particle": 5}
