@@ -47,6 +47,14 @@ def predicted_positions(initial_pos, predicted_rollout):
     return np.concatenate([np.asarray(initial_pos)[None], np.asarray(initial_pos)[None] + steps], axis=0)
 
 
+def position_losses(prediction_data):
+    """Per-step mean squared position error of a rollout against its trajectory, with a leading 0 for the start
+    (train_meshnet_sim.py:296-301, generate_mesh_predictions.py:103-109)."""
+    pred = predicted_positions(prediction_data["initial_pos"], prediction_data["predicted_rollout"])
+    truth = np.asarray(prediction_data["node_coords"])
+    return [0] + [float(((truth[i] - pred[i]) ** 2).mean()) for i in range(1, pred.shape[0])]
+
+
 def save_mesh(mesh, path, name="mesh.hdf5"):
     """generate_mesh_predictions.py:34-38.  Returns the path written (`.npz` instead of `.hdf5` without h5py)."""
     arrays = {k: getattr(mesh, k).detach().cpu().numpy() for k in mesh.keys() if isinstance(getattr(mesh, k), torch.Tensor)}

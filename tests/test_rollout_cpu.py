@@ -35,3 +35,16 @@ def test_rollout_to_prediction_files(tmp_path):
     last = load_mesh(paths[-1], device="cpu")
     assert np.allclose(last.pos.numpy(), r["initial_pos"] + r["predicted_rollout"].sum(0), atol=1e-6)
     assert np.array_equal(last.edge_index.numpy(), r["edge_index"])
+
+
+def test_position_losses_follow_the_reference_loop():
+    from meshnet.mesh_data import position_losses
+    from meshnet.rollout import rollout
+
+    r = rollout(fake_scene.ToySimulator(), fake_scene.rollout_features(), 4, torch.device("cpu"), 2, 0.01)
+    losses = position_losses(r)
+    want = [0]
+    for i in range(len(r["predicted_rollout"])):                        # train_meshnet_sim.py:296-301, as written there
+        pred_points = r["initial_pos"] + r["predicted_rollout"][:i + 1].sum(axis=0)
+        want.append(((r["node_coords"][i + 1] - pred_points) ** 2).mean().item())
+    assert len(losses) == 5 and np.allclose(losses, want, rtol=1e-5, atol=0) and losses[0] == 0 and min(losses[1:]) > 0
