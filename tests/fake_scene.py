@@ -217,3 +217,16 @@ def rollout_features(T=6, n=4, seed=12):
     node_type[5] = 1.0
     return {"pos": pos, "vel": vel, "actions": torch.randn((T, 3), generator=g) * 0.02, "node_type": node_type,
             "edge_index": torch.from_numpy(ei), "faces": torch.from_numpy(np.ascontiguousarray(faces.T)), "grasped_particle": 5}
+
+
+# ---- simulator training samples (tests/make_golden_trajectory_dataset.py, tests/test_trajectory_dataset_cpu.py) ----
+def trajectories(lengths=(9, 7, 12), N=6, seed=21):
+    rng = np.random.default_rng(seed)
+    out = []
+    for k, T in enumerate(lengths):
+        node_type = np.zeros((T, N, 1), np.float32)
+        node_type[:, k + 1] = 1.0
+        out.append({"pos": rng.standard_normal((T, N, 3)).astype(np.float32), "velocity": rng.standard_normal((T, N, 3)).astype(np.float32),
+                    "node_type": node_type, "actions": rng.standard_normal((T, 3)).astype(np.float32) * 0.1,
+                    "edge_faces": [torch.from_numpy(rng.integers(0, N, (3, 4))) for _ in range(T)], "grasped_particle": k + 1})
+    return out
