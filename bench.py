@@ -37,6 +37,41 @@ import csb_synth as S  # noqa: E402
 PARAM_NAMES = ("means3D", "scales", "rotations", "opacities", "shs")
 
 
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def pair_counts(workload, views):
+    """(pixel, Gaussian) pair counts of the seeded workload, per view (profiles/pair_counts.json, made by
+    tools/pair_counts.py with the CPU oracle; they depend on the inputs only)."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "pair_counts.json")))[workload]["views"]
+        sel = [rec[v] for v in views]
+        return {k: sum(r[k] for r in sel) for k in ("instances", "evaluated", "blended")}
+    except Exception:
+        return None
+
+
+def fp32_peaks(dev):
+    """FP32 FMA and SFU peaks of this GPU, measured now by the library's micro-benchmark (csb_measure_fp32_peaks)."""
+    import ctypes
+
+    import csb_cabi
+
+    lib = csb_cabi.lib()
+    scratch = torch.empty(148 * 8 * 256 * 4 * 2, dtype=torch.uint8, device=dev)
+    a, b, c = ctypes.c_double(0), ctypes.c_double(0), ctypes.c_double(0)
+    rc = lib.csb_measure_fp32_peaks(scratch.data_ptr(), scratch.numel(), ctypes.byref(a), ctypes.byref(b), ctypes.byref(c),
+                                    torch.cuda.current_stream().cuda_stream)
+    csb_cabi.check(rc, "csb_measure_fp32_peaks")
+    return {"ffma_tflops": 2 * a.value / 1e12, "ffma2_tflops": 2 * b.value / 1e12, "mufu_tops": c.value / 1e12,
+            "how": "csb_measure_fp32_peaks: dependent-chain-free fma.rn.f32 / fma.rn.f32x2 / ex2.approx loops, 8 blocks of "
+                   "256 threads per SM, best of 3, CUDA events, this run"}
+
+
 # ------------------------------------------------------------------------------------------
 # workloads
 # ------------------------------------------------------------------------------------------
@@ -178,6 +213,14 @@ def gnn_bench(dev, impl, peaks, flush, with_cpu=True, iters=30):
     torch.manual_seed(0)
     model = EncodeProcessDecode(8, 3, 4, 128, 15, 2, 128).eval().to(dev)
     sd = {k: v.detach() for k, v in model.state_dict().items()}
+    ref_model = None
+    if impl == "reference":
+        mod = reference_gnn_module()
+        if mod is not None:
+            ref_model = mod.EncodeProcessDecode(8, 3, 4, 128, 15, 2, 128).eval().to(dev)
+            ref_model.load_state_dict(model.state_dict())
+        out["reference_impl"] = ("the reference's meshnet/graph_network.py (nn.Module) under oracle/pyg_stub" if ref_model is not None
+                                 else "oracle/gnn_oracle.py (the module file did not travel: baseline/_ref absent)")
     cases = {"c1_20x20": (20, 1), "batch128_40x40": (40, 128)}
     for name, (n, graphs) in cases.items():
         x, ei, ef = gnn_batch_inputs(n, graphs)
@@ -198,15 +241,22 @@ def gnn_bench(dev, impl, peaks, flush, with_cpu=True, iters=30):
                 yh.copy_(y, non_blocking=True)
                 torch.cuda.current_stream().synchronize()
         else:
+            if ref_model is not None:
+                def ref_fwd():
+                    return ref_model(xt, eit, eft)
+            else:
+                def ref_fwd():
+                    return gnn_oracle.forward(sd, xt, eit, eft, device=dev)
+
             def step():
                 with torch.no_grad():
-                    return gnn_oracle.forward(sd, xt, eit, eft, device=dev)
+                    return ref_fwd()
 
             def e2e():
                 xt.copy_(xh, non_blocking=True)
                 eft.copy_(efh, non_blocking=True)
                 with torch.no_grad():
-                    y = gnn_oracle.forward(sd, xt, eit, eft, device=dev)
+                    y = ref_fwd()
                 yh.copy_(y, non_blocking=True)
                 torch.cuda.current_stream().synchronize()
         it = iters if graphs == 1 else max(5, iters // 3)
@@ -260,7 +310,7 @@ def c5_batch(graphs, n=40, F=10, L=2, seed=4):
     return d
 
 
-def gnn_train_bench(dev, impl, peaks, graphs, F=10, iters=5, world=1):
+def gnn_train_bench(dev, impl, peaks, graphs, F=10, iters=5, world=1, rank=0):
     """One optimisation step of the cloth simulator on this rank's share of C5 (1024 graphs of 1600 nodes over
     8 GPUs = 128 per GPU): zero_grad, 10-step rollout loss (train_meshnet_sim.py:491-527), backward, ONE flat
     all-reduce of the 2.33 M parameter gradients, fused Adam step."""
@@ -282,9 +332,15 @@ def gnn_train_bench(dev, impl, peaks, graphs, F=10, iters=5, world=1):
                 sd = dict(self.inner.named_parameters())
                 return gnn_oracle.forward(sd, x, ei, ea, device=x.device, differentiable=True)
 
-        sim._encode_process_decode = OracleGnn(sim._encode_process_decode)
+        mod = reference_gnn_module()
+        if mod is not None:  # the reference's own module under torch autograd
+            ref_model = mod.EncodeProcessDecode(8, 3, 4, 128, 15, 2, 128).to(dev)
+            ref_model.load_state_dict(sim._encode_process_decode.state_dict())
+            sim._encode_process_decode = ref_model
+        else:
+            sim._encode_process_decode = OracleGnn(sim._encode_process_decode)
     sim.train()
-    d = c5_batch(graphs, F=F)
+    d = c5_batch(graphs, F=F, seed=4 + rank)  # every rank trains on its own shard of the 1024 graphs
     t = {k: torch.from_numpy(v).to(dev) for k, v in d.items()}
     N, E = t["velocity"].shape[0], t["edge_index"].shape[1]
     flat = csb_dist.attach_flat_grads(sim.parameters())
@@ -324,13 +380,16 @@ def gnn_train_bench(dev, impl, peaks, graphs, F=10, iters=5, world=1):
 # ------------------------------------------------------------------------------------------
 # product arm
 # ------------------------------------------------------------------------------------------
-def run_b200(args, rank, world, dev):
+def raster_leg(workload, rank, world, dev, steps, warmup, fp32, peaks, with_e2e=True):
+    """Forward + backward of this rank's views of `workload`, device-resident (C-ABI wrapper layer, no autograd) and --
+    with_e2e -- through the public API with host buffers.  Returns the measurements of one workload."""
     import csb_cabi
+    import csb_dist
     import diff_gaussian_rasterization as dgr
     import torch.distributed as dist
 
     lib = csb_cabi.lib()
-    g_np, cams, dl_np, desc = make_workload(args.workload, rank, world)
+    g_np, cams, dl_np, desc = make_workload(workload, rank, world)
     V, H, W = len(cams), cams[0].image_height, cams[0].image_width
     P = g_np["means3D"].shape[0]
     gd = {k: torch.from_numpy(v).to(dev) for k, v in g_np.items()}
@@ -343,8 +402,6 @@ def run_b200(args, rank, world, dev):
 
     def views_of(b):
         return [(sl[v].viewmatrix, sl[v].projmatrix, sl[v].campos, sl[v].bg, sl[v].tanfovx, sl[v].tanfovy) for v in b]
-
-    import csb_dist
 
     # 3+3+4+1+48 floats per Gaussian, one flat buffer -> one all-reduce per step
     bucket = csb_dist.FlatGradBucket({k: gd[k].shape for k in PARAM_NAMES}, dev)
@@ -416,140 +473,226 @@ def run_b200(args, rank, world, dev):
             dist.all_reduce(total, op=dist.ReduceOp.MAX)
         return float(total.item()) / steps, ms
 
-    sampler = ClockSampler(dev.index) if rank == 0 else None
     launches0 = lib.csb_launch_count()
     if bucket.peer:
         bucket.peer.stats(reset=True)
-    ms_step, ms_all = timed(device_step, args.steps, args.warmup)
+    ms_step, ms_all = timed(device_step, steps, warmup)
     allreduce = None
     if world > 1:
         allreduce = {"impl": "csb_peer_all_reduce (one kernel over NVLink peer memory)" if bucket.peer else "NCCL",
                      "floats": bucket.numel}
         if bucket.peer:  # the kernel's own clock, mean over warm-up + timed calls on rank 0
             allreduce.update({k: round(v, 2) if isinstance(v, float) else v for k, v in bucket.peer.stats().items()})
-    launches = (lib.csb_launch_count() - launches0) // (args.steps + args.warmup) * args.steps
+    launches = (lib.csb_launch_count() - launches0) // (steps + warmup) * steps
     R_step = device_step()
     torch.cuda.synchronize()
-    mpix = V * H * W / 1e6
+    out = {"workload": workload, "desc": desc, "V": V, "H": H, "W": W, "P": P, "ms_step": ms_step, "ms_all": ms_all,
+           "R_step": int(R_step), "launches": int(launches), "allreduce": allreduce, "peer": bool(bucket.peer)}
 
     # ---- end to end through the public API with host buffers --------------------------------------
-    host = {k: torch.from_numpy(g_np[k]).pin_memory() for k in PARAM_NAMES}
-    dl_host = torch.from_numpy(dl_np).pin_memory()
-    leaves = {k: torch.empty_like(gd[k]).requires_grad_(True) for k in PARAM_NAMES}
-    dl_dev = torch.empty_like(dl)
-    grads_host = {k: torch.empty(g_np[k].shape, dtype=torch.float32).pin_memory() for k in PARAM_NAMES}
-    h2d = sum(t.numel() * 4 for t in host.values()) + dl_host.numel() * 4
-    d2h = sum(t.numel() * 4 for t in grads_host.values())
+    if with_e2e:
+        host = {k: torch.from_numpy(g_np[k]).pin_memory() for k in PARAM_NAMES}
+        dl_host = torch.from_numpy(dl_np).pin_memory()
+        leaves = {k: torch.empty_like(gd[k]).requires_grad_(True) for k in PARAM_NAMES}
+        dl_dev = torch.empty_like(dl)
+        grads_host = {k: torch.empty(g_np[k].shape, dtype=torch.float32).pin_memory() for k in PARAM_NAMES}
+        out["h2d"] = sum(t.numel() * 4 for t in host.values()) + dl_host.numel() * 4
+        out["d2h"] = sum(t.numel() * 4 for t in grads_host.values())
 
-    copy_stream = torch.cuda.Stream(device=dev)
-    # one staged upload per launch set (C4: 4 sets of 16 views): a set's backward waits for ITS views only
-    staged = [dgr.StagedPixelGrads(dl_dev[b[0]:b[-1] + 1], copy_stream) for b in view_batches]
+        copy_stream = torch.cuda.Stream(device=dev)
+        # one staged upload per launch set (C4: 4 sets of 16 views): a set's backward waits for ITS views only
+        staged = [dgr.StagedPixelGrads(dl_dev[b[0]:b[-1] + 1], copy_stream) for b in view_batches]
 
-    def e2e_step():
-        # the parameters (2.4 MB) are enqueued FIRST: host-to-device copies of all streams go through the copy engine in
-        # submission order, and the forward only needs them.  dL/dpixel (30.7 MB, needed by the backward only) follows
-        # on a side stream while the forward renders
-        with torch.no_grad():
-            for k in PARAM_NAMES:
-                leaves[k].copy_(host[k], non_blocking=True)
-                leaves[k].grad = None
-        # ... and the side stream is held back until they are through (the L2 flush in front of the step would otherwise
-        # let the big copy slip ahead of them in the copy engine)
-        copy_stream.wait_stream(stream)
-        # one copy + event per view: view v's compositing backward starts when ITS plane has arrived
-        for st, b in zip(staged, view_batches):
-            st.upload(dl_host[b[0]:b[-1] + 1])
-        for st, b in zip(staged, view_batches):
-            color, radii, depth = dgr.rasterize_views([sl[v] for v in b], leaves["means3D"], leaves["opacities"],
-                                                      shs=leaves["shs"], scales=leaves["scales"],
-                                                      rotations=leaves["rotations"])
-            dgr.backward_staged(color, st)
-        if world > 1:
-            # the autograd gradients go into the peer-memory bucket, one NVLink all-reduce kernel sums it in place
-            bucket.copy_({k: leaves[k].grad for k in PARAM_NAMES})
-            bucket.all_reduce()
-            for k in PARAM_NAMES:
-                grads_host[k].copy_(bucket.view(k), non_blocking=True)
-        else:
-            for k in PARAM_NAMES:
-                grads_host[k].copy_(leaves[k].grad, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        def e2e_step():
+            # the parameters (2.4 MB) are enqueued FIRST: host-to-device copies of all streams go through the copy engine
+            # in submission order, and the forward only needs them.  dL/dpixel (30.7 MB, needed by the backward only)
+            # follows on a side stream while the forward renders
+            with torch.no_grad():
+                for k in PARAM_NAMES:
+                    leaves[k].copy_(host[k], non_blocking=True)
+                    leaves[k].grad = None
+            # ... and the side stream is held back until they are through (the L2 flush in front of the step would
+            # otherwise let the big copy slip ahead of them in the copy engine)
+            copy_stream.wait_stream(stream)
+            # one copy + event per view: view v's compositing backward starts when ITS plane has arrived
+            for st, b in zip(staged, view_batches):
+                st.upload(dl_host[b[0]:b[-1] + 1])
+            for st, b in zip(staged, view_batches):
+                color, radii, depth = dgr.rasterize_views([sl[v] for v in b], leaves["means3D"], leaves["opacities"],
+                                                          shs=leaves["shs"], scales=leaves["scales"],
+                                                          rotations=leaves["rotations"])
+                dgr.backward_staged(color, st)
+            if world > 1:
+                # the autograd gradients go into the peer-memory bucket, one NVLink all-reduce kernel sums it in place
+                bucket.copy_({k: leaves[k].grad for k in PARAM_NAMES})
+                bucket.all_reduce()
+                for k in PARAM_NAMES:
+                    grads_host[k].copy_(bucket.view(k), non_blocking=True)
+            else:
+                for k in PARAM_NAMES:
+                    grads_host[k].copy_(leaves[k].grad, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
 
-    ms_e2e, _ = timed(e2e_step, args.steps, args.warmup)
-    clocks = sampler.stop() if sampler else None
+        out["ms_e2e"], _ = timed(e2e_step, steps, warmup)
 
-    # ---- per-kernel device time of the same step (library CUDA events) -> roofline -----------------
+    # ---- per-kernel device time of the same step (library CUDA events) -> one roofline per kernel ---
+    nprof = max(3, min(steps, 10))
     lib.csb_profile_enable(1)
-    for _ in range(max(3, min(args.steps, 10))):
+    for _ in range(nprof):
         flush()
         device_step()
     torch.cuda.synchronize()
     prof = csb_cabi.profile_read()
     lib.csb_profile_enable(0)
-    kernels = {k: {"ms_per_launch": ms / n, "launches_per_step": n / max(3, min(args.steps, 10)),
-                   "ms_per_step": ms / max(3, min(args.steps, 10))} for k, (ms, n) in prof.items()}
-    top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
+    kernels = {k: {"ms_per_launch": ms / n, "launches_per_step": n / nprof, "ms_per_step": ms / nprof}
+               for k, (ms, n) in prof.items()}
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
-    R_launch = R_step / max(1, len(view_batches))
+    nb = max(1, len(view_batches))
+    R_launch = R_step / nb
     Vb = len(view_batches[0])
-    alg = {  # algorithmic bytes per launch (DESIGN.md "roofline")
+    alg = {  # algorithmic bytes per launch of the HBM-bound stages
         "preprocess": 311.0 * P * Vb,
         "emit": 20.0 * P * Vb + 12.0 * R_launch,
         "sort_onesweep": 16.0 * R_launch,
         "sort_histogram": 4.0 * R_launch,
         "tile_ranges": 16.0 * R_launch + 8.0 * tiles * Vb,
-        "render_forward": 44.0 * R_launch + 24.0 * Vb * H * W,
-        "render_backward": 40.0 * R_launch + 20.0 * Vb * H * W + 36.0 * R_launch,
+        "bin_ranges": 8.0 * tiles * Vb,
+        "bin_fill": 20.0 * P * Vb + 8.0 * R_launch,
+        "bin_sort": 16.0 * R_launch,
         "gaussian_backward": (236.0 + 24 + 40 * Vb + 256) * P,
     }
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    ach = alg.get(top, 0.0) / (kernels[top]["ms_per_launch"] * 1e-3) / 1e9
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    for k, b_ in alg.items():
+        if k in kernels:
+            ach = b_ / (kernels[k]["ms_per_launch"] * 1e-3) / 1e9
+            kernels[k]["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s",
+                                      "frac": ach / hbm_peak, "algorithmic_bytes_per_launch": b_}
+    # compositing kernels: FP32 FMA pipe + SFU.  Pairs counted by the CPU oracle on these very inputs
+    # (profiles/pair_counts.json): forward 10 flop / evaluated + 9 / blended pair and one exp per evaluated pair,
+    # backward 10 / evaluated + 60 / blended
+    view_ids = list(range(rank, V * world, world)) if workload == "c2" else (
+        list(range(rank * V, rank * V + V)) if workload == "c4" else list(range(V)))
+    pc = pair_counts(workload, view_ids) if (workload != "c2" or world == 1) else None
+    if pc:
+        out["pairs_per_step"] = pc
+        fl = {"render_forward": 10.0 * pc["evaluated"] + 9.0 * pc["blended"],
+              "render_backward": 10.0 * pc["evaluated"] + 60.0 * pc["blended"]}
+        for k, f in fl.items():
+            if k in kernels:
+                t = kernels[k]["ms_per_step"] * 1e-3
+                ach = f / t / 1e12
+                kernels[k]["roofline"] = {"bound": "fp32", "achieved": ach, "peak": fp32["ffma2_tflops"], "unit": "TFLOP/s",
+                                          "frac": ach / fp32["ffma2_tflops"], "flops_per_step": f,
+                                          "sfu_frac": pc["evaluated"] / t / 1e12 / fp32["mufu_tops"],
+                                          "peak_source": "csb_measure_fp32_peaks, this run"}
+    out["kernels"] = kernels
+    return out
+
+
+def knn_bench(dev, impl, flush, iters=10):
+    """distCUDA2 (simple_knn.cu:185-221) at the sizes BASELINE.md names: the 38x38 / C2 clouds and 1 M random points."""
+    out = {"metric": "distCUDA2 Mpoints/s", "impl": impl}
+    clouds = {"1444": S.mesh_gaussians(20, 2, 1)["means3D"], "10108": S.mesh_gaussians(20, 14, 1)["means3D"],
+              "1000000": S.config_c3(1_000_000, 1920, 1080)[0]["means3D"]}
+    if impl == "b200":
+        from simple_knn._C import distCUDA2 as fn
+    else:
+        from oracle import ref_cuda
+
+        fn = ref_cuda.dist_cuda2
+    for name, pts in clouds.items():
+        t = torch.from_numpy(np.ascontiguousarray(pts)).to(dev)
+        ms, _ = _time_cuda(lambda: fn(t), iters, 3, flush)
+        out[name] = {"points": int(t.shape[0]), "ms": ms, "mpoints_per_s": t.shape[0] / 1e6 / (ms * 1e-3),
+                     "hbm_frac_16B_per_point": 16.0 * t.shape[0] / (ms * 1e-3) / 1e9 / 6535.0}
+    return out
+
+
+def run_b200(args, rank, world, dev):
+    import csb_cabi
+    import torch.distributed as dist
+
+    lib = csb_cabi.lib()
+    if args.render_variant >= 0:
+        lib.csb_debug_render_variant(args.render_variant)
+    peaks = load_peaks()
+    fp32 = fp32_peaks(dev)
+    flush = l2_flusher(dev)
+    sampler = ClockSampler(dev.index) if rank == 0 else None
+    main = raster_leg(args.workload, rank, world, dev, args.steps, args.warmup, fp32, peaks)
+    clocks = sampler.stop() if sampler else None
+    V, H, W, P = main["V"], main["H"], main["W"], main["P"]
+    ms_step, ms_e2e, ms_all, kernels = main["ms_step"], main["ms_e2e"], main["ms_all"], main["kernels"]
+    strong = args.workload == "c4"  # 64 views split over the ranks: the total work is fixed
+    mpix = V * world * H * W / 1e6  # all ranks' views
+
+    top = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
+    roofline = dict(kernels[top].get("roofline", {"bound": "latency"}))
+    roofline["kernel"] = top
+    roofline["ms_per_launch"] = kernels[top]["ms_per_launch"]
     # dram__bytes_read.sum + dram__bytes_write.sum per launch of that kernel, from the committed ncu --set full
-    # capture of this same command (profiles/r1_traffic.json; not measured live: ncu replays kernels)
+    # capture of this same command (profiles/r2_traffic.json; not measured live: ncu replays kernels)
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))[args.workload].get(top)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))[args.workload].get(top)
     except Exception:
         pass
-    roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": traffic, "peak_source": "measured" if peaks else "fallback",
-                "note": "compositing kernels are FP32/SFU-issue bound, not HBM bound; see kernels{} and DESIGN.md"}
-    # what does bound it: issue-slot and pipe utilisation of the same kernel from the committed ncu --set full capture
-    try:
-        for r in json.load(open(os.path.join(ROOT, "profiles", f"r1_ncu_{args.workload}_step.json"))):
-            if r["kernel"].startswith(top):
-                roofline["ncu"] = {"issue_slots_busy_pct": r["issue %"], "fma_pipe_pct": r["fma %"], "alu_pipe_pct": r["alu %"],
-                                   "xu_pipe_pct": r["xu %"], "dram_pct": r["dram %"], "source": f"profiles/r1_ncu_{args.workload}_step.json"}
-    except Exception:
-        pass
+    roofline["traffic"] = traffic
+    roofline["fp32_peaks"] = fp32
 
     line = {
-        "metric": "rasterizer fwd+bwd Mpix/s", "value": world * mpix / (ms_step * 1e-3), "unit": "Mpix/s",
+        "metric": "rasterizer fwd+bwd Mpix/s", "value": mpix / (ms_step * 1e-3), "unit": "Mpix/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "gaussians": P, "views_per_gpu": V, "width": W, "height": H,
-                   "instances_per_step": int(R_step), "l2": "flushed between steps (256 MB write)",
-                   "parallelism": f"views x{world}" + ((" + 1 flat gradient all-reduce (" + ("csb_peer_all_reduce over NVLink peer memory" if bucket.peer else "NCCL")
+        "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": main["desc"], "gaussians": P, "views_per_gpu": V, "width": W, "height": H,
+                   "instances_per_step": main["R_step"], "l2": "flushed between steps (256 MB write)",
+                   "parallelism": f"views x{world}" + ((" + 1 flat gradient all-reduce (" + ("csb_peer_all_reduce over NVLink peer memory" if main["peer"] else "NCCL")
                                                              + ")") if world > 1 else "")},
-        "e2e": {"value": world * mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e,
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+        "e2e": {"value": mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": main["h2d"], "d2h_bytes_per_step": main["d2h"],
                 "api": "diff_gaussian_rasterization.rasterize_views + autograd backward"
                        + " (dL/dpixel uploaded and consumed view by view: StagedPixelGrads / backward_staged)"},
-        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
-        "impl": "b200",
+        "gpu_launches": main["launches"], "clocks": clocks, "roofline": roofline, "kernels": kernels,
+        "impl": "b200", "render_variant": int(lib.csb_debug_render_variant(-1)),
         # spread of the timed steps on rank 0 (device time): what a synchronous all-reduce turns into rank skew
         "step_ms_spread": {"min": min(ms_all), "median": statistics.median(ms_all), "max": max(ms_all),
                            "std": statistics.pstdev(ms_all)},
     }
-    if allreduce:
-        line["allreduce"] = allreduce
+    if main.get("pairs_per_step"):
+        line["config"]["pairs_per_step"] = main["pairs_per_step"]
+    if main["allreduce"]:
+        line["allreduce"] = main["allreduce"]
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        g_np, cams, dl_np, _ = make_workload(args.workload, rank, world)
         line["cpu_baseline"] = cpu_baseline(g_np, cams, dl_np)
+    # ---- the other configurations of BASELINE.json, one sub-record each ------------------------------------
+    if not args.no_sub and args.workload == "c2":
+        # C4: 100k Gaussians x 64 views split over the ranks (strong scaling), gradients all-reduced once per step
+        c4 = raster_leg("c4", rank, world, dev, max(3, args.steps // 6), 3, fp32, peaks, with_e2e=False)
+        if rank == 0:
+            line["c4"] = {"workload": c4["desc"], "scaling": "strong", "views_total": c4["V"] * world,
+                          "views_per_gpu": c4["V"], "ms_per_step": c4["ms_step"],
+                          "value": c4["V"] * world * c4["H"] * c4["W"] / 1e6 / (c4["ms_step"] * 1e-3), "unit": "Mpix/s",
+                          "instances_per_step_per_gpu": c4["R_step"], "gpu_launches": c4["launches"],
+                          "kernels": c4["kernels"], "allreduce": c4["allreduce"]}
+        if rank == 0 and world == 1:
+            c3 = raster_leg("c3", rank, world, dev, max(3, args.steps // 3), 3, fp32, peaks, with_e2e=False)
+            line["c3"] = {"workload": c3["desc"], "ms_per_step": c3["ms_step"],
+                          "value": c3["H"] * c3["W"] / 1e6 / (c3["ms_step"] * 1e-3), "unit": "Mpix/s",
+                          "instances_per_step": c3["R_step"], "pairs_per_step": c3.get("pairs_per_step"),
+                          "gpu_launches": c3["launches"], "kernels": c3["kernels"]}
+            k3 = c3["kernels"]
+            mine = sum(k3[k]["ms_per_step"] for k in ("sort_onesweep", "sort_histogram", "emit", "tile_ranges") if k in k3)
+            line["sort"] = {"instances": c3["R_step"],
+                            "b200_ms": mine,
+                            "b200_stages": "depth sort (4 onesweep passes over V*P u32 keys) + emit (scan + duplicate) + "
+                                           "tile sort (2 passes over the 13 tile bits) + tile_ranges, inside the C3 step",
+                            "reference_stages": "InclusiveSum + duplicateWithKeys + cub::DeviceRadixSort::SortPairs(u64,u32; "
+                                                "45 bits) + identifyTileRanges: see the reference arm's `stages` record"}
+            line["knn"] = knn_bench(dev, "b200", flush)
+        if world > 1:
+            dist.barrier()
     if not args.no_gnn:
         l0 = lib.csb_launch_count()
         if rank == 0:
@@ -557,7 +700,7 @@ def run_b200(args, rank, world, dev):
         if world > 1:
             dist.barrier()
         # every rank trains on its own 128 graphs of C5 (1024 graphs over 8 GPUs), gradients all-reduced
-        tr = gnn_train_bench(dev, "b200", peaks, args.gnn_graphs, world=world)
+        tr = gnn_train_bench(dev, "b200", peaks, args.gnn_graphs, world=world, rank=rank)
         if world > 1:
             tms = torch.tensor([tr["ms_per_step"]], dtype=torch.float64, device=dev)
             dist.all_reduce(tms, op=dist.ReduceOp.MAX)
@@ -570,6 +713,11 @@ def run_b200(args, rank, world, dev):
         l0 = lib.csb_launch_count()
         line["refine_tail"] = loss_adam_bench(dev, "b200", peaks, flush)
         line["refine_tail"]["gpu_launches"] = int(lib.csb_launch_count() - l0)
+    if rank == 0 and world == 1 and not args.no_dropin and args.workload == "c2":
+        try:
+            line["dropin"] = dropin_bench(dev, "b200")
+        except Exception as ex:  # the sub-record must never cost the headline
+            line["dropin"] = {"error": repr(ex)}
     if rank == 0:
         print(json.dumps(line), flush=True)
 
@@ -672,28 +820,69 @@ def cpu_baseline(g_np, cams, dl_np, budget_s=12.0):
             "sample": f"{n} x (view 0 of the workload, {W}x{H}, fwd+bwd) with the OpenMP C oracle (oracle/rast_oracle*.c)"}
 
 
-def run_reference(args, rank, world, dev):
+def reference_gnn_module():
+    """The reference's own meshnet/graph_network.py (copied unmodified into git-ignored baseline/_ref/ by
+    __graft_entry__.build(), so that it travels to the GPU box) imported under oracle/pyg_stub, the stand-in for the one
+    torch_geometric class it needs (real torch_geometric is not installable in this image)."""
+    import importlib.util
+
+    path = os.path.join(ROOT, "baseline", "_ref", "meshnet", "graph_network.py")
+    if not os.path.exists(path):
+        return None
+    stub = os.path.join(ROOT, "oracle", "pyg_stub")
+    if stub not in sys.path:
+        sys.path.insert(0, stub)
+    spec = importlib.util.spec_from_file_location("ref_graph_network", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def ref_stage_times(fn_fwd, fn_bwd):
+    """Per-kernel device time of one forward and one backward of the UNMODIFIED reference, from CUPTI through
+    torch.profiler (the kernels are launched by oracle/_ref/libref_cuda.so; nothing is re-stated or instrumented)."""
+    try:
+        from torch.profiler import ProfilerActivity, profile
+    except Exception:
+        return None
+
+    def grab(fn):
+        fn()
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            fn()
+            torch.cuda.synchronize()
+        out = {}
+        for ev in prof.events():
+            if getattr(ev, "device_type", None) is not None and "cuda" in str(ev.device_type).lower():
+                name = ev.name
+                for key, stage in (("preprocessCUDA", "preprocess"), ("computeCov2DCUDA", "computeCov2D"),
+                                   ("DeviceScan", "InclusiveSum"), ("duplicateWithKeys", "duplicateWithKeys"),
+                                   ("DeviceRadixSort", "SortPairs"), ("identifyTileRanges", "identifyTileRanges"),
+                                   ("renderCUDA", "render"), ("Memcpy", "memcpy"), ("Memset", "memset")):
+                    if key in name:
+                        out[stage] = out.get(stage, 0.0) + ev.device_time / 1e3  # us -> ms
+                        break
+                else:
+                    out["other"] = out.get("other", 0.0) + ev.device_time / 1e3
+        return out
+
+    try:
+        return {"forward_ms": grab(fn_fwd), "backward_ms": grab(fn_bwd),
+                "how": "torch.profiler (CUPTI) kernel durations of one warm call of the unmodified reference"}
+    except Exception as ex:
+        return {"error": repr(ex)}
+
+
+def ref_raster_leg(workload, dev, steps, warmup, with_e2e=True, with_stages=False):
+    """The reference's own kernels (compiled unmodified for sm_100a) on this B200, view by view like
+    train_utils.py:259 does.  The shim adds no synchronisation (torch's default stream is the legacy stream the
+    reference launches on); the reference's own blocking D2H of the instance count stays."""
     from oracle import ref_cuda
 
-    if rank != 0:
-        return
-    g_np, cams, dl_np, desc = make_workload(args.workload, 0, 1)
+    g_np, cams, dl_np, desc = make_workload(workload, 0, 1)
     V, H, W = len(cams), cams[0].image_height, cams[0].image_width
     P = g_np["means3D"].shape[0]
-    mpix = V * H * W / 1e6
-    base = {"metric": "rasterizer fwd+bwd Mpix/s", "unit": "Mpix/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "impl": "reference",
-            "config": {"workload": desc, "gaussians": P, "views_per_gpu": V, "width": W, "height": H}}
-    if not (ref_cuda.available() and torch.cuda.is_available()):
-        cb = cpu_baseline(g_np, cams, dl_np, budget_s=20.0)
-        base.update(value=cb["value"], ms_per_step=mpix / cb["value"] * 1e3, cpu_baseline=cb,
-                    e2e={"value": cb["value"], "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                    gpu_launches=0)
-        print(json.dumps(base), flush=True)
-        return
-    # The reference's rasterizer exists only as CUDA: time its own kernels (compiled unmodified for
-    # sm_100a) on this B200, view by view like train_utils.py:259 does.
     host = {k: torch.from_numpy(g_np[k]).pin_memory() for k in PARAM_NAMES}
     dl_host = torch.from_numpy(dl_np).pin_memory()
     gd = {k: torch.empty(g_np[k].shape, dtype=torch.float32, device=dev) for k in PARAM_NAMES}
@@ -706,23 +895,23 @@ def run_reference(args, rank, world, dev):
     flush = l2_flusher(dev)
     stream = torch.cuda.current_stream()
 
+    def fwd(v):
+        t, c = cam_t[v], cams[v]
+        return ref.forward(gd["means3D"], gd["opacities"], t["viewmatrix"], t["projmatrix"], t["campos"], t["bg"],
+                           c.tanfovx, c.tanfovy, H, W, shs=gd["shs"], scales=gd["scales"], rotations=gd["rotations"],
+                           sh_degree=3, sync=False)
+
     def render_all():
         tot = None
-        for v, c in enumerate(cams):
-            t = cam_t[v]
-            ref.forward(gd["means3D"], gd["opacities"], t["viewmatrix"], t["projmatrix"], t["campos"], t["bg"],
-                        c.tanfovx, c.tanfovy, H, W, shs=gd["shs"], scales=gd["scales"], rotations=gd["rotations"],
-                        sh_degree=3)
-            g = ref.backward(dl[v])
+        for v in range(V):
+            fwd(v)
+            g = ref.backward(dl[v], sync=False)
             if tot is None:
                 tot = {k: g[k] for k in PARAM_NAMES}
             else:
                 for k in PARAM_NAMES:
                     tot[k] += g[k]
         return tot
-
-    def device_step():
-        render_all()
 
     def e2e_step():
         for k in PARAM_NAMES:
@@ -734,61 +923,104 @@ def run_reference(args, rank, world, dev):
         torch.cuda.synchronize()
 
     def timed(fn):
-        for _ in range(args.warmup):
+        for _ in range(warmup):
             fn()
         torch.cuda.synchronize()
-        ms = []
-        for _ in range(args.steps):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for a, b_ in ev:  # same loop as the product arm: events on the launching stream, read after the last step
             flush()
-            torch.cuda.synchronize()
-            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
             fn()
-            torch.cuda.synchronize()  # the reference launches on the legacy default stream
             b_.record(stream)
-            b_.synchronize()
-            ms.append(a.elapsed_time(b_))
+        torch.cuda.synchronize()
+        ms = [a.elapsed_time(b_) for a, b_ in ev]
         return sum(ms) / len(ms)
 
     for k in PARAM_NAMES:
         gd[k].copy_(host[k])
     dl.copy_(dl_host)
+    out = {"desc": desc, "V": V, "H": H, "W": W, "P": P, "ms_step": timed(render_all)}
+    if with_e2e:
+        out["ms_e2e"] = timed(e2e_step)
+        out["h2d"] = sum(t.numel() * 4 for t in host.values()) + dl_host.numel() * 4
+        out["d2h"] = sum(t.numel() * 4 for t in grads_host.values())
+    if with_stages:
+        out["stages"] = ref_stage_times(lambda: fwd(0), lambda: ref.backward(dl[0], sync=False))
+    out["R_view0"] = int(fwd(0)[0])
+    torch.cuda.synchronize()
+    return out
+
+
+def run_reference(args, rank, world, dev):
+    from oracle import ref_cuda
+
+    if rank != 0:
+        return
+    g_np, cams, dl_np, desc = make_workload(args.workload, 0, 1)
+    V, H, W = len(cams), cams[0].image_height, cams[0].image_width
+    P = g_np["means3D"].shape[0]
+    mpix = V * H * W / 1e6
+    base = {"metric": "rasterizer fwd+bwd Mpix/s", "unit": "Mpix/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "strong" if args.workload == "c4" else "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
+            "config": {"workload": desc, "gaussians": P, "views_per_gpu": V, "width": W, "height": H}}
+    if not (ref_cuda.available() and torch.cuda.is_available()):
+        cb = cpu_baseline(g_np, cams, dl_np, budget_s=20.0)
+        base.update(value=cb["value"], ms_per_step=mpix / cb["value"] * 1e3, cpu_baseline=cb,
+                    e2e={"value": cb["value"], "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                    gpu_launches=0)
+        print(json.dumps(base), flush=True)
+        return
+    flush = l2_flusher(dev)
+    peaks = load_peaks()
     sampler = ClockSampler(dev.index)
-    ms_dev = timed(device_step)
-    ms_e2e = timed(e2e_step)
+    main = ref_raster_leg(args.workload, dev, args.steps, args.warmup, with_e2e=True, with_stages=True)
     clocks = sampler.stop()
-    h2d = sum(t.numel() * 4 for t in host.values()) + dl_host.numel() * 4
-    d2h = sum(t.numel() * 4 for t in grads_host.values())
+    ms_dev, ms_e2e = main["ms_step"], main["ms_e2e"]
     base.update(
         value=mpix / (ms_dev * 1e-3), ms_per_step=ms_dev, clocks=clocks,
-        e2e={"value": mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
-             "d2h_bytes_per_step": d2h},
+        e2e={"value": mpix / (ms_e2e * 1e-3), "unit": "Mpix/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": main["h2d"],
+             "d2h_bytes_per_step": main["d2h"]},
         cpu_baseline={"value": mpix / (ms_dev * 1e-3), "unit": "Mpix/s", "cores": 0, "kind": "reference",
                       "sample": "the reference has no CPU rasterizer: its own CUDA kernels (forward.cu, backward.cu, "
                                 "rasterizer_impl.cu recompiled for sm_100a, CUB onesweep sort) on this B200, "
                                 f"{V} views sequentially per step"},
-        gpu_launches=0)
+        gpu_launches=0, stages=main.get("stages"))
     base["config"]["l2"] = "flushed between steps (256 MB write)"
+    if not args.no_sub and args.workload == "c2":
+        c4 = ref_raster_leg("c4", dev, 3, 3, with_e2e=False)
+        base["c4"] = {"workload": c4["desc"], "scaling": "strong", "views_total": c4["V"], "ms_per_step": c4["ms_step"],
+                      "value": c4["V"] * c4["H"] * c4["W"] / 1e6 / (c4["ms_step"] * 1e-3), "unit": "Mpix/s",
+                      "note": "one GPU renders the 64 views one after another (the reference is single-GPU)"}
+        c3 = ref_raster_leg("c3", dev, max(3, args.steps // 3), 3, with_e2e=False, with_stages=True)
+        base["c3"] = {"workload": c3["desc"], "ms_per_step": c3["ms_step"],
+                      "value": c3["H"] * c3["W"] / 1e6 / (c3["ms_step"] * 1e-3), "unit": "Mpix/s",
+                      "instances_per_step": c3["R_view0"], "stages": c3.get("stages")}
+        st = (c3.get("stages") or {}).get("forward_ms") or {}
+        if st:
+            base["sort"] = {"instances": c3["R_view0"],
+                            "reference_ms": sum(st.get(k, 0.0) for k in ("InclusiveSum", "duplicateWithKeys", "SortPairs",
+                                                                         "identifyTileRanges")),
+                            "SortPairs_ms": st.get("SortPairs"),
+                            "what": "InclusiveSum + duplicateWithKeys + cub::DeviceRadixSort::SortPairs (u64 keys, u32 "
+                                    "values, bits [0, 45)) + identifyTileRanges of the reference's C3 forward "
+                                    "(rasterizer_impl.cu:276-318)"}
+        base["knn"] = knn_bench(dev, "reference", flush)
     if not args.no_gnn:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        # the reference's GNN = stock PyTorch fp32 ops (index_select, cat, addmm, layer_norm, index_add_); its
-        # op sequence, restated in oracle/gnn_oracle.py (torch_geometric is not installed), timed on this B200
+        # the reference's GNN = its own meshnet/graph_network.py (nn.Module, fp32 torch ops) under the MessagePassing
+        # stand-in; if the copy did not travel, its op sequence restated in oracle/gnn_oracle.py
         base["gnn"] = gnn_bench(dev, "reference", peaks, flush, with_cpu=True)
         # bounded sample: torch autograd keeps every [E, 384] / [E, 128] activation of the 150 message-passing
         # steps of a 10-step rollout (~8 GB per graph-batch of 1), 128 graphs do not fit in 180 GB
         base["gnn"]["train_c5"] = gnn_train_bench(dev, "reference", peaks, args.gnn_ref_graphs, iters=3)
         base["gnn"]["train_c5"]["sample"] = f"{args.gnn_ref_graphs} of the 128 graphs a GPU owns in C5"
     if not args.no_loss:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
         base["refine_tail"] = loss_adam_bench(dev, "reference", peaks, flush)
+    if not args.no_dropin and args.workload == "c2":
+        try:
+            base["dropin"] = dropin_bench(dev, "reference")
+        except Exception as ex:
+            base["dropin"] = {"error": repr(ex)}
     print(json.dumps(base), flush=True)
 
 
@@ -802,6 +1034,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gnn", action="store_true")
     ap.add_argument("--no-loss", action="store_true", help="skip the image-loss / Adam leg")
+    ap.add_argument("--render-variant", type=int, default=-1,
+                    help="A/B timing: csb_debug_render_variant (0 one pixel per lane, 1 one pixel pair, 2 two pairs)")
+    ap.add_argument("--no-sub", action="store_true", help="skip the C3 / C4 / kNN / sort sub-records")
+    ap.add_argument("--no-dropin", action="store_true", help="skip the drop-in train_step sub-record")
     ap.add_argument("--gnn-graphs", type=int, default=128, help="graphs per GPU of the C5 training leg")
     ap.add_argument("--gnn-ref-graphs", type=int, default=4, help="graphs of the reference arm's bounded sample")
     args = ap.parse_args()

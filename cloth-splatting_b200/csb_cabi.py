@@ -81,6 +81,9 @@ _OPTIONAL = [
     ("csb_dist_cuda2_bytes", c_size_t, [c_int]),
     ("csb_dist_cuda2", c_int, [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     ("csb_launch_count", ctypes.c_ulonglong, []),
+    ("csb_debug_render_variant", c_int, [c_int]),
+    ("csb_measure_fp32_peaks", c_int, [c_void_p, c_size_t, POINTER(ctypes.c_double), POINTER(ctypes.c_double),
+                                       POINTER(ctypes.c_double), c_void_p]),
     ("csb_profile_enable", None, [c_int]),
     ("csb_profile_read", c_int, [c_char_p, POINTER(ctypes.c_double), POINTER(ctypes.c_ulonglong)]),
     ("csb_profile_names", c_int, [c_char_p, c_size_t]),

@@ -70,4 +70,9 @@ class Adam(torch.optim.Optimizer):
                 rc = lib.csb_adam_step(n, P, G, M, V, N, LR, b1, b2, eps, step, int(self.zero_grads),
                                        _abi.current_stream_ptr())
             _abi.check(rc, "csb_adam_step")
+            # the kernel wrote through raw pointers: tell autograd (saved-tensor checks) and every cache keyed on
+            # tensor versions (EncodeProcessDecode's packed bf16 weights) that these parameters changed
+            torch.autograd.graph.increment_version([p for p, _, _ in items])
+            if self.zero_grads:
+                torch.autograd.graph.increment_version([p.grad for p, _, _ in items])
         return loss

@@ -34,6 +34,7 @@ cudaEvent_t take_event() {
 }  // namespace
 
 namespace csb {
+int g_render_variant = 1;
 LaunchScope::LaunchScope(const char* name_, cudaStream_t stream_) : name(name_), stream(stream_), slot(-1) {
     g_launches.fetch_add(1, std::memory_order_relaxed);
     if (g_profile.load(std::memory_order_relaxed)) {
@@ -67,6 +68,12 @@ const char* csb_error_string(int code) {
 }
 
 unsigned long long csb_launch_count(void) { return g_launches.load(); }
+
+int csb_debug_render_variant(int variant) {
+    const int old = csb::g_render_variant;
+    if (variant >= 0 && variant <= 2) csb::g_render_variant = variant;
+    return old;
+}
 
 void csb_profile_enable(int on) {
     std::lock_guard<std::mutex> lk(g_mu);

@@ -73,6 +73,21 @@ static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 b
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: opt in once per (kernel, device), not once per
+// process (a process that drives a second GPU would otherwise launch > 48 KB kernels there without the opt-in).
+// `done_mask` is a caller-owned static bit mask over device ordinals (devices >= 64 set the attribute every time).
+template <typename K>
+static inline cudaError_t opt_in_dynamic_smem(K kernel, int bytes, unsigned long long* done_mask) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const unsigned long long bit = dev < 64 ? (1ull << dev) : 0ull;
+    if (bit && (__atomic_load_n(done_mask, __ATOMIC_ACQUIRE) & bit)) return cudaSuccess;
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess && bit) __atomic_fetch_or(done_mask, bit, __ATOMIC_RELEASE);
+    return e;
+}
+
 // Bump allocator over a caller-provided workspace (256-byte aligned slices).
 struct Carver {
     char* base;

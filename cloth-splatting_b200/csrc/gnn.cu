@@ -535,12 +535,9 @@ struct GraphWs {
 
 template <int MODE>
 static int launch_role(const Args& a, int kin, int nout, cudaStream_t stream, const char* name) {
-    static bool configured = false;
+    static unsigned long long configured = 0;  // per-device opt-in (common.cuh)
     const size_t smem = smem_bytes(MODE, kin, nout);
-    if (!configured) {
-        CSB_CUDA_TRY(cudaFuncSetAttribute(gnn_mlp_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 1024));
-        configured = true;
-    }
+    CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_mlp_kernel<MODE>, 232448 - 1024, &configured));
     if (smem > 232448 - 1024) return CSB_ERR_UNSUPPORTED;
     const int tiles = (a.rows + TILE_M - 1) / TILE_M;
     if (tiles == 0) return 0;
@@ -799,11 +796,8 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_edge2_kernel(const __grid_cons
 }
 
 static int launch_edge2(const Args& a, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
-        CSB_CUDA_TRY(cudaFuncSetAttribute(gnn_edge2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E2_SMEM));
-        configured = true;
-    }
+    static unsigned long long configured = 0;
+    CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_edge2_kernel, (int)E2_SMEM, &configured));
     const int tiles = (a.rows + TILE_M - 1) / TILE_M;
     if (tiles == 0) return 0;
     int dev = 0, sms = 148;

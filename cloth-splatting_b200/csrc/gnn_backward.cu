@@ -840,12 +840,9 @@ static int sm_count() {
 
 template <int MODE>
 static int launch_bwd(const BArgs& a, cudaStream_t stream, const char* name) {
-    static bool configured = false;
+    static unsigned long long configured = 0;  // per-device opt-in (common.cuh)
     const size_t smem = bwd_smem_bytes(MODE, a.kin, a.nout);
-    if (!configured) {
-        CSB_CUDA_TRY(cudaFuncSetAttribute(gnn_bwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 1024));
-        configured = true;
-    }
+    CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_bwd_kernel<MODE>, 232448 - 1024, &configured));
     if (smem > 232448 - 1024) return CSB_ERR_UNSUPPORTED;
     const int tiles = (a.rows + TILE_M - 1) / TILE_M;
     if (tiles == 0) return 0;
@@ -855,11 +852,8 @@ static int launch_bwd(const BArgs& a, cudaStream_t stream, const char* name) {
 }
 
 static int launch_wgrad(WArgs& w, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
-        CSB_CUDA_TRY(cudaFuncSetAttribute(gnn_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WGRAD_SMEM));
-        configured = true;
-    }
+    static unsigned long long configured = 0;
+    CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_wgrad_kernel, (int)WGRAD_SMEM, &configured));
     const int tiles = (w.rows + TILE_M - 1) / TILE_M;
     if (tiles == 0 || w.njobs == 0) return 0;
     int per_job = sm_count() / w.njobs;

@@ -8,7 +8,7 @@
 // The reference issues 9 global atomics per blended (pixel, Gaussian) pair.  Here the 32 pixels
 // of a warp are summed with shuffles first and one lane adds the warp's total, so the atomic
 // count drops by up to 32x; the per-pair arithmetic is unchanged.
-#include "rasterize_math.cuh"
+#include "render_lanes.cuh"
 
 namespace csb {
 
@@ -643,6 +643,26 @@ gaussian_backward_split_kernel(const ViewBatch vb, int S, int D, int M, const fl
 
 using namespace csb;
 
+static int launch_render_backward(cudaStream_t stream, dim3 grid, const ViewBatch& vb, const uint2* ranges,
+                                  const uint32_t* point_list, const float2* means2D, const float4* conic_opacity,
+                                  const float4* rgb_depth, const float* final_T, const uint32_t* n_contrib,
+                                  const float* dL_dpix, float* grad_acc, int view0) {
+    switch (g_render_variant) {
+        case 0:
+            CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, grid, dim3(CSB_TILE_PIX), 0, stream, vb, ranges, point_list, means2D,
+                                                             conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0));
+            break;
+        case 2:
+            CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_lanes_kernel<2>, grid, dim3(LaneTiling<2>::THREADS), 0, stream, vb, ranges, point_list,
+                                                             means2D, conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0));
+            break;
+        default:
+            CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_lanes_kernel<1>, grid, dim3(LaneTiling<1>::THREADS), 0, stream, vb, ranges, point_list,
+                                                             means2D, conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0));
+    }
+    return 0;
+}
+
 extern "C" {
 
 static int backward_impl(int num_views, const csb_view* views, int P, int D, int M, int width, int height,
@@ -675,26 +695,23 @@ static int backward_impl(int num_views, const csb_view* views, int P, int D, int
             // its event has fired, while the later views are still in flight
             for (int v = 0; v < num_views; ++v) {
                 if (view_ready[v]) CSB_CUDA_TRY(cudaStreamWaitEvent(stream, (cudaEvent_t)view_ready[v], 0));
-                CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, dim3(vb.gx, vb.gy, 1), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, point_list, g.means2D,
-                                                                          g.conic_opacity, g.rgb_depth, im.final_T,
-                                                                          im.n_contrib, dL_dpix, g.grad_acc, v));
+                rc = launch_render_backward(stream, dim3(vb.gx, vb.gy, 1), vb, im.ranges, point_list, g.means2D, g.conic_opacity,
+                                            g.rgb_depth, im.final_T, im.n_contrib, dL_dpix, g.grad_acc, v);
+                if (rc) return rc;
             }
         } else {
             dim3 tgrid(vb.gx, vb.gy, num_views);
-            CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, point_list, g.means2D,
-                                                                      g.conic_opacity, g.rgb_depth, im.final_T,
-                                                                      im.n_contrib, dL_dpix, g.grad_acc, 0));
+            rc = launch_render_backward(stream, tgrid, vb, im.ranges, point_list, g.means2D, g.conic_opacity, g.rgb_depth,
+                                        im.final_T, im.n_contrib, dL_dpix, g.grad_acc, 0);
+            if (rc) return rc;
         }
     }
     const float* cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
     const int gb = P < 148 * 256 ? 64 : 128;  // few Gaussians (C2: 10 k): smaller blocks reach every SM
     const size_t gsmem = (shs && dL_dsh) ? (size_t)2 * gb * (M * 3 + 1) * sizeof(float) : 0;
     {
-        static bool configured = false;
-        if (!configured) {
-            CSB_CUDA_TRY(cudaFuncSetAttribute(gaussian_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-            configured = true;
-        }
+        static unsigned long long configured = 0;
+        CSB_CUDA_TRY(opt_in_dynamic_smem(gaussian_backward_kernel, 64 * 1024, &configured));
     }
     if (gsmem > 64 * 1024) return CSB_ERR_UNSUPPORTED;
     const int S = num_views >= 8 ? 8 : (num_views >= 4 ? 4 : num_views);
@@ -702,11 +719,8 @@ static int backward_impl(int num_views, const csb_view* views, int P, int D, int
     const size_t ssmem = ((shs && dL_dsh) ? (size_t)(1 + S) * GB_SPLIT_G * pitch : 0) * sizeof(float) +
                          (size_t)S * GB_SPLIT_G * GB_PART * sizeof(float);
     if (S >= 2 && P < 148 * 256 && ssmem <= 64 * 1024) {
-        static bool configured_split = false;
-        if (!configured_split) {
-            CSB_CUDA_TRY(cudaFuncSetAttribute(gaussian_backward_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-            configured_split = true;
-        }
+        static unsigned long long configured_split = 0;
+        CSB_CUDA_TRY(opt_in_dynamic_smem(gaussian_backward_split_kernel, 64 * 1024, &configured_split));
         CSB_LAUNCH("gaussian_backward", stream, launch_pdl(gaussian_backward_split_kernel, dim3((P + GB_SPLIT_G - 1) / GB_SPLIT_G), dim3(GB_SPLIT_G * S), ssmem, stream,
             vb, S, D, M, means3D, shs, cov3D_precomp ? nullptr : scales, scale_modifier, rotations, cov3D, radii, g.clamped,
             g.grad_acc, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations));

@@ -3,7 +3,7 @@
 // Replaces CudaRasterizer::Rasterizer::forward (RAST/cuda_rasterizer/rasterizer_impl.cu:198-339)
 // and its kernels preprocessCUDA / duplicateWithKeys / identifyTileRanges / renderCUDA
 // (forward.cu:155-256, rasterizer_impl.cu:70-138, forward.cu:261-379).
-#include "rasterize_math.cuh"
+#include "render_lanes.cuh"
 
 namespace csb {
 
@@ -795,6 +795,27 @@ int fill_view_batch(ViewBatch& vb, int num_views, const csb_view* views, int P, 
 
 using namespace csb;
 
+// renderCUDA forward: the multi-pixel-per-lane kernels (render_lanes.cuh) unless the debugging knob asks for the first version
+static int launch_render_forward(cudaStream_t stream, dim3 tgrid, const ViewBatch& vb, const uint2* ranges,
+                                 const uint32_t* point_list, const float2* means2D, const float4* conic_opacity,
+                                 const float4* rgb_depth, float* final_T, uint32_t* n_contrib, float* out_color,
+                                 float* out_depth) {
+    switch (g_render_variant) {
+        case 0:
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, tgrid, dim3(CSB_TILE_PIX), 0, stream, vb, ranges, point_list, means2D,
+                                                            conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
+            break;
+        case 2:
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_lanes_kernel<2>, tgrid, dim3(LaneTiling<2>::THREADS), 0, stream, vb, ranges, point_list,
+                                                            means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
+            break;
+        default:
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_lanes_kernel<1>, tgrid, dim3(LaneTiling<1>::THREADS), 0, stream, vb, ranges, point_list,
+                                                            means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
+    }
+    return 0;
+}
+
 extern "C" {
 
 size_t csb_rasterize_geom_bytes(int num_views, int P) { return GeomState::carve(nullptr, num_views, P).bytes; }
@@ -851,11 +872,8 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
         const size_t rec_smem = (size_t)256 * (M * 3 + 1) * sizeof(float);
         const int stage_sh = (shs != nullptr && colors_precomp == nullptr && rec_smem <= 56 * 1024) ? 1 : 0;
         {
-            static bool configured = false;
-            if (!configured) {
-                CSB_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 56 * 1024));
-                configured = true;
-            }
+            static unsigned long long configured = 0;
+            CSB_CUDA_TRY(opt_in_dynamic_smem(preprocess_kernel, 56 * 1024, &configured));
         }
         CSB_LAUNCH("preprocess", stream, launch_pdl(preprocess_kernel, dim3(blocks), dim3(256), stage_sh ? rec_smem : 0, stream, vb, D, M, means3D, scales, scale_modifier, rotations, opacities,
                                                       shs, cov3D_precomp, colors_precomp, radii, g, stage_sh,
@@ -879,9 +897,8 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             CSB_LAUNCH("bin_sort", stream, launch_pdl(bin_sort_kernel, dim3(sblocks), dim3(256), 0, stream, im.ranges, (const uint32_t*)g.control,
                                                        (uint32_t)total_tiles, (const uint32_t*)fill_d, (const uint32_t*)fill_v, st, sv,
                                                        (flags & 1) ? b.keys : nullptr));
-            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, sv, g.means2D, g.conic_opacity,
-                                                                     g.rgb_depth, im.final_T, im.n_contrib, out_color,
-                                                                     out_depth));
+            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth);
+            if (rc) return rc;
             if (num_rendered_host && !early_count)
                 CSB_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost,
                                              stream));
@@ -916,16 +933,14 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             CSB_LAUNCH("tile_ranges", stream, launch_pdl(tile_ranges_kernel, dim3(rblocks), dim3(256), 0, stream, g.control + CTRL_NUM_RENDERED, st, sv, g.rgb_depth,
                                                             im.ranges, (flags & 1) ? b.keys : nullptr,
                                                             (uint32_t)vb.tiles));
-            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, sv, g.means2D, g.conic_opacity,
-                                                                     g.rgb_depth, im.final_T, im.n_contrib, out_color,
-                                                                     out_depth));
+            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth);
+            if (rc) return rc;
             if (tside != sorted_side(total_tiles)) return CSB_ERR_UNSUPPORTED;  // consumers recompute the side
         }
     } else {
         CSB_CUDA_TRY(cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream));
-        CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, dim3(tgrid), dim3(CSB_TILE_PIX), 0, stream, vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity,
-                                                                 g.rgb_depth, im.final_T, im.n_contrib, out_color,
-                                                                 out_depth));
+        rc = launch_render_forward(stream, tgrid, vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth);
+        if (rc) return rc;
     }
     if (num_rendered_host && !early_count)
         CSB_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost,

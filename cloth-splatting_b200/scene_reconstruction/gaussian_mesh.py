@@ -496,7 +496,14 @@ class MultiGaussianMesh(torch.nn.Module):
                                 n(self.face_bary), face_offset, n(self.face_ids).astype(np.float32)[:, None]), axis=1)
         names = ply_io.gaussian_attribute_names(f_dc.shape[1], f_rest.shape[1], self._scaling.shape[1], self._rotation.shape[1])
         ply_io.write_vertex_ply(os.path.join(path, "point_cloud.ply"), names, table)
-        mesh = {"pos": n(self.mesh.pos), "face": n(self.mesh.face)}
+        # every dataset the reference's loader reads (meshnet/data_utils.py:450-457): pos, norm, face, edge_index
+        from meshnet.mesh_data import face_to_edge, mesh_normals
+
+        edge_index = getattr(self.mesh, "edge_index", None)
+        if edge_index is None:
+            edge_index = face_to_edge(self.mesh.face, self.mesh.pos.shape[0])
+        mesh = {"pos": n(self.mesh.pos), "norm": n(mesh_normals(self.mesh.pos, self.mesh.face)), "face": n(self.mesh.face),
+                "edge_index": n(edge_index)}
         try:
             import h5py
 
@@ -521,7 +528,7 @@ class MultiGaussianMesh(torch.nn.Module):
             import h5py
 
             with h5py.File(os.path.join(path, "mesh.hdf5"), "r") as f:
-                mesh = {k: np.asarray(f[k]) for k in ("pos", "face")}
+                mesh = {k: np.asarray(f[k]) for k in f.keys()}
         else:
             mesh = dict(np.load(os.path.join(path, "mesh.npz")))
         T = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a), dtype=dt, device=device)  # noqa: E731
@@ -540,6 +547,13 @@ class MultiGaussianMesh(torch.nn.Module):
                            T(stack("scale_")), T(stack("rot_")), T(col["opacity"][:, None]))
         self.face_offset = torch.nn.Parameter(T(col["o"][:, None]))
         self.active_sh_degree = sh_degree
+        # the reference's load_ply rebuilds the rest-pose edge features regularization() reads (gaussian_mesh.py:467-480)
+        if "edge_index" in mesh:
+            self.set_edges(T(mesh["edge_index"], torch.long))
+        else:
+            from meshnet.mesh_data import face_to_edge
+
+            self.set_edges(face_to_edge(self.mesh.face, self.mesh.pos.shape[0]))
         return self
 
     def get_rotation(self, deformed_vertices=None):

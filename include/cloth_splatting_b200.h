@@ -55,6 +55,16 @@ unsigned long long csb_launch_count(void);
 void csb_profile_enable(int on);
 int csb_profile_read(const char* name, double* total_ms, unsigned long long* launches);
 int csb_profile_names(char* out, size_t out_bytes);
+/* Debugging / A-B timing knob (process-wide, like the profiler switch): which compositing kernels the rasterizer entry
+ * points launch.  0 = one pixel per lane (round-1 kernels), 1 = one vertical pixel pair per lane (default), 2 = two pairs
+ * per lane.  All three produce the same per-pixel bits in the forward pass.  Returns the previous value; values outside
+ * 0..2 only query. */
+int csb_debug_render_variant(int variant);
+/* Micro-benchmarks of the FP32 FMA pipe (scalar FFMA and packed FFMA2, FMAs per second) and of the SFU (MUFU.EX2 per
+ * second) on the current device: the denominators of bench.py's compositing roofline, measured in the same
+ * run as the kernels.  `scratch`: at least 8 * 256 * 4 bytes per SM of device memory.  Synchronises the stream. */
+int csb_measure_fp32_peaks(void* scratch, size_t scratch_bytes, double* ffma_per_s, double* ffma2_per_s,
+                           double* mufu_per_s, void* stream);
 
 /* ------------------------------------------------------------------------- *
  * Rasterizer

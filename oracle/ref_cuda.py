@@ -55,14 +55,18 @@ class RefRasterizer:
 
     def forward(self, means3D, opacities, viewmatrix, projmatrix, campos, bg, tanfovx, tanfovy, H, W, shs=None,
                 colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None, sh_degree=3,
-                scale_modifier=1.0):
+                scale_modifier=1.0, sync=True):
+        """sync=False: no host synchronisation is added around the call -- torch's default stream IS the legacy default
+        stream the reference launches on, so stream order already holds (bench.py times the reference this way; the
+        tests keep the conservative default)."""
         dev = means3D.device
         P = means3D.shape[0]
         M = shs.shape[1] if shs is not None else 0
         color = torch.zeros((3, H, W), dtype=torch.float32, device=dev)
         depth = torch.zeros((1, H, W), dtype=torch.float32, device=dev)
         radii = torch.zeros(P, dtype=torch.int32, device=dev)
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         R = lib().ref_rasterize_forward(
             self.ctx, ctypes.c_int(P), ctypes.c_int(sh_degree), ctypes.c_int(M), _p(bg), ctypes.c_int(W),
             ctypes.c_int(H), _p(means3D), _p(shs), _p(colors_precomp), _p(opacities), _p(scales),
@@ -78,14 +82,15 @@ class RefRasterizer:
                           scale_modifier=scale_modifier, radii=radii)
         return R, color, radii, depth
 
-    def backward(self, dL_dpix):
+    def backward(self, dL_dpix, sync=True):
         a = self._args
         dev = dL_dpix.device
         P, M = self.P, self.M
         z = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
         g = dict(means2D=z(P, 3), conic=z(P, 2, 2), opacities=z(P, 1), colors=z(P, 3), means3D=z(P, 3),
                  cov3D=z(P, 6), shs=z(P, max(M, 1), 3), scales=z(P, 3), rotations=z(P, 4))
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         rc = lib().ref_rasterize_backward(
             self.ctx, ctypes.c_int(P), ctypes.c_int(a["sh_degree"]), ctypes.c_int(M), ctypes.c_int(self.R),
             _p(a["bg"]), ctypes.c_int(self.W), ctypes.c_int(self.H), _p(a["means3D"]), _p(a["shs"]),
@@ -96,7 +101,8 @@ class RefRasterizer:
             _p(g["shs"]), _p(g["scales"]), _p(g["rotations"]))
         if rc != 0:
             raise RuntimeError(f"reference backward failed: cudaError {-rc}")
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         if M == 0:
             g["shs"] = None
         return g

@@ -93,3 +93,30 @@ def test_adam_refuses_cpu_parameters():
         Adam([p], lr=1e-3).step()
     with pytest.raises(NotImplementedError):
         Adam([p], lr=1e-3, amsgrad=True)
+
+
+def test_adam_step_invalidates_the_packed_gnn_weights():
+    """csb_optim.Adam writes the parameters through raw pointers: it must bump their tensor versions, or
+    EncodeProcessDecode keeps using its cached packed bf16 weights and training silently does nothing."""
+    import csb_synth as S
+    from csb_optim import Adam
+    from meshnet import EncodeProcessDecode
+
+    x, ei, ef, _, _ = S.gnn_inputs(7, 3)
+    xt, eit, eft = (torch.from_numpy(a).cuda() for a in (x, ei, ef))
+    outs = {}
+    for name, opt_cls in (("csb", Adam), ("torch", torch.optim.Adam)):
+        torch.manual_seed(0)
+        m = EncodeProcessDecode(8, 3, 4, 128, 15, 2, 128).cuda()
+        opt = opt_cls(m.parameters(), lr=1e-3)
+        y0 = m(xt, eit, eft)
+        v0 = [p._version for p in m.parameters()]
+        y0.square().sum().backward()
+        opt.step()
+        assert all(p._version > v for p, v in zip(m.parameters(), v0)), name
+        with torch.no_grad():
+            y1 = m(xt, eit, eft)
+        assert float((y1 - y0.detach()).abs().max()) > 0, f"{name}: the forward after step() still sees the old weights"
+        outs[name] = y1
+    scale = float(outs["torch"].abs().max())
+    assert float((outs["csb"] - outs["torch"]).abs().max()) < 2e-2 * scale

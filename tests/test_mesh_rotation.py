@@ -34,6 +34,34 @@ def test_oracle_recovers_known_rigid_motion():
     assert float((MO.quat_product(ident, torch.from_numpy(qh)) - torch.from_numpy(qh)).abs().max()) < 1e-12
 
 
+def test_oracle_agrees_with_scipy():
+    """roma is not installable here (no network, not in the wheelhouse), so the restated oracle is cross-checked against
+    an independent third-party implementation that IS in the image: SciPy 1.18 `Rotation.align_vectors` (Kabsch with
+    the det correction), `Rotation.from_matrix(...).as_quat()` (the algorithm roma's rotmat_to_unitquat is adapted
+    from, XYZW) and rotation composition (= the quaternion product).  Noisy, non-rigid triangle pairs like the ones
+    get_rotation sees."""
+    from scipy.spatial.transform import Rotation
+
+    rng = np.random.default_rng(1)
+    n = 200
+    R, _ = _rand_rot(rng, n)
+    x = rng.standard_normal((n, 3, 3)) * 0.02          # rest triangle
+    y = np.einsum("nab,nkb->nka", R, x) + rng.standard_normal((n, 3, 3)) * 0.004 + 0.3   # deformed, not rigid
+    Rh = MO.rigid_points_registration(torch.from_numpy(x), torch.from_numpy(y)).numpy()
+    qh = MO.rotmat_to_unitquat(torch.from_numpy(Rh)).numpy()
+    p = rng.standard_normal((n, 4))
+    p /= np.linalg.norm(p, axis=1, keepdims=True)
+    comp = MO.quat_product(torch.from_numpy(p), torch.from_numpy(qh)).numpy()
+    for i in range(n):
+        xc, yc = x[i] - x[i].mean(0), y[i] - y[i].mean(0)
+        rs, _ = Rotation.align_vectors(yc, xc)          # y ~ R x
+        assert np.abs(rs.as_matrix() - Rh[i]).max() < 1e-7, i
+        qs = Rotation.from_matrix(Rh[i]).as_quat()
+        assert min(np.abs(qs - qh[i]).max(), np.abs(qs + qh[i]).max()) < 1e-9, i
+        cs = (Rotation.from_quat(p[i]) * Rotation.from_quat(qh[i])).as_quat()
+        assert min(np.abs(cs - comp[i]).max(), np.abs(cs + comp[i]).max()) < 1e-9, i
+
+
 def _case(n, per_face, seed, noise):
     verts, faces, _ = S.cloth_mesh(n)
     rng = np.random.default_rng(seed)

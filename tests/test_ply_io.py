@@ -79,3 +79,16 @@ def test_mesh_gaussians_round_trip(tmp_path):
     for a in ("face_bary", "face_offset", "_features_dc", "_features_rest", "_scaling", "_rotation", "_opacity"):
         assert torch.equal(getattr(r, a).detach(), getattr(m, a).detach()), a
     assert torch.equal(r.mesh.pos, m.mesh.pos) and r.active_sh_degree == 3
+    # the mesh file carries every dataset the reference's loader reads (meshnet/data_utils.py:450-457) ...
+    mesh_file = tmp_path / ("mesh.hdf5" if os.path.exists(tmp_path / "mesh.hdf5") else "mesh.npz")
+    if str(mesh_file).endswith(".npz"):
+        assert set(np.load(mesh_file).keys()) == {"pos", "norm", "face", "edge_index"}
+    # ... and a loaded model can run the regularisers (they read mesh.edge_index and edge_norm, set by set_edges)
+    import types
+
+    from scene_reconstruction.train_utils import regularization
+
+    opt = types.SimpleNamespace(lambda_deform_mag=0.1, lambda_rigid=0.5, lambda_momentum=0.1)
+    deform = torch.stack([r.mesh.pos, r.mesh.pos * 1.01, r.mesh.pos * 1.03])
+    assert r.mesh.edge_index.shape[0] == 2 and r.edge_norm.shape == (r.mesh.edge_index.shape[1], 1)
+    assert float(regularization(deform, r, opt)) > 0

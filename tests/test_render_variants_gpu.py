@@ -1,0 +1,79 @@
+"""The three generations of compositing kernels (csb_debug_render_variant: 0 = one pixel per lane, 1 = one vertical pixel
+pair per lane on packed fp32x2, 2 = two pairs per lane; csrc/render_lanes.cuh) against each other and against the
+reference's own CUDA (renderCUDA forward.cu:261-379, backward.cu:399-557).
+
+Forward: every per-pixel output bit for bit across the variants (same operand order, same FMA contraction, expf kept).
+Backward: the warp-reduced sums differ in association only -> 1e-4 relative, the north_star's gradient tolerance."""
+import contextlib
+
+import numpy as np
+import pytest
+import torch
+
+import conftest  # noqa: F401
+import csb_synth as S
+import helpers as Hh
+
+pytestmark = pytest.mark.gpu
+
+
+@contextlib.contextmanager
+def variant(v):
+    import csb_cabi
+
+    lib = csb_cabi.lib()
+    old = lib.csb_debug_render_variant(v)
+    try:
+        yield
+    finally:
+        lib.csb_debug_render_variant(old)
+
+
+def _scenes():
+    g, cam = Hh.small_scene(seed=11)
+    yield "small", g, [cam]
+    g, cam = Hh.small_scene(P=2000, W=149, H=83, seed=31)  # ragged: partial tiles on both edges
+    yield "ragged", g, [cam]
+    g, cams = S.config_c2(3, 800)
+    yield "c2", {k: g[k] for k in ("means3D", "scales", "rotations", "opacities", "shs")}, cams
+    g, cams = S.config_c3(100_000, 1920, 1080)  # long tile lists: several staged batches per tile, partial last tile row
+    yield "c3_100k", g, cams
+
+
+def test_variants_agree():
+    for name, g, cams in _scenes():
+        gc = Hh.to_cuda(g)
+        V, P = len(cams), g["means3D"].shape[0]
+        H, W = cams[0].image_height, cams[0].image_width
+        dl = torch.from_numpy(S.pixel_grad(V, H, W)).cuda()
+        res = {}
+        for v in (0, 1, 2):
+            with variant(v):
+                views, fwd = Hh.product_forward(gc, cams, 3)
+                grads = Hh.product_backward(gc, cams, views, fwd, dl, 3)
+                nc = Hh.product_state("n_contrib", torch.int32, (V, H, W), V, P, W, H, fwd)
+                fT = Hh.product_state("final_T", torch.float32, (V, H, W), V, P, W, H, fwd)
+                res[v] = (fwd[1].clone(), fwd[2].clone(), nc, fT, {k: t.clone() for k, t in grads.items()})
+        for v in (1, 2):
+            assert torch.equal(res[v][0], res[0][0]), f"{name}: colour of variant {v}"
+            assert torch.equal(res[v][1], res[0][1]), f"{name}: depth of variant {v}"
+            assert torch.equal(res[v][2], res[0][2]), f"{name}: n_contrib of variant {v}"
+            assert torch.equal(res[v][3], res[0][3]), f"{name}: final_T of variant {v}"
+            for k in ("means2D", "means3D", "opacities", "shs", "scales", "rotations", "cov3D"):
+                rel = Hh.rel_err(res[v][4][k].cpu().numpy(), res[0][4][k].cpu().numpy())
+                assert rel < (3e-4 if k == "cov3D" else 1e-4), f"{name}: grad {k} of variant {v}: rel {rel}"
+
+
+@pytest.mark.parametrize("v", [0, 2])  # variant 1 is the default every other test runs
+def test_variant_vs_reference_cuda(v):
+    from oracle import ref_cuda
+
+    if not ref_cuda.available():
+        pytest.skip("oracle/_ref/libref_cuda.so not built")
+    import test_rasterizer_gpu as T
+
+    with variant(v):
+        g, cam = Hh.small_scene(seed=13)
+        T._compare_with_reference(g, cam)
+        g, cams = S.config_c2(4, 800)
+        T._compare_with_reference({k: g[k] for k in ("means3D", "scales", "rotations", "opacities", "shs")}, cams[2])
