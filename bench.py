@@ -1034,8 +1034,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gnn", action="store_true")
     ap.add_argument("--no-loss", action="store_true", help="skip the image-loss / Adam leg")
-    ap.add_argument("--render-variant", type=int, default=-1,
-                    help="A/B timing: csb_debug_render_variant (0 one pixel per lane, 1 one pixel pair, 2 two pairs)")
+    ap.add_argument("--render-variant", type=lambda v: int(v, 0), default=-1,
+                    help="A/B timing: csb_debug_render_variant (low nibble forward kernel, high nibble backward kernel)")
     ap.add_argument("--no-sub", action="store_true", help="skip the C3 / C4 / kNN / sort sub-records")
     ap.add_argument("--no-dropin", action="store_true", help="skip the drop-in train_step sub-record")
     ap.add_argument("--gnn-graphs", type=int, default=128, help="graphs per GPU of the C5 training leg")

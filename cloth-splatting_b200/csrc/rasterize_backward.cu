@@ -647,19 +647,23 @@ static int launch_render_backward(cudaStream_t stream, dim3 grid, const ViewBatc
                                   const uint32_t* point_list, const float2* means2D, const float4* conic_opacity,
                                   const float4* rgb_depth, const float* final_T, const uint32_t* n_contrib,
                                   const float* dL_dpix, float* grad_acc, int view0) {
-    switch (g_render_variant) {
+#define CSB_RB_LANES(NP, MINB, DELAY)                                                                                    \
+    CSB_LAUNCH("render_backward", stream,                                                                                \
+               launch_pdl(render_backward_lanes_kernel<NP, MINB, DELAY>, grid, dim3(LaneTiling<NP>::THREADS), 0, stream, \
+                          vb, ranges, point_list, means2D, conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0))
+    switch ((g_render_variant >> 4) & 15) {
         case 0:
             CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, grid, dim3(CSB_TILE_PIX), 0, stream, vb, ranges, point_list, means2D,
                                                              conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0));
             break;
-        case 2:
-            CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_lanes_kernel<2>, grid, dim3(LaneTiling<2>::THREADS), 0, stream, vb, ranges, point_list,
-                                                             means2D, conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0));
-            break;
-        default:
-            CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_lanes_kernel<1>, grid, dim3(LaneTiling<1>::THREADS), 0, stream, vb, ranges, point_list,
-                                                             means2D, conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0));
+        case 2: CSB_RB_LANES(2, 1, false); break;
+        case 3: CSB_RB_LANES(1, 6, false); break;
+        case 4: CSB_RB_LANES(1, 1, true); break;
+        case 5: CSB_RB_LANES(1, 6, true); break;
+        case 6: CSB_RB_LANES(2, 1, true); break;
+        default: CSB_RB_LANES(1, 1, false);
     }
+#undef CSB_RB_LANES
     return 0;
 }
 

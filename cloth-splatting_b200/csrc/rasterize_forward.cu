@@ -800,7 +800,7 @@ static int launch_render_forward(cudaStream_t stream, dim3 tgrid, const ViewBatc
                                  const uint32_t* point_list, const float2* means2D, const float4* conic_opacity,
                                  const float4* rgb_depth, float* final_T, uint32_t* n_contrib, float* out_color,
                                  float* out_depth) {
-    switch (g_render_variant) {
+    switch (g_render_variant & 15) {
         case 0:
             CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, tgrid, dim3(CSB_TILE_PIX), 0, stream, vb, ranges, point_list, means2D,
                                                             conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));

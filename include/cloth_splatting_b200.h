@@ -56,9 +56,10 @@ void csb_profile_enable(int on);
 int csb_profile_read(const char* name, double* total_ms, unsigned long long* launches);
 int csb_profile_names(char* out, size_t out_bytes);
 /* Debugging / A-B timing knob (process-wide, like the profiler switch): which compositing kernels the rasterizer entry
- * points launch.  0 = one pixel per lane (round-1 kernels), 1 = one vertical pixel pair per lane (default), 2 = two pairs
- * per lane.  All three produce the same per-pixel bits in the forward pass.  Returns the previous value; values outside
- * 0..2 only query. */
+ * points launch.  Low nibble = forward kernel (0 = one pixel per lane, 1 = one vertical pixel pair per lane, 2 = two
+ * pairs), high nibble = backward kernel (0 = one pixel per lane, 1 / 2 = one / two pairs per lane, 3 = one pair under a
+ * register cap, 4 / 5 / 6 = 1 / 3 / 2 with the delayed warp reduction).  All forward kernels produce the same per-pixel
+ * bits.  Returns the previous value; a negative or out-of-range value only queries. */
 int csb_debug_render_variant(int variant);
 /* Micro-benchmarks of the FP32 FMA pipe (scalar FFMA and packed FFMA2, FMAs per second) and of the SFU (MUFU.EX2 per
  * second) on the current device: the denominators of bench.py's compositing roofline, measured in the same

@@ -1,6 +1,7 @@
-"""The three generations of compositing kernels (csb_debug_render_variant: 0 = one pixel per lane, 1 = one vertical pixel
-pair per lane on packed fp32x2, 2 = two pairs per lane; csrc/render_lanes.cuh) against each other and against the
-reference's own CUDA (renderCUDA forward.cu:261-379, backward.cu:399-557).
+"""The generations of compositing kernels (csb_debug_render_variant: low nibble = forward kernel, high nibble = backward
+kernel; 0 = one pixel per lane, 1 = one vertical pixel pair per lane on packed fp32x2, 2 = two pairs per lane, backward 3..6
+= register-capped / delayed-reduction builds; csrc/render_lanes.cuh) against each other and against the reference's own
+CUDA (renderCUDA forward.cu:261-379, backward.cu:399-557).
 
 Forward: every per-pixel output bit for bit across the variants (same operand order, same FMA contraction, expf kept).
 Backward: the warp-reduced sums differ in association only -> 1e-4 relative, the north_star's gradient tolerance."""
@@ -29,6 +30,9 @@ def variant(v):
         lib.csb_debug_render_variant(old)
 
 
+VARIANTS = (0x00, 0x11, 0x22, 0x30, 0x40, 0x50, 0x60)
+
+
 def _scenes():
     g, cam = Hh.small_scene(seed=11)
     yield "small", g, [cam]
@@ -47,14 +51,14 @@ def test_variants_agree():
         H, W = cams[0].image_height, cams[0].image_width
         dl = torch.from_numpy(S.pixel_grad(V, H, W)).cuda()
         res = {}
-        for v in (0, 1, 2):
+        for v in VARIANTS:
             with variant(v):
                 views, fwd = Hh.product_forward(gc, cams, 3)
                 grads = Hh.product_backward(gc, cams, views, fwd, dl, 3)
                 nc = Hh.product_state("n_contrib", torch.int32, (V, H, W), V, P, W, H, fwd)
                 fT = Hh.product_state("final_T", torch.float32, (V, H, W), V, P, W, H, fwd)
                 res[v] = (fwd[1].clone(), fwd[2].clone(), nc, fT, {k: t.clone() for k, t in grads.items()})
-        for v in (1, 2):
+        for v in VARIANTS[1:]:
             assert torch.equal(res[v][0], res[0][0]), f"{name}: colour of variant {v}"
             assert torch.equal(res[v][1], res[0][1]), f"{name}: depth of variant {v}"
             assert torch.equal(res[v][2], res[0][2]), f"{name}: n_contrib of variant {v}"
@@ -64,7 +68,7 @@ def test_variants_agree():
                 assert rel < (3e-4 if k == "cov3D" else 1e-4), f"{name}: grad {k} of variant {v}: rel {rel}"
 
 
-@pytest.mark.parametrize("v", [0, 2])  # variant 1 is the default every other test runs
+@pytest.mark.parametrize("v", [0x00, 0x22, 0x41, 0x60])  # the default variant is what every other test runs
 def test_variant_vs_reference_cuda(v):
     from oracle import ref_cuda
 
