@@ -796,6 +796,149 @@ def loss_adam_bench(dev, impl, peaks, flush, V=4, H=800, W=800, P=10108, iters=2
 
 
 # ------------------------------------------------------------------------------------------
+# The refinement iteration as a reference caller writes it (scene_reconstruction/train_utils.py:240-321)
+# ------------------------------------------------------------------------------------------
+def _dropin_options():
+    import types
+
+    return types.SimpleNamespace(
+        lambda_dssim=0.2, lambda_deform_mag=0.1, lambda_rigid=0.5, lambda_momentum=0.05, densify_until_iter=15000,
+        densify_from_iter=500, densification_interval=100, pruning_from_iter=500, pruning_interval=300,
+        opacity_reset_interval=3000, bary_cleanup=700, iterations=30000, opacity_threshold_fine_init=0.5,
+        opacity_threshold_fine_after=0.4, densify_grad_threshold_fine_init=1e-4, densify_grad_threshold_after=5e-5,
+        position_lr_init=1.6e-4, feature_lr=2.5e-3, opacity_lr=0.05, scaling_lr=5e-3, rotation_lr=1e-3)
+
+
+def dropin_bench(dev, impl, warm=8, steps=40, W=800, H=800):
+    """`train_step` with the reference's signature on a C2-sized scene (20x20 cloth, 10108 mesh-anchored Gaussians, the 3
+    consecutive-time views of a training item at 800x800): simulator -> get_xyz / get_rotation -> one GaussianRasterizer call per
+    view -> image_losses + regularisers -> backward -> densification statistics -> both Adam steps, the loss_dict `.item()`
+    reads included.  Wall clock per iteration (the loop synchronises once per iteration, like the reference's).
+      b200:      the package's train_step (CUDA graph replay between schedule events).
+      reference: the same loop over the reference's own CUDA rasterizer (oracle/_ref) behind an autograd wrapper, the reference's
+                 torch op sequences for the loss (oracle/loss_oracle.py), get_xyz / get_rotation (oracle/mesh_oracle.py: the
+                 batched SVD roma runs), torch.optim.Adam -- what train_utils.py:240-321 executes, where it can be run here."""
+    import types
+
+    from meshnet.meshnet_network import ResidualMeshSimulator
+    from scene_reconstruction.gaussian_mesh import MultiGaussianMesh
+
+    verts, faces, ei = S.cloth_mesh(20)
+    pos = torch.from_numpy(verts).to(dev)
+    g = torch.Generator(device=dev).manual_seed(0)
+    pc = MultiGaussianMesh.from_mesh(pos, torch.from_numpy(np.ascontiguousarray(faces.T)).to(dev), gaussian_init_factor=14,
+                                     generator=g)
+    pc.set_edges(torch.from_numpy(ei).to(dev))
+    pc.active_sh_degree = 3
+    with torch.no_grad():
+        pc._opacity.add_(2.0)
+        pc._features_dc.add_(torch.randn(pc._features_dc.shape, device=dev, generator=g))
+    opt = _dropin_options()
+    pc.training_setup(opt)
+    pc.init_densification_stats(0.01)
+    sim = ResidualMeshSimulator(torch.stack([pos, pos + 0.01, pos + 0.02]), device=dev)
+    mesh_opt = torch.optim.Adam(sim.parameters(), lr=1e-4)
+    cams = S.ring_cameras(3, W, H, 0.6911, verts.mean(0))
+    for i, cam in enumerate(cams):
+        for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+            setattr(cam, k, torch.from_numpy(getattr(cam, k)).to(dev))
+        cam.time, cam.mask = i / 2, None
+        cam.original_image = torch.rand((3, H, W), generator=torch.Generator().manual_seed(i)).pin_memory()
+    bg = torch.ones(3, device=dev)
+    pipe, uargs = types.SimpleNamespace(compute_cov3D_python=False), types.SimpleNamespace(no_shadow=True)
+
+    if impl == "b200":
+        from scene_reconstruction.train_utils import train_step
+
+        def step(it):
+            return train_step(it, cams, pc, sim, mesh_opt, pipe, opt, 5.0, bg, user_args=uargs)
+    else:
+        step = _reference_train_step(dev, pc, sim, mesh_opt, cams, opt, bg)
+
+    losses, t = [], []
+    for it in range(1, warm + steps + 1):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        _, loss, _ = step(it)
+        torch.cuda.synchronize()
+        t.append((time.perf_counter() - t0) * 1e3)
+        losses.append(float(loss))
+    ms = sorted(t[warm:])
+    med = ms[len(ms) // 2]
+    return {"what": "train_step (reference signature), 3 views 800x800, 10108 Gaussians, SH 3, one iteration", "impl": impl,
+            "steps": steps, "warmup": warm, "ms_per_iteration": med, "ms_min": ms[0], "ms_max": ms[-1],
+            "mpix_per_s": 3 * W * H / med / 1e3, "loss_first": losses[0], "loss_last": losses[-1],
+            "timing": "wall clock around the call, device synchronised on both sides"}
+
+
+def _reference_train_step(dev, pc, sim, mesh_opt, cams, opt, bg):
+    """The reference's iteration with the reference's kernels and op sequences (see dropin_bench)."""
+    import math
+
+    from oracle import loss_oracle, mesh_oracle, ref_cuda
+    from scene_reconstruction.train_utils import regularization
+
+    refs = [ref_cuda.RefRasterizer() for _ in cams]
+
+    class RefRaster(torch.autograd.Function):  # rasterize_gaussians / _RasterizeGaussians of the reference, over its own CUDA
+        @staticmethod
+        def forward(ctx, v, means3D, means2D, shs, opacities, scales, rotations):
+            cam = cams[v]
+            R, color, radii, depth = refs[v].forward(
+                means3D.detach(), opacities.detach(), cam.world_view_transform, cam.full_proj_transform, cam.camera_center, bg,
+                math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), int(cam.image_height), int(cam.image_width),
+                shs=shs.detach().contiguous(), scales=scales.detach(), rotations=rotations.detach().contiguous(), sh_degree=3,
+                sync=False)
+            ctx.v = v
+            ctx.mark_non_differentiable(radii, depth)
+            return color, radii, depth
+
+        @staticmethod
+        def backward(ctx, dcolor, _r, _d):
+            g = refs[ctx.v].backward(dcolor.contiguous(), sync=False)
+            return None, g["means3D"], g["means2D"], g["shs"], g["opacities"], g["scales"], g["rotations"]
+
+    params = [pc.face_bary, pc._features_dc, pc._features_rest, pc._opacity, pc._scaling, pc._rotation]
+    groups = [{"params": [p], "lr": lr} for p, lr in zip(params, (1.6e-4, 2.5e-3, 1.25e-4, 0.05, 5e-3, 1e-3))]
+    gopt = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+    rest = pc.mesh.pos
+    face, ids = pc.mesh.face, pc.face_ids
+
+    def step(it):
+        pk = []
+        for v, cam in enumerate(cams):
+            tvec = torch.full((rest.shape[0], 1), float(cam.time), device=dev)
+            verts = sim(time_vector=tvec)  # the reference's forward, device-to-host bounds check included
+            xyz = mesh_oracle.get_xyz(verts, face, ids, pc.face_bary)
+            rot = mesh_oracle.get_rotation(rest, verts, face, ids, pc._rotation)
+            m2 = torch.zeros_like(xyz, requires_grad=True)
+            color, radii, depth = RefRaster.apply(v, xyz, m2, pc.get_features, pc.get_opacity, pc.get_scaling, rot)
+            pk.append((color, radii, verts, m2))
+        img = torch.stack([p[0] for p in pk])
+        gt = torch.stack([c.original_image.to(dev, non_blocking=True) for c in cams])
+        mse = ((img - gt) ** 2).view(img.shape[0], -1).mean(1, keepdim=True)
+        ps = (20 * torch.log10(1.0 / torch.sqrt(mse))).mean().double()
+        loss, l1, ssim_loss = loss_oracle.image_losses(img, gt, opt.lambda_dssim)
+        d = {"l1": l1.item(), "ssim_loss": ssim_loss.item()}  # the reference's two .item() reads (train_utils.py:66-71)
+        loss = loss + regularization(torch.stack([p[2] for p in pk]), pc, opt)
+        loss.backward()
+        with torch.no_grad():
+            grad = sum(p[3].grad for p in pk)
+            radii = torch.stack([p[1] for p in pk]).max(0).values
+            seen = torch.stack([p[1] > 0 for p in pk]).any(0)
+            pc.max_radii2D[seen] = torch.max(pc.max_radii2D[seen], radii[seen].float())  # the reference's mask indexing
+            pc.pos_gradient_accum[seen] += torch.norm(grad[seen, :2], dim=-1, keepdim=True)
+            pc.denom[seen] += 1
+            gopt.step()
+            mesh_opt.step()
+            gopt.zero_grad(set_to_none=True)
+            mesh_opt.zero_grad()
+        return ps, loss.detach(), d
+
+    return step
+
+
+# ------------------------------------------------------------------------------------------
 # CPU baseline (oracle port on the host cores) and reference arm
 # ------------------------------------------------------------------------------------------
 def cpu_baseline(g_np, cams, dl_np, budget_s=12.0):

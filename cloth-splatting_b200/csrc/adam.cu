@@ -22,6 +22,7 @@ struct AdamTable {
     long long numel[ADAM_MAX_TENSORS];
     unsigned block_end[ADAM_MAX_TENSORS];  // exclusive prefix end of the blocks of tensor i
     float neg_step_size[ADAM_MAX_TENSORS]; // -(lr / (1 - beta1^t))
+    double lr[ADAM_MAX_TENSORS];           // capturable mode: the step size is formed on the device
     unsigned char vec[ADAM_MAX_TENSORS];   // all four pointers 16-byte aligned
     int n;
 };
@@ -33,7 +34,17 @@ struct AdamScalars {
     float bc2_sqrt;  // sqrt(1 - beta2^t)
     float eps;
     int zero_grads;
+    // capturable mode (CUDA graphs): the step count lives on the device; adam_advance_kernel derives the two bias
+    // corrections from it in double, like torch does on the host, and the step kernel reads them from here
+    const double* dev_bias;  // [0] = 1 - beta1^t, [1] = sqrt(1 - beta2^t); nullptr: host-side scalars above
 };
+
+__global__ void adam_advance_kernel(long long* step, double beta1, double beta2, double* bias) {
+    const long long t = *step + 1;
+    *step = t;
+    bias[0] = 1.0 - pow(beta1, (double)t);
+    bias[1] = sqrt(1.0 - pow(beta2, (double)t));
+}
 
 __device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v, float nss, const AdamScalars& s) {
     m = __fadd_rn(m, __fmul_rn(s.w1, __fsub_rn(g, m)));                    // exp_avg.lerp_(grad, 1 - beta1)
@@ -43,7 +54,8 @@ __device__ __forceinline__ void adam_update(float& p, float g, float& m, float& 
 }
 
 __global__ void __launch_bounds__(256)
-adam_step_kernel(const __grid_constant__ AdamTable t, const AdamScalars s) {
+adam_step_kernel(const __grid_constant__ AdamTable t, const AdamScalars s_in) {
+    AdamScalars s = s_in;
     // which tensor owns this block
     int lo = 0, hi = t.n - 1;
     while (lo < hi) {
@@ -58,7 +70,11 @@ adam_step_kernel(const __grid_constant__ AdamTable t, const AdamScalars s) {
     float* __restrict__ G = t.g[ti];
     float* __restrict__ M = t.m[ti];
     float* __restrict__ V = t.v[ti];
-    const float nss = t.neg_step_size[ti];
+    float nss = t.neg_step_size[ti];
+    if (s.dev_bias) {
+        nss = (float)(-(t.lr[ti] / s.dev_bias[0]));
+        s.bc2_sqrt = (float)s.dev_bias[1];
+    }
     if (t.vec[ti] && base + ADAM_BLOCK_ELEMS <= n) {
 #pragma unroll
         for (int k = 0; k < ADAM_BLOCK_ELEMS / (256 * 4); ++k) {
@@ -92,13 +108,19 @@ adam_step_kernel(const __grid_constant__ AdamTable t, const AdamScalars s) {
 
 using namespace csb;
 
-extern "C" int csb_adam_step(int n_tensors, float* const* params, float* const* grads, float* const* exp_avg,
-                             float* const* exp_avg_sq, const int64_t* numel, const double* lr, double beta1,
-                             double beta2, double eps, int step, int zero_grads, void* stream_) {
-    if (n_tensors < 0 || step < 1) return CSB_ERR_BAD_ARG;
+static int adam_step_impl(int n_tensors, float* const* params, float* const* grads, float* const* exp_avg,
+                          float* const* exp_avg_sq, const int64_t* numel, const double* lr, double beta1,
+                          double beta2, double eps, int step, long long* step_dev, double* bias_dev, int zero_grads,
+                          void* stream_) {
+    if (n_tensors < 0 || (step < 1 && !step_dev)) return CSB_ERR_BAD_ARG;
     if (n_tensors == 0) return 0;
     if (!params || !grads || !exp_avg || !exp_avg_sq || !numel || !lr) return CSB_ERR_BAD_ARG;
+    if (step_dev && !bias_dev) return CSB_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
+    if (step_dev) {
+        step = 1;  // placeholders below; the kernel takes the device values
+        CSB_LAUNCH("adam_advance", stream, adam_advance_kernel<<<1, 1, 0, stream>>>(step_dev, beta1, beta2, bias_dev));
+    }
     // torch/optim/adam.py: bias_correction1 = 1 - beta1 ** step; step_size = lr / bias_correction1;
     // bias_correction2_sqrt = sqrt(1 - beta2 ** step)   (Python floats = doubles)
     const double bc1 = 1.0 - __builtin_pow(beta1, (double)step);
@@ -110,6 +132,7 @@ extern "C" int csb_adam_step(int n_tensors, float* const* params, float* const* 
     s.bc2_sqrt = (float)bc2_sqrt;
     s.eps = (float)eps;
     s.zero_grads = zero_grads;
+    s.dev_bias = step_dev ? bias_dev : nullptr;
 
     AdamTable t;
     t.n = 0;
@@ -140,8 +163,25 @@ extern "C" int csb_adam_step(int n_tensors, float* const* params, float* const* 
         blocks += (unsigned)nb;
         t.block_end[k] = blocks;
         t.neg_step_size[k] = (float)(-(lr[i] / bc1));
+        t.lr[k] = lr[i];
         t.vec[k] = ((((uintptr_t)params[i]) | ((uintptr_t)grads[i]) | ((uintptr_t)exp_avg[i]) |
                      ((uintptr_t)exp_avg_sq[i])) & 15u) == 0;
     }
     return flush();
+}
+
+extern "C" int csb_adam_step(int n_tensors, float* const* params, float* const* grads, float* const* exp_avg,
+                             float* const* exp_avg_sq, const int64_t* numel, const double* lr, double beta1,
+                             double beta2, double eps, int step, int zero_grads, void* stream_) {
+    return adam_step_impl(n_tensors, params, grads, exp_avg, exp_avg_sq, numel, lr, beta1, beta2, eps, step, nullptr,
+                          nullptr, zero_grads, stream_);
+}
+
+extern "C" int csb_adam_step_capturable(int n_tensors, float* const* params, float* const* grads,
+                                        float* const* exp_avg, float* const* exp_avg_sq, const int64_t* numel,
+                                        const double* lr, double beta1, double beta2, double eps, long long* step_dev,
+                                        double* bias_dev, int zero_grads, void* stream_) {
+    if (!step_dev || !bias_dev) return CSB_ERR_BAD_ARG;
+    return adam_step_impl(n_tensors, params, grads, exp_avg, exp_avg_sq, numel, lr, beta1, beta2, eps, 0, step_dev,
+                          bias_dev, zero_grads, stream_);
 }

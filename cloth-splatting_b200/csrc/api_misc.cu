@@ -34,7 +34,7 @@ cudaEvent_t take_event() {
 }  // namespace
 
 namespace csb {
-int g_render_variant = 0x10;
+int g_render_variant = 0x40;  // forward: one pixel per lane; backward: one pixel pair per lane, delayed reduction (measured best on B200)
 LaunchScope::LaunchScope(const char* name_, cudaStream_t stream_) : name(name_), stream(stream_), slot(-1) {
     g_launches.fetch_add(1, std::memory_order_relaxed);
     if (g_profile.load(std::memory_order_relaxed)) {

@@ -40,8 +40,23 @@ _small_bins = {}
 _ring_next = {}
 
 
+_reserved_words = []  # pinned words handed out next (set by reserve_count_words for a CUDA-graph capture)
+_captured_forwards = []  # PendingCount of every forward recorded into a CUDA graph since the list was last cleared
+
+
+def reserve_count_words(n):
+    """Pinned count words for the next `n` forwards, allocated NOW: a forward that is being captured in a CUDA graph must
+    not allocate pinned memory, and its word must not be recycled by the ring while the graph lives.  Returns the
+    tensor [n] (keep it alive with the graph; after a replay word i holds the instance count of the i-th forward)."""
+    t = torch.full((n,), -1, dtype=torch.int32).pin_memory()
+    _reserved_words[:] = [t[i:i + 1] for i in range(n)]
+    return t
+
+
 def _pinned_word(device):
     """One int32 word of a pinned (device-accessible) ring per device: calls in flight never share a word."""
+    if _reserved_words:
+        return _reserved_words.pop(0)
     t = _pinned_counter.get(device)
     if t is None:
         t = torch.zeros(_RING, dtype=torch.int32).pin_memory()
@@ -99,6 +114,21 @@ class PendingCount:
 
     __int__ = wait
     __index__ = wait
+
+    def check_replay(self):
+        """After a replay of the graph this forward was captured into (and a synchronisation): did the frame fit the
+        workspace the graph owns?  Updates the size hints like wait() does; False = the images of that replay are
+        incomplete and the graph must be captured again."""
+        v = int(self.word.item()) & 0xFFFFFFFF
+        if v == 0xFFFFFFFF:
+            return True  # not replayed yet
+        if self.small and v == _COUNT_REFUSED:
+            _small_bins[self.key] = False
+            return False
+        _capacity_hint[self.key] = max(v, _capacity_hint.get(self.key, 0))
+        if self.small and v > 96 * self.n_tiles:
+            _small_bins[self.key] = False
+        return v <= self.capacity
 
 
 def _f32c(t, name):
@@ -166,6 +196,12 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
     key = (dev, V, P, W, H)
     hint = _capacity_hint.get(key, 0)
     capacity = max(int(hint * 1.25) + 4096 if hint else 0, _PER_GAUSSIAN * V * P, _MIN_CAPACITY) if P else 0
+    capturing = torch.cuda.is_current_stream_capturing()
+    if capturing:
+        # a captured forward is replayed on later frames with this workspace: no host word to poll, no retry, so the count
+        # is deferred (the owner of the graph checks the pinned words after a replay) and the capacity gets head room
+        defer_count = True
+        capacity = max(capacity, 2 * hint + 4096)
     stream = _abi.current_stream_ptr()
     # short tile lists (cloth-sized scenes) are binned per tile (count / scan / fill / per-tile sort: flags bit2) instead
     # of going through the two global radix sorts; the library refuses when a tile list is too long and the global
@@ -173,7 +209,8 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
     n_tiles = V * ((W + 15) // 16) * ((H + 15) // 16)
     small = _small_bins.get(key, n_tiles <= (1 << 20) and V * P <= (1 << 19)) and P > 0
     while True:
-        host_word.fill_(-1)
+        if not capturing:
+            host_word.fill_(-1)
         nbytes = lib.csb_rasterize_binning_bytes(V, P, W, H, capacity)
         # canonical capacity of a buffer of that size: the backward pass recovers it from numel()
         capacity = lib.csb_rasterize_binning_capacity(V, P, W, H, nbytes)
@@ -187,8 +224,10 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
         _abi.check(rc, "csb_rasterize_forward")
         if defer_count:
             del keep
-            return (PendingCount(host_word, torch.cuda.current_stream(), capacity, key, small, n_tiles), out_color,
-                    out_depth, radii, geom, binning, img)
+            pending = PendingCount(host_word, torch.cuda.current_stream(), capacity, key, small, n_tiles)
+            if capturing:
+                _captured_forwards.append(pending)
+            return (pending, out_color, out_depth, radii, geom, binning, img)
         # no stream synchronisation: the instance count is polled from pinned memory as soon as the binning
         # kernel knows it (the reference blocks on a cudaMemcpy in the middle, rasterizer_impl.cu:282)
         rendered = _await_count(host_word, torch.cuda.current_stream())

@@ -45,8 +45,12 @@ def project_to_pixels(cam, points):
 
 
 def render(viewpoint_camera, pc, simulator, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None,
-           log_deform_path=None, no_shadow=False, render_static=False, project_vertices=False) -> RenderResults:
-    """Render one view of the mesh-anchored Gaussians at viewpoint_camera.time.  bg_color must be on the GPU."""
+           log_deform_path=None, no_shadow=False, render_static=False, project_vertices=False,
+           project_gaussians=True) -> RenderResults:
+    """Render one view of the mesh-anchored Gaussians at viewpoint_camera.time.  bg_color must be on the GPU.
+    Extensions for callers that replay the step as a CUDA graph (train_utils.train_step): a camera may carry `time_tensor`
+    (a [1, 1] device tensor holding its time: the value then is an input of the graph, not a constant baked into it), and
+    `project_gaussians=False` skips the pixel projections the refinement loop never reads (`projections` is then None)."""
     if getattr(pipe, "compute_cov3D_python", False):
         raise NotImplementedError("compute_cov3D_python is outside the accelerated path (SURVEY.md section 8)")
     dev = pc.mesh.pos.device
@@ -69,8 +73,14 @@ def render(viewpoint_camera, pc, simulator, pipe, bg_color: torch.Tensor, scalin
         means3D_deform = base_xyz
         rotations_deform = pc.get_rotation()
     else:
-        time = torch.full((pc.mesh.pos.shape[0], 1), float(viewpoint_camera.time), device=dev)  # no host-to-device copy
-        vertice_deform = simulator(time_vector=time)
+        time = getattr(viewpoint_camera, "time_tensor", None)
+        if time is None:
+            time = torch.full((pc.mesh.pos.shape[0], 1), float(viewpoint_camera.time), device=dev)  # no host-to-device copy
+        if hasattr(simulator, "check_time"):
+            simulator.check_time(viewpoint_camera.time)  # on the host: no synchronisation inside the step
+            vertice_deform = simulator(time_vector=time, checked=True)
+        else:
+            vertice_deform = simulator(time_vector=time)
         means3D_deform = pc.get_xyz(vertice_deform)
         rotations_deform = pc.get_rotation(vertice_deform)
     opacity = pc.get_opacity
@@ -85,6 +95,7 @@ def render(viewpoint_camera, pc, simulator, pipe, bg_color: torch.Tensor, scalin
     return RenderResults(
         render=rendered_image, viewspace_points=screenspace_points, visibility_filter=radii > 0, radii=radii,
         depth=depth, means3D_deform=means3D_deform, vertice_deform=vertice_deform, shadows_mean=None, shadows_std=None,
-        projections=project_to_pixels(viewpoint_camera, means3D_deform), rotations=rotations_deform,
+        projections=project_to_pixels(viewpoint_camera, means3D_deform) if project_gaussians else None,
+        rotations=rotations_deform,
         opacities=opacity, shadows=None,
         vertice_projections=project_to_pixels(viewpoint_camera, vertice_deform) if project_vertices else None)

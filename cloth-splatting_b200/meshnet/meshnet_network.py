@@ -51,13 +51,23 @@ class ResidualMeshSimulator(nn.Module):
         nn.init.normal_(self.output.weight, 0.0, 0.00001)
         nn.init.constant_(self.output.bias, 0.0)
 
-    def forward(self, time_vector):
+    def check_time(self, time: float):
+        """The reference's bounds check (meshnet_network.py:367-369) from a host-side time: callers that know the time as a
+        Python number (render() does: viewpoint_camera.time) check here and pass `checked=True` to forward(), which then
+        needs no device-to-host synchronisation."""
+        if round(float(time) / self.time_delta) >= self.n_times:
+            raise ValueError(f"Time {time} is out of bounds for the mesh simulator.")
+
+    def forward(self, time_vector, checked=False):
         time = time_vector[0, :]
         h = torch.relu(self.input(self.encoder(time)))
         h = torch.relu(self.hidden(h))
         residual = self.output(h).reshape(-1, 3)
         time_id = torch.round(time / self.time_delta).to(dtype=torch.long)
-        if time_id >= self.n_times:
+        if checked:
+            # the host check used double arithmetic: a last-ulp disagreement must not become an out-of-bounds read
+            time_id = time_id.clamp(max=self.n_times - 1)
+        elif time_id >= self.n_times:  # a device-to-host read, as in the reference
             raise ValueError(f"Time {time} is out of bounds for the mesh simulator.")
         return self.mesh_predictions[time_id].squeeze() + residual
 

@@ -313,6 +313,13 @@ int csb_image_loss_backward(int n_img, int C, int H, int W, const float* img, co
 int csb_adam_step(int n_tensors, float* const* params, float* const* grads, float* const* exp_avg,
                   float* const* exp_avg_sq, const int64_t* numel, const double* lr, double beta1, double beta2,
                   double eps, int step, int zero_grads, void* stream);
+/* The same step with the step count on the device, for capture in a CUDA graph (torch's `capturable=True`): one
+ * extra one-thread launch increments *step_dev (int64) and derives the two bias corrections from it in double into
+ * bias_dev[2]; the step kernel reads them.  No host-side value changes between calls. */
+int csb_adam_step_capturable(int n_tensors, float* const* params, float* const* grads, float* const* exp_avg,
+                             float* const* exp_avg_sq, const int64_t* numel, const double* lr, double beta1,
+                             double beta2, double eps, long long* step_dev, double* bias_dev, int zero_grads,
+                             void* stream);
 
 /* ------------------------------------------------------------------------- *
  * Gradient all-reduce over NVLink peer memory

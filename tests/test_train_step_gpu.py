@@ -107,3 +107,46 @@ def test_densifying_iteration_leaves_a_model_the_next_one_renders():
     w = sim.output.weight.detach().clone()
     train_step(603, cams, pc, sim, mesh_opt, PIPE, opt, 5.0, bg, static=True, user_args=ARGS)
     assert torch.equal(sim.output.weight.detach(), w)
+
+
+@pytest.mark.gpu
+def test_graph_replay_equals_the_eager_iterations():
+    """Seven schedule-free iterations through the captured CUDA graph (two eager warm-up frames, the capture, replays with
+    new cameras / times / ground truth every frame) against the same seven iterations run op by op
+    (opt.cuda_graph = False): same losses, same parameters, same statistics, same Adam step counts -- up to the order of
+    the rasterizer's float atomics."""
+    from scene_reconstruction.train_utils import drop_step_graph, train_step
+
+    def run(graph):
+        torch.manual_seed(0)  # the simulator's nn.Linear layers draw from the global generator
+        pc, sim, mesh_opt, cams, opt, bg = scene()
+        opt.cuda_graph = graph
+        losses = []
+        for it in range(1, 8):
+            order = cams[it % 3:] + cams[:it % 3]        # the views of a frame change from iteration to iteration
+            for j, c in enumerate(order):
+                c.time = ((it + j) % 3) / 2
+            ps, loss, d = train_step(it, order, pc, sim, mesh_opt, PIPE, opt, 5.0, bg, user_args=ARGS)
+            assert isinstance(d["l1"], float) and isinstance(d["ssim_loss"], float)
+            losses.append((float(loss), float(ps), d["l1"]))
+        captured = pc.__dict__.get("_csb_step_graph") is not None and pc.__dict__["_csb_step_graph"].graph_a is not None
+        drop_step_graph(pc)
+        steps = {int(pc.optimizer.state[g["params"][0]]["step"]) for g in pc.optimizer.param_groups
+                 if "step" in pc.optimizer.state.get(g["params"][0], {})}  # f_rest: SH degree 0 is active, no gradient
+        return pc, sim, losses, captured, steps
+
+    pc_g, sim_g, loss_g, captured, steps_g = run(True)
+    pc_e, sim_e, loss_e, not_captured, steps_e = run(False)
+    assert captured and not not_captured
+    assert steps_g == steps_e == {7}
+    rel = [[abs(x - y) / max(abs(y), 1e-6) for x, y in zip(a, b)] for a, b in zip(loss_g, loss_e)]
+    assert max(rel[0]) <= 1e-5, rel      # first frame: same state, same inputs
+    assert max(max(r) for r in rel) <= 5e-3, rel   # later frames: Adam amplifies the float-atomic noise of the gradients
+    for n in ("face_bary", "f_dc", "opacity", "scaling", "rotation"):
+        a, b = getattr(pc_g, pc_g._GROUP_ATTR[n]).detach(), getattr(pc_e, pc_e._GROUP_ATTR[n]).detach()
+        lr = [g["lr"] for g in pc_e.optimizer.param_groups if g["name"] == n][0]
+        assert float((a - b).abs().max()) <= 0.5 * lr, n    # Adam normalises: a flipped sign of a ~0 gradient moves a value by <= lr
+        assert float((a - b).abs().mean()) <= 0.02 * lr, n
+    assert float((sim_g.output.weight - sim_e.output.weight).abs().max()) <= 1e-4
+    assert torch.equal(pc_g.denom, pc_e.denom) and torch.equal(pc_g.max_radii2D, pc_e.max_radii2D)
+    assert float((pc_g.pos_gradient_accum - pc_e.pos_gradient_accum).abs().max()) <= 1e-3 * float(pc_e.pos_gradient_accum.abs().max())
