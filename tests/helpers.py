@@ -115,3 +115,17 @@ def product_state(name, dtype, shape, V, P, W, H, fwd):
                            ctypes.c_size_t(n * out.element_size()), ctypes.c_int(3))
         assert rc == 0, rc
     return out
+
+
+def same_as_golden(a, g, rtol=4e-6, atol=1e-7):
+    """Comparison with a golden the reference's own function produced on the build container's host: integers, booleans and
+    indices bit for bit; floating point to a few ulp, because torch's CPU kernels (exp / log / rsqrt, LAPACK) round the last
+    bit differently on hosts with different vector units (the goldens were written on an AVX-512 machine)."""
+    import numpy as np
+
+    a, g = np.asarray(a), np.asarray(g)
+    if a.shape != g.shape:
+        return False
+    if a.dtype.kind in "fc" or g.dtype.kind in "fc":
+        return bool(np.allclose(a, g, rtol=rtol, atol=atol, equal_nan=True))
+    return bool(np.array_equal(a, g))

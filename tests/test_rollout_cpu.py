@@ -3,6 +3,7 @@ of train_meshnet_sim.py) with the same toy simulator, and through to the mesh pr
 import os
 
 import numpy as np
+from helpers import same_as_golden
 import pytest
 import torch
 
@@ -19,7 +20,7 @@ def test_rollout_matches_the_reference_function(tag, real_world):
     keep = {k: v.clone() for k, v in f.items() if isinstance(v, torch.Tensor)}
     r = rollout(fake_scene.ToySimulator(), f, 4, torch.device("cpu"), 2, 0.01, real_world=real_world)
     for k in ("predicted_rollout", "ground_truth_rollout", "mean_loss"):
-        assert np.array_equal(np.asarray(r[k]), G[f"{tag}/{k}"]), k
+        assert same_as_golden(np.asarray(r[k]), G[f"{tag}/{k}"]), k
     assert all(torch.equal(f[k], v) for k, v in keep.items())               # the trajectory is left as it was
     assert np.array_equal(r["initial_pos"], keep["pos"][0].numpy()) and r["predicted_rollout"].shape == (4, 16, 3)
     assert np.array_equal(r["predicted_rollout"][:, 5], f["actions"][:4].numpy())   # the grasped particle follows the actions

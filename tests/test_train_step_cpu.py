@@ -7,6 +7,7 @@ take different branches of the schedule.  The kernels behind render / image_loss
 import os
 
 import numpy as np
+from helpers import same_as_golden
 import pytest
 
 import fake_scene
@@ -30,7 +31,7 @@ def test_train_step_matches_the_reference_function(train_step, name):
     keys = {k[len(name) + 1:] for k in G.files if k.startswith(name + "/")}
     assert keys == set(out), keys ^ set(out)
     for k, v in out.items():
-        assert np.array_equal(np.asarray(v), G[f"{name}/{k}"]), (name, k)
+        assert same_as_golden(np.asarray(v), G[f"{name}/{k}"], rtol=2e-5, atol=2e-7), (name, k)
 
 
 def test_cases_take_different_branches():
