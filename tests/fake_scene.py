@@ -230,3 +230,73 @@ def trajectories(lengths=(9, 7, 12), N=6, seed=21):
                     "node_type": node_type, "actions": rng.standard_normal((T, 3)).astype(np.float32) * 0.1,
                     "edge_faces": [torch.from_numpy(rng.integers(0, N, (3, 4))) for _ in range(T)], "grasped_particle": k + 1})
     return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# stand-ins for pinning the `render()` glue (tests/make_golden_render.py, tests/test_render_glue_cpu.py)
+# ------------------------------------------------------------------------------------------------------------------
+class StandInRasterizer(torch.nn.Module):
+    """A CPU stand-in with `GaussianRasterizer`'s call signature: a smooth, deterministic function of EVERY argument and of
+    every field of the raster settings, so that a wrong argument, a swapped matrix or a dropped field of the glue changes
+    the image.  It is not a rasterizer (the kernels' parity is tested on the GPU against the reference's CUDA)."""
+
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None):
+        s = self.raster_settings
+        H, W = s.image_height, s.image_width
+        ph = torch.cat([means3D, torch.ones_like(means3D[:, :1])], 1) @ s.projmatrix
+        view = torch.cat([means3D, torch.ones_like(means3D[:, :1])], 1) @ s.viewmatrix
+        ndc = ph[:, :2] / (ph[:, 3:] + 1e-7)
+        pix = ((ndc + 1.0) * torch.tensor([W, H], dtype=ndc.dtype) - 1.0) * 0.5 + means2D[:, :2]
+        sigma = 1.5 + 40.0 * s.scale_modifier * scales.sum(1) + 0.2 * rotations[:, 0] + 0.1 * rotations[:, 1:].sum(1) * s.tanfovx / s.tanfovy
+        ys, xs = torch.meshgrid(torch.arange(H, dtype=ndc.dtype), torch.arange(W, dtype=ndc.dtype), indexing="ij")
+        d2 = (xs[None] - pix[:, 0, None, None]) ** 2 + (ys[None] - pix[:, 1, None, None]) ** 2
+        w = opacities[:, :, None] * torch.exp(-0.5 * d2 / (sigma[:, None, None] ** 2 + 1.0))             # [P, H, W]
+        if colors_precomp is not None:
+            colour = colors_precomp
+        else:
+            n = (s.sh_degree + 1) ** 2
+            direction = torch.nn.functional.normalize(means3D - s.campos[None], dim=1)
+            colour = torch.sigmoid(shs[:, 0, :] + 0.3 * shs[:, 1:n, :].sum(1) * direction)
+        total = w.sum(0)
+        image = (w[:, None] * colour[:, :, None, None]).sum(0) / (1.0 + total) + s.bg[:, None, None] / (1.0 + total)
+        depth = (w * view[:, 2, None, None]).sum(0, keepdim=True)
+        radii = (torch.ceil(3.0 * sigma.detach()) * (view[:, 2].detach() > 0.2)).to(torch.int32)
+        return image, radii, depth
+
+
+def render_scene(seed=4, n_times=3, H=10, W=14):
+    """A 3x3-vertex mesh with 24 CPU Gaussians, its residual simulator and cameras built by the mirror's Camera class."""
+    from oracle import mesh_oracle
+    from scene_reconstruction.cameras import Camera
+
+    m, sim, _, _, bg = build(seed)
+
+    def get_rotation(deformed_vertices=None):
+        if deformed_vertices is None:
+            return torch.nn.functional.normalize(m._rotation)
+        return mesh_oracle.get_rotation(m.mesh.pos, deformed_vertices, m.mesh.face, m.face_ids, m._rotation)
+
+    m.get_rotation = get_rotation
+    m.active_sh_degree = 2
+    g = torch.Generator().manual_seed(seed + 100)
+    if n_times != 3:
+        from meshnet.meshnet_network import ResidualMeshSimulator
+
+        pos = m.mesh.pos
+        sim = ResidualMeshSimulator(torch.stack([pos + 0.02 * k * torch.randn(pos.shape, generator=g) for k in range(n_times)]),
+                                    device="cpu")
+        with torch.no_grad():
+            for p in sim.parameters():
+                p.copy_(torch.randn(p.shape, generator=g) * (1e-3 if p.shape[0] == 27 else 0.2))
+    cams = []
+    for i, t in enumerate((0.0, 0.26, 0.5, 0.74, 1.0, 1.3)):
+        ang = 0.4 * i
+        R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+        cams.append(Camera(colmap_id=i, R=R, T=np.array([-0.4, -0.5, 2.0 + 0.1 * i]), FoVx=0.7, FoVy=0.55,
+                           image=torch.rand((3, H, W), generator=g), gt_alpha_mask=None, image_name=str(i), uid=i,
+                           data_device="cpu", time=t))
+    return m, sim, cams, bg

@@ -13,7 +13,13 @@ COLS = [("us", "gpu__time_duration.sum", 1.0), ("rd MB", "dram__bytes_read.sum",
         ("alu %", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", 1.0),
         ("xu %", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", 1.0),
         ("lsu %", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", 1.0),
+        ("tensor %", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", 1.0),
         ("L2 hit %", "lts__t_sector_hit_rate.pct", 1.0), ("Minst", "smsp__inst_executed.sum", 1e-6)]
+# older reports name the tensor pipe differently: first column found wins
+ALIASES = {"tensor %": ["sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+                        "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active",
+                        "sm__pipe_tensor_op_hmma_cycles_active.avg.pct_of_peak_sustained_active",
+                        "sm__inst_executed_pipe_tensor.avg.pct_of_peak_sustained_active"]}
 
 
 def main(rep, out=None):
@@ -29,6 +35,8 @@ def main(rep, out=None):
         vals = {}
         for label, m, scale in COLS:
             if m not in hdr:
+                m = next((a for a in ALIASES.get(label, []) if a in hdr), None)
+            if m is None or m not in hdr:
                 vals[label] = None
                 continue
             i = hdr.index(m)
