@@ -5,7 +5,8 @@ meshnet/generate_mesh_predictions.py:34-46,94-119 writes them and meshnet/data_u
 The reference builds them with torch_geometric transforms (`FaceToEdge(remove_faces=False)`, `GenerateMeshNormals`,
 `Cartesian(norm=False)`, `Distance(norm=False)`); torch_geometric (2.x) is not in this image, so their published rules are
 restated here in torch -- parity of this file is UNPINNED and tested by properties (tests/test_mesh_data_cpu.py).  h5py is
-absent too: the files are written as `.hdf5` when h5py is importable and as `.npz` with the same dataset names otherwise."""
+absent too: the `.hdf5` container is written and read by utils/hdf5_lite.py (HDF5 file-format structures from the
+specification, checked against a libhdf5-written file), so the files are real HDF5 either way."""
 import os
 
 import numpy as np
@@ -55,31 +56,46 @@ def position_losses(prediction_data):
     return [0] + [float(((truth[i] - pred[i]) ** 2).mean()) for i in range(1, pred.shape[0])]
 
 
-def save_mesh(mesh, path, name="mesh.hdf5"):
-    """generate_mesh_predictions.py:34-38.  Returns the path written (`.npz` instead of `.hdf5` without h5py)."""
-    arrays = {k: getattr(mesh, k).detach().cpu().numpy() for k in mesh.keys() if isinstance(getattr(mesh, k), torch.Tensor)}
+def write_datasets(path, arrays):
+    """`with h5py.File(path, "w") as f: f.create_dataset(key, data=value)` for every item: through h5py when it is
+    importable, else through utils/hdf5_lite (same container format)."""
     try:
         import h5py
     except ImportError:
-        out = os.path.join(path, os.path.splitext(name)[0] + ".npz")
-        np.savez(out, **arrays)
-        return out
-    out = os.path.join(path, name)
-    with h5py.File(out, "w") as f:
+        from utils import hdf5_lite
+
+        return hdf5_lite.write_hdf5(path, arrays)
+    with h5py.File(path, "w") as f:
         for k, v in arrays.items():
             f.create_dataset(k, data=v)
-    return out
+    return path
+
+
+def read_datasets(path, names=None):
+    """{name: array} of an HDF5 file's root datasets (h5py when importable, else utils/hdf5_lite); a legacy `.npz` of an
+    earlier version of this package next to a missing `.hdf5` is still read."""
+    if not os.path.exists(path) and os.path.exists(os.path.splitext(path)[0] + ".npz"):
+        with np.load(os.path.splitext(path)[0] + ".npz") as f:
+            return {k: f[k] for k in (names or f.files)}
+    try:
+        import h5py
+    except ImportError:
+        from utils import hdf5_lite
+
+        return hdf5_lite.read_hdf5(path, names)
+    with h5py.File(path, "r") as f:
+        return {k: f[k][:] for k in (names or f.keys())}
+
+
+def save_mesh(mesh, path, name="mesh.hdf5"):
+    """generate_mesh_predictions.py:34-38.  Returns the path written."""
+    arrays = {k: getattr(mesh, k).detach().cpu().numpy() for k in mesh.keys() if isinstance(getattr(mesh, k), torch.Tensor)}
+    return write_datasets(os.path.join(path, name), arrays)
 
 
 def load_mesh(path, device="cuda"):
     """load_mesh_from_h5py (meshnet/data_utils.py:450-457): Data(pos, norm, face, edge_index) on `device`."""
-    if path.endswith(".npz") or not os.path.exists(path):
-        with np.load(os.path.splitext(path)[0] + ".npz") as f:
-            arrays = {k: f[k] for k in ("pos", "norm", "face", "edge_index")}
-    else:
-        import h5py
-        with h5py.File(path, "r") as f:
-            arrays = {k: f[k][:] for k in ("pos", "norm", "face", "edge_index")}
+    arrays = read_datasets(path, ("pos", "norm", "face", "edge_index"))
     return Data(**{k: torch.tensor(v, device=device) for k, v in arrays.items()})
 
 

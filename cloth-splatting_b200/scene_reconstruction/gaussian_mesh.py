@@ -478,8 +478,8 @@ class MultiGaussianMesh(torch.nn.Module):
     def save_ply(self, path):
         """`<path>/point_cloud.ply` with the reference's columns (gaussian_mesh.py:438-460): positions, zero normals,
         f_dc / f_rest channel-major, opacity, log-scales, quaternion, barycentric coordinates, face offset, face id.
-        The mesh goes to `<path>/mesh.hdf5` (datasets `pos`, `face`; :462-465) when h5py is importable, otherwise to
-        `<path>/mesh.npz` with the same names (h5py is not in this image)."""
+        The mesh goes to `<path>/mesh.hdf5` (:462-465; every dataset load_mesh_from_h5py reads) -- through h5py when it is
+        importable, else through utils/hdf5_lite.py, the same container format."""
         import os
 
         import numpy as np
@@ -504,14 +504,9 @@ class MultiGaussianMesh(torch.nn.Module):
             edge_index = face_to_edge(self.mesh.face, self.mesh.pos.shape[0])
         mesh = {"pos": n(self.mesh.pos), "norm": n(mesh_normals(self.mesh.pos, self.mesh.face)), "face": n(self.mesh.face),
                 "edge_index": n(edge_index)}
-        try:
-            import h5py
+        from meshnet.mesh_data import write_datasets
 
-            with h5py.File(os.path.join(path, "mesh.hdf5"), "w") as f:
-                for k, v in mesh.items():
-                    f.create_dataset(k, data=v)
-        except ImportError:
-            np.savez(os.path.join(path, "mesh.npz"), **mesh)
+        write_datasets(os.path.join(path, "mesh.hdf5"), mesh)
 
     @classmethod
     def load_ply(cls, path, sh_degree=3, device="cuda"):
@@ -524,13 +519,9 @@ class MultiGaussianMesh(torch.nn.Module):
         from . import ply_io
 
         col = ply_io.read_vertex_ply(os.path.join(path, "point_cloud.ply"))
-        if os.path.exists(os.path.join(path, "mesh.hdf5")):
-            import h5py
+        from meshnet.mesh_data import read_datasets
 
-            with h5py.File(os.path.join(path, "mesh.hdf5"), "r") as f:
-                mesh = {k: np.asarray(f[k]) for k in f.keys()}
-        else:
-            mesh = dict(np.load(os.path.join(path, "mesh.npz")))
+        mesh = read_datasets(os.path.join(path, "mesh.hdf5"))
         T = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a), dtype=dt, device=device)  # noqa: E731
 
         def stack(prefix):

@@ -49,7 +49,7 @@ def test_prediction_files_round_trip(tmp_path):
     pos = predicted_positions(verts.astype(np.float32), roll)
     assert pos.shape == (5, verts.shape[0], 3) and np.allclose(pos[3], verts + roll[:3].sum(0), atol=1e-6)
     paths = write_mesh_predictions(str(tmp_path), verts.astype(np.float32), roll, faces.T)
-    assert len(paths) == 6 and paths[1].endswith(("mesh_000.npz", "mesh_000.hdf5")) and "mesh_predictions" in paths[-1]
+    assert len(paths) == 6 and paths[1].endswith("mesh_000.hdf5") and paths[0].endswith("init_mesh.hdf5") and "mesh_predictions" in paths[-1]
     first, start, last = (load_mesh(p, device="cpu") for p in (paths[0], paths[1], paths[-1]))
     assert torch.equal(first.pos, start.pos) and np.array_equal(last.pos.numpy(), pos[4])
     assert np.array_equal(last.edge_index.numpy(), ei) and np.array_equal(last.face.numpy(), faces.T)
