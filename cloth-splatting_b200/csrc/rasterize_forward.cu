@@ -805,6 +805,14 @@ static int launch_render_forward(cudaStream_t stream, dim3 tgrid, const ViewBatc
             CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, tgrid, dim3(CSB_TILE_PIX), 0, stream, vb, ranges, point_list, means2D,
                                                             conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
             break;
+        case 3:
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_packed_kernel<1>, tgrid, dim3(LaneTiling<1>::THREADS), 0, stream, vb, ranges, point_list,
+                                                            means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
+            break;
+        case 4:
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_packed_kernel<2>, tgrid, dim3(LaneTiling<2>::THREADS), 0, stream, vb, ranges, point_list,
+                                                            means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
+            break;
         case 2:
             CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_lanes_kernel<2>, tgrid, dim3(LaneTiling<2>::THREADS), 0, stream, vb, ranges, point_list,
                                                             means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
