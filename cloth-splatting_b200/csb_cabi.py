@@ -100,6 +100,8 @@ _OPTIONAL = [
     ("csb_peer_import", c_int, [c_char_p, POINTER(c_void_p)]),
     ("csb_peer_close", c_int, [c_void_p]),
     ("csb_peer_all_reduce", c_int, [c_int, c_int, POINTER(c_void_p), c_size_t, ctypes.c_uint, c_void_p]),
+    ("csb_peer_set_timeout", c_int, [ctypes.c_double]),
+    ("csb_peer_timed_out", c_int, [c_void_p, POINTER(ctypes.c_uint)]),
 ]
 
 _lib = None

@@ -95,6 +95,8 @@ class PeerBuffer:
                 raise PeerUnavailable(f"peer buffer: a rank could not map its peers ({err})")
             self._blob = _CudaBlob(self.base + self.header, self.padded)
             self.flat = torch.as_tensor(self._blob, device=self.device)[: self.numel]
+            if os.environ.get("CSB_PEER_TIMEOUT_S"):  # seconds a rank waits for its peers inside the kernel (default 600)
+                self.check(self.lib.csb_peer_set_timeout(float(os.environ["CSB_PEER_TIMEOUT_S"])), "csb_peer_set_timeout")
 
     def _abandon(self):
         for p in self.opened:
@@ -112,10 +114,21 @@ class PeerBuffer:
                                                 csb_cabi.current_stream_ptr()), "csb_peer_all_reduce")
         return self.flat
 
+    def check_timeout(self):
+        """Raises if a call of all_reduce() gave up waiting for a peer (the kernel then left the bucket unsummed).
+        Synchronises the device; stats() calls it, training loops may call it where they synchronise anyway."""
+        seq = ctypes.c_uint(0)
+        with torch.cuda.device(self.device):
+            self.check(self.lib.csb_peer_timed_out(self.base, ctypes.byref(seq)), "csb_peer_timed_out")
+        if seq.value:
+            raise RuntimeError(f"peer all-reduce: call {seq.value} on rank {self.rank} timed out waiting for a peer "
+                               "(CSB_PEER_TIMEOUT_S); the gradient bucket was not summed")
+
     def stats(self, reset=False):
         """Mean device-side ns per call of the three phases (waiting for the peers to arrive = rank skew, reduce +
         push, fence + departure barrier), as the kernel timed itself with %globaltimer."""
         torch.cuda.synchronize(self.device)
+        self.check_timeout()
         words = torch.as_tensor(_CudaBlob(self.base, self.header // 4), device=self.device)
         q = words[64:76].view(torch.int64)
         t_arrive, t_reduce, t_depart, calls, t_fence, t_count = (int(v) for v in q.cpu())

@@ -13,6 +13,7 @@
 //               that when the kernel retires on this rank all slices have landed here and nobody still reads it.
 // Payloads are small (2.4 MB of Gaussian gradients at C2, 9.3 MB of GNN parameters at C5): the cost is three
 // NVLink round trips, not bandwidth -- which is why a latency-optimised single kernel beats a ring.
+#include <stddef.h>
 #include <string.h>
 #include "common.cuh"
 
@@ -26,7 +27,8 @@ struct Header {
     uint32_t arrive[16];   // [src rank] written by src at the start of call `seq`
     uint32_t done[16];     // [src rank] written by src when its slice has been pushed everywhere
     uint32_t blocks_done;  // local grid counter
-    uint32_t pad[31];
+    uint32_t timed_out;    // sequence number of a call in which a peer never showed up (0 = none): csb_peer_timed_out
+    uint32_t pad[30];
     // [64] self-timing of the calls so far (ns, %globaltimer; block 0 / the last block): waiting for the peers to
     // arrive (rank skew), reducing + pushing, fence + waiting for the peers' done flags; number of calls
     unsigned long long t_arrive, t_reduce, t_depart, calls, t_fence, t_count;
@@ -43,7 +45,9 @@ struct Args {
     int world, rank;
     uint32_t seq;
     unsigned long long n4;  // float4s of payload
+    unsigned long long timeout_ns;  // 0 = wait for ever
 };
+unsigned long long g_timeout_ns = 600ull * 1000000000ull;
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -58,13 +62,19 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 // (.relaxed.sys stores went out as single 16-byte packets: the push phase then ran at ~120 GB/s.)
 __device__ __forceinline__ float4 ld_peer(const float4* p) { return __ldcg(p); }
 __device__ __forceinline__ void st_peer(float4* p, float4 v) { __stcg(p, v); }
-// spins until the flag has reached seq (flags only grow; compared modulo 2^32); traps instead of hanging the GPU
-__device__ __forceinline__ void wait_flag(const uint32_t* p, uint32_t seq) {
-    const long long t0 = clock64();
+// Spins until the flag has reached seq (flags only grow; compared modulo 2^32).  A peer that does not show up within
+// `timeout_ns` of wall-clock time (%globaltimer; default 10 minutes, csb_peer_set_timeout -- rank skew from a first-use
+// build, a checkpoint or a re-render on one rank is legitimate and can be long) makes the wait give up: the caller
+// records the call in the header and leaves the kernel without touching the payload.  No __trap(): the context, the
+// peers' IPC mappings and the other streams survive, and the host raises from PeerBuffer.check_timeout().
+__device__ __forceinline__ bool wait_flag(const uint32_t* p, uint32_t seq, unsigned long long timeout_ns) {
+    const unsigned long long t0 = now_ns();
+    uint32_t spins = 0;
     while ((int)(ld_acquire_sys(p) - seq) < 0) {
-        if (clock64() - t0 > 20000000000ll) __trap();  // ~10 s: a peer never arrived
+        if ((++spins & 1023u) == 0 && timeout_ns && now_ns() - t0 > timeout_ns) return false;
         __nanosleep(20);
     }
+    return true;
 }
 
 template <int W>
@@ -77,8 +87,12 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_all_reduce_kernel(const __g
     if (blockIdx.x == 0 && tid < W) {
         st_release_sys(&reinterpret_cast<Header*>(a.buf[tid])->arrive[a.rank], a.seq);
     }
-    if (tid < W) wait_flag(&mine->arrive[tid], a.seq);
-    __syncthreads();
+    bool ok = true;
+    if (tid < W) ok = wait_flag(&mine->arrive[tid], a.seq, a.timeout_ns);
+    if (__syncthreads_or(!ok)) {  // a peer never arrived: every block of the grid finds out by itself and leaves
+        if (tid == 0) mine->timed_out = a.seq;
+        return;
+    }
     const unsigned long long t1 = now_ns();
 
     // 1. reduce slice `rank`, push the sums to every bucket
@@ -118,7 +132,7 @@ __global__ void __launch_bounds__(PEER_THREADS) peer_all_reduce_kernel(const __g
     const unsigned long long t3 = now_ns();
     if (tid < W) {
         st_release_sys(&reinterpret_cast<Header*>(a.buf[tid])->done[a.rank], a.seq);
-        wait_flag(&mine->done[tid], a.seq);
+        if (!wait_flag(&mine->done[tid], a.seq, a.timeout_ns)) mine->timed_out = a.seq;
     }
     __syncwarp();
     if (tid == 0) {  // the last block's view of the call (its own phases; it is also the one that waits at the end)
@@ -182,6 +196,19 @@ int csb_peer_close(void* p) {
     return 0;
 }
 
+int csb_peer_set_timeout(double seconds) {
+    if (!(seconds >= 0.0)) return CSB_ERR_BAD_ARG;
+    g_timeout_ns = (unsigned long long)(seconds * 1e9);  // 0 = never give up
+    return 0;
+}
+int csb_peer_timed_out(const void* local_buf, unsigned* seq_out) {
+    if (!local_buf || !seq_out) return CSB_ERR_BAD_ARG;
+    uint32_t v = 0;
+    CSB_CUDA_TRY(cudaMemcpy(&v, (const char*)local_buf + offsetof(Header, timed_out), 4, cudaMemcpyDeviceToHost));
+    *seq_out = v;
+    return 0;
+}
+
 int csb_peer_all_reduce(int world, int rank, void* const* bufs, size_t n_floats, unsigned seq, void* stream_) {
     if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world || !bufs) return CSB_ERR_BAD_ARG;
     if (n_floats % 4 != 0) return CSB_ERR_BAD_ARG;
@@ -195,6 +222,7 @@ int csb_peer_all_reduce(int world, int rank, void* const* bufs, size_t n_floats,
     a.rank = rank;
     a.seq = seq;
     a.n4 = n_floats / 4;
+    a.timeout_ns = g_timeout_ns;
     const unsigned long long slice = (a.n4 + world - 1) / world;
     unsigned long long blocks = (slice + PEER_THREADS - 1) / PEER_THREADS;
     if (blocks < 1) blocks = 1;

@@ -334,7 +334,11 @@ int csb_adam_step_capturable(int n_tensors, float* const* params, float* const* 
  * csb_peer_all_reduce enqueues ONE kernel on `stream`: bufs[r] = rank r's buffer as mapped in this process
  * (bufs[rank] = the own allocation), n_floats (a multiple of 4) payload floats, seq = 1, 2, 3, ... incremented by
  * the caller on every call (the same value on all ranks).  In place; the sum is formed in rank order on every
- * element, so all ranks hold bit-identical results.  world <= 8.  Returns 0 or a CSB_ERR_* / cudaError_t code. */
+ * element, so all ranks hold bit-identical results.  world <= 8.  Returns 0 or a CSB_ERR_* / cudaError_t code.
+ * A peer that does not reach the call within the timeout (csb_peer_set_timeout, seconds of wall-clock time measured on
+ * the device; default 600, 0 = wait for ever) makes the kernel leave without touching the payload and record the call's
+ * seq in the buffer's header: csb_peer_timed_out (synchronous read of that word; 0 = no call has timed out).  The CUDA
+ * context survives -- NCCL's behaviour (an error to handle), not a trap. */
 size_t csb_peer_header_bytes(void);
 int csb_peer_alloc(size_t bytes, void** ptr);
 int csb_peer_free(void* ptr);
@@ -342,6 +346,8 @@ int csb_peer_export(void* ptr, void* handle64);
 int csb_peer_import(const void* handle64, void** ptr);
 int csb_peer_close(void* ptr);
 int csb_peer_all_reduce(int world, int rank, void* const* bufs, size_t n_floats, unsigned seq, void* stream);
+int csb_peer_set_timeout(double seconds);
+int csb_peer_timed_out(const void* local_buf, unsigned* seq_out);
 
 #ifdef __cplusplus
 }

@@ -66,3 +66,40 @@ def test_peer_all_reduce_two_ranks(tmp_path):
     out = str(tmp_path / "ok.pt")
     mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
     assert torch.load(out) == [True, True]
+
+
+def _timeout_worker(rank, world, port, out):
+    sys.path.insert(0, conftest.PKG)
+    import csb_dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    os.environ["CSB_PEER_TIMEOUT_S"] = "0.3"
+    dev = torch.device("cuda", rank % torch.cuda.device_count())
+    torch.cuda.set_device(dev)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    buf = csb_dist.PeerBuffer(4096, dev)
+    ok = True
+    if rank == 0:  # rank 1 never enters the call: the kernel gives up after 0.3 s instead of trapping
+        buf.flat.fill_(1.0)
+        buf.all_reduce()
+        try:
+            buf.check_timeout()
+            ok = False
+        except RuntimeError as ex:
+            ok &= "timed out" in str(ex)
+        ok &= float(buf.flat.sum()) == 4096.0                      # the bucket was left alone
+        ok &= float((torch.ones(8, device=dev) * 2).sum()) == 16.0  # and the context is alive
+    res = [None] * world
+    dist.all_gather_object(res, ok)
+    if rank == 0:
+        torch.save(res, out)
+    dist.barrier()
+    buf.close()
+    dist.destroy_process_group()
+
+
+def test_a_missing_peer_is_a_timeout_error_not_a_trap(tmp_path):
+    out = str(tmp_path / "ok.pt")
+    mp.spawn(_timeout_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    assert torch.load(out) == [True, True]
