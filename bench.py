@@ -340,6 +340,8 @@ def gnn_train_bench(dev, impl, peaks, graphs, F=10, iters=5, world=1, rank=0):
         else:
             sim._encode_process_decode = OracleGnn(sim._encode_process_decode)
     sim.train()
+    if world > 1:
+        csb_dist.sync_normalizers(sim)  # the running statistics are those of all ranks' graphs, identical on every rank
     d = c5_batch(graphs, F=F, seed=4 + rank)  # every rank trains on its own shard of the 1024 graphs
     t = {k: torch.from_numpy(v).to(dev) for k, v in d.items()}
     N, E = t["velocity"].shape[0], t["edge_index"].shape[1]

@@ -154,6 +154,17 @@ class PeerBuffer:
         self.base = None
 
 
+def sync_normalizers(module) -> int:
+    """Graph-sharded training: makes every meshnet Normalizer under `module` accumulate the statistics of the whole
+    (all-rank) batch instead of its own shard's (see Normalizer.sync_ranks).  Returns how many were switched."""
+    n = 0
+    for m in module.modules():
+        if hasattr(m, "sync_ranks") and hasattr(m, "_acc_sum"):
+            m.sync_ranks = True
+            n += 1
+    return n
+
+
 def peer_capable(device) -> bool:
     """True when the gradient sum can run over peer memory: several ranks, all CUDA devices of this node."""
     return (_world() > 1 and torch.device(device).type == "cuda" and dist.get_backend() == "nccl"

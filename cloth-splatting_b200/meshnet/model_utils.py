@@ -47,6 +47,10 @@ class Normalizer(nn.Module):
         self._num_accumulations = torch.tensor(0, **f32)
         self._acc_sum = torch.zeros((1, size), **f32)
         self._acc_sum_squared = torch.zeros((1, size), **f32)
+        # Data-parallel training (graphs sharded over the ranks, csb_dist.sync_normalizers): every batch's sums are added
+        # over the ranks before they are accumulated, so all replicas normalise with the statistics of the WHOLE batch
+        # and a rank-0 checkpoint carries all of them.  Off by default: a single process behaves like the reference.
+        self.sync_ranks = False
 
     def forward(self, batched_data, accumulate=True):
         if accumulate and self._num_accumulations < self._max_accumulations:
@@ -57,9 +61,20 @@ class Normalizer(nn.Module):
         return normalized_batch_data * self._std_with_epsilon() + self._mean()
 
     def _accumulate(self, batched_data):
-        self._acc_sum += batched_data.sum(dim=0, keepdim=True)
-        self._acc_sum_squared += (batched_data ** 2).sum(dim=0, keepdim=True)
-        self._acc_count += batched_data.shape[0]
+        s1 = batched_data.sum(dim=0, keepdim=True)
+        s2 = (batched_data ** 2).sum(dim=0, keepdim=True)
+        count = batched_data.shape[0]
+        if self.sync_ranks:
+            import torch.distributed as dist
+
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+                packed = torch.cat([s1.flatten(), s2.flatten(), s1.new_tensor([float(count)])])
+                dist.all_reduce(packed)  # 2 * size + 1 floats: plumbing, not a data-path collective
+                n = s1.numel()
+                s1, s2, count = packed[:n].view_as(s1), packed[n:2 * n].view_as(s2), packed[2 * n]
+        self._acc_sum += s1
+        self._acc_sum_squared += s2
+        self._acc_count += count
         self._num_accumulations += 1
 
     def _safe_count(self):
