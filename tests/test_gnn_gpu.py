@@ -125,3 +125,32 @@ def test_ragged_sizes_and_no_edges():
 
 
 
+
+
+def test_graph_cache_by_identity_content_and_caller_supplied_graph():
+    """A PyG-style caller rebuilds `edge_index` every step: equal content must reuse the prepared (dst-sorted) graph
+    instead of sorting again; an edited topology must not; a PreparedGraph may be passed in place of edge_index."""
+    from meshnet.graph_network import PreparedGraph
+
+    x, ei, ef, _, _ = S.gnn_inputs(9, 4)
+    m = _model()
+    xt, eit, eft = torch.from_numpy(x).cuda(), torch.from_numpy(ei).cuda(), torch.from_numpy(ef).cuda()
+    with torch.no_grad():
+        y0 = m(xt, eit, eft)
+        g0 = m._graph
+        y1 = m(xt, eit, eft)                       # same object
+        assert m._graph is g0
+        y2 = m(xt, eit.clone(), eft)               # new tensor, same content
+        assert m._graph is g0
+        y3 = m(xt, PreparedGraph(eit, x.shape[0]), eft)
+        flipped = eit.flip(1).contiguous()         # same edges in another order: a different topology tensor
+        y4 = m(xt, flipped, eft.flip(0).contiguous())
+        assert m._graph is not g0
+        eit2 = eit.clone()
+        m(xt, eit2, eft)
+        g5 = m._graph
+        eit2[0, 0], eit2[1, 0] = eit2[1, 0].clone(), eit2[0, 0].clone()  # in-place edit of the caller's tensor
+        m(xt, eit2, eft)
+        assert m._graph is not g5
+    assert torch.equal(y0, y1) and torch.equal(y0, y2) and torch.equal(y0, y3)
+    assert float((y4 - y0).abs().max()) < DEEP * float(y0.abs().max())
