@@ -34,7 +34,7 @@ cudaEvent_t take_event() {
 }  // namespace
 
 namespace csb {
-int g_render_variant = 0x40;  // forward: one pixel per lane; backward: one pixel pair per lane, delayed reduction (measured best on B200)
+int g_render_variant = 0x4F;  // forward: packed kernels chosen by path (15); backward: one pixel pair per lane, delayed reduction (measured best on B200)
 LaunchScope::LaunchScope(const char* name_, cudaStream_t stream_) : name(name_), stream(stream_), slot(-1) {
     g_launches.fetch_add(1, std::memory_order_relaxed);
     if (g_profile.load(std::memory_order_relaxed)) {
@@ -71,7 +71,7 @@ unsigned long long csb_launch_count(void) { return g_launches.load(); }
 
 int csb_debug_render_variant(int variant) {
     const int old = csb::g_render_variant;
-    if (variant >= 0 && (variant & 15) <= 4 && (variant >> 4) <= 6) csb::g_render_variant = variant;
+    if (variant >= 0 && ((variant & 15) <= 4 || (variant & 15) == 15) && (variant >> 4) <= 6) csb::g_render_variant = variant;
     return old;
 }
 

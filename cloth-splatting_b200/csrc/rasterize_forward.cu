@@ -799,8 +799,13 @@ using namespace csb;
 static int launch_render_forward(cudaStream_t stream, dim3 tgrid, const ViewBatch& vb, const uint2* ranges,
                                  const uint32_t* point_list, const float2* means2D, const float4* conic_opacity,
                                  const float4* rgb_depth, float* final_T, uint32_t* n_contrib, float* out_color,
-                                 float* out_depth) {
-    switch (g_render_variant & 15) {
+                                 float* out_depth, bool long_lists) {
+    // 15 = by path (measured on B200, profiles/r2_summary.md): cloth-sized scenes on the per-tile binning path (small
+    // footprints, ~30 entries per tile) run fastest with one pixel pair per lane (8x8 pixels per warp: finer culling), the
+    // global sort path (C3 / C4: footprints of many tiles, thousands of entries per tile) with two pairs per lane
+    int fv = g_render_variant & 15;
+    if (fv == 15) fv = long_lists ? 4 : 3;
+    switch (fv) {
         case 0:
             CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_kernel, tgrid, dim3(CSB_TILE_PIX), 0, stream, vb, ranges, point_list, means2D,
                                                             conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
@@ -905,7 +910,7 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             CSB_LAUNCH("bin_sort", stream, launch_pdl(bin_sort_kernel, dim3(sblocks), dim3(256), 0, stream, im.ranges, (const uint32_t*)g.control,
                                                        (uint32_t)total_tiles, (const uint32_t*)fill_d, (const uint32_t*)fill_v, st, sv,
                                                        (flags & 1) ? b.keys : nullptr));
-            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth);
+            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, false);
             if (rc) return rc;
             if (num_rendered_host && !early_count)
                 CSB_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost,
@@ -941,13 +946,13 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             CSB_LAUNCH("tile_ranges", stream, launch_pdl(tile_ranges_kernel, dim3(rblocks), dim3(256), 0, stream, g.control + CTRL_NUM_RENDERED, st, sv, g.rgb_depth,
                                                             im.ranges, (flags & 1) ? b.keys : nullptr,
                                                             (uint32_t)vb.tiles));
-            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth);
+            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, true);
             if (rc) return rc;
             if (tside != sorted_side(total_tiles)) return CSB_ERR_UNSUPPORTED;  // consumers recompute the side
         }
     } else {
         CSB_CUDA_TRY(cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream));
-        rc = launch_render_forward(stream, tgrid, vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth);
+        rc = launch_render_forward(stream, tgrid, vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, true);
         if (rc) return rc;
     }
     if (num_rendered_host && !early_count)
