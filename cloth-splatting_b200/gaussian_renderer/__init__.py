@@ -2,8 +2,8 @@
 KTH-RPL/cloth-splatting) over the sm_100a kernels:
 
     vertices  = simulator(time)                       ResidualMeshSimulator (mesh prediction + residual MLP)
-    means3D   = pc.get_xyz(vertices)                  csb_mesh_xyz_*
-    rotations = pc.get_rotation(vertices)             csb_mesh_rotation_*   (closed-form Kabsch, no SVD)
+    means3D, rotations = pc.get_xyz_rotation(vertices)   csb_mesh_transform_*  (get_xyz + get_rotation fused: barycentric
+                                                          placement, closed-form Kabsch of the face, quaternion compose)
     image, radii, depth = GaussianRasterizer(...)     csb_rasterize_*
 
 Same signature and the same 14-field RenderResults.  The `shadow_scalars` branch of the reference is dead code
@@ -81,8 +81,11 @@ def render(viewpoint_camera, pc, simulator, pipe, bg_color: torch.Tensor, scalin
             vertice_deform = simulator(time_vector=time, checked=True)
         else:
             vertice_deform = simulator(time_vector=time)
-        means3D_deform = pc.get_xyz(vertice_deform)
-        rotations_deform = pc.get_rotation(vertice_deform)
+        if callable(getattr(pc, "get_xyz_rotation", None)):  # one fused launch (csb_mesh_transform_*), same arithmetic
+            means3D_deform, rotations_deform = pc.get_xyz_rotation(vertice_deform)
+        else:
+            means3D_deform = pc.get_xyz(vertice_deform)
+            rotations_deform = pc.get_rotation(vertice_deform)
     opacity = pc.get_opacity
     if log_deform_path is not None:
         np.savez(log_deform_path, means3D=base_xyz.detach().cpu().numpy(),

@@ -26,6 +26,12 @@ def _bind(lib):
     lib.csb_mesh_rotation_forward.argtypes = [c_int, c_int, c_int] + [c_void_p] * 7
     lib.csb_mesh_rotation_backward.restype = c_int
     lib.csb_mesh_rotation_backward.argtypes = [c_int, c_int, c_int] + [c_void_p] * 9
+    lib.csb_mesh_transform_workspace_bytes.restype = ctypes.c_size_t
+    lib.csb_mesh_transform_workspace_bytes.argtypes = [c_int, c_int]
+    lib.csb_mesh_transform_forward.restype = c_int
+    lib.csb_mesh_transform_forward.argtypes = [c_int] * 4 + [c_void_p] * 10
+    lib.csb_mesh_transform_backward.restype = c_int
+    lib.csb_mesh_transform_backward.argtypes = [c_int] * 4 + [c_void_p] * 13 + [ctypes.c_size_t, c_void_p]
     lib._mesh_bound = True
 
 
@@ -103,6 +109,72 @@ class _MeshRotation(torch.autograd.Function):
                                                 _abi.ptr(dq) if dq is not None else None, _abi.current_stream_ptr())
         _abi.check(rc, "csb_mesh_rotation_backward")
         return None, dv, None, None, dq
+
+
+class _MeshTransform(torch.autograd.Function):
+    """get_xyz AND get_rotation (gaussian_mesh.py:151-188) of `V` deformed meshes in one launch: csb_mesh_transform_*.
+    `vertices` [V,Nv,3]; `residual` None or [V,Nv,3] (the deformed mesh is their sum, formed inside the kernel)."""
+
+    @staticmethod
+    def forward(ctx, rest_vertices, vertices, residual, face, face_ids, face_bary, rotation):
+        lib = _abi.lib()
+        _bind(lib)
+        if not vertices.is_cuda:
+            raise ValueError("the mesh transform (B200) needs CUDA tensors; there is no CPU path")
+        v0 = rest_vertices.detach().float().contiguous()
+        v = vertices.detach().float().contiguous()
+        r = None if residual is None else residual.detach().float().contiguous()
+        b = face_bary.detach().float().contiguous()
+        q = rotation.detach().float().contiguous()
+        f = face.to(torch.int64).contiguous()
+        ids = face_ids.to(torch.int64).contiguous()
+        V, Nv, P, F = v.size(0), v.size(1), ids.numel(), f.size(1)
+        xyz = torch.empty((V, P, 3), dtype=torch.float32, device=v.device)
+        rot = torch.empty((V, P, 4), dtype=torch.float32, device=v.device)
+        with torch.cuda.device(v.device):
+            rc = lib.csb_mesh_transform_forward(V, P, Nv, F, _abi.ptr(v0), _abi.ptr(v), _abi.ptr(r) if r is not None else None,
+                                                _abi.ptr(f), _abi.ptr(ids), _abi.ptr(b), _abi.ptr(q), _abi.ptr(xyz),
+                                                _abi.ptr(rot), _abi.current_stream_ptr())
+        _abi.check(rc, "csb_mesh_transform_forward")
+        ctx.save_for_backward(v0, v, f, ids, b, q, *([] if r is None else [r]))
+        return xyz, rot
+
+    @staticmethod
+    def backward(ctx, g_xyz, g_rot):
+        lib = _abi.lib()
+        v0, v, f, ids, b, q, *rest = ctx.saved_tensors
+        r = rest[0] if rest else None
+        V, Nv, P, F = v.size(0), v.size(1), ids.numel(), f.size(1)
+        gx = None if g_xyz is None else g_xyz.float().contiguous()
+        gr = None if g_rot is None else g_rot.float().contiguous()
+        need_v = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        dv = torch.empty_like(v) if need_v else None
+        db = torch.empty_like(b) if ctx.needs_input_grad[5] and gx is not None else None
+        dq = torch.empty_like(q) if ctx.needs_input_grad[6] and gr is not None else None
+        ws = torch.empty(lib.csb_mesh_transform_workspace_bytes(V, F), dtype=torch.uint8, device=v.device)
+        with torch.cuda.device(v.device):
+            rc = lib.csb_mesh_transform_backward(
+                V, P, Nv, F, _abi.ptr(v0), _abi.ptr(v), _abi.ptr(r) if r is not None else None, _abi.ptr(f), _abi.ptr(ids),
+                _abi.ptr(b), _abi.ptr(q), _abi.ptr(gx) if gx is not None else None, _abi.ptr(gr) if gr is not None else None,
+                _abi.ptr(dv) if dv is not None else None, _abi.ptr(db) if db is not None else None,
+                _abi.ptr(dq) if dq is not None else None, _abi.ptr(ws), ws.numel(), _abi.current_stream_ptr())
+        _abi.check(rc, "csb_mesh_transform_backward")
+        if db is None and ctx.needs_input_grad[5]:
+            db = torch.zeros_like(b)
+        if dq is None and ctx.needs_input_grad[6]:
+            dq = torch.zeros_like(q)
+        return (None, dv if ctx.needs_input_grad[1] else None, dv if ctx.needs_input_grad[2] else None, None, None, db, dq)
+
+
+def mesh_transform(rest_vertices, vertices, face, face_ids, face_bary, rotation, residual=None):
+    """(xyz [V,P,3], rotations [V,P,4]) of the Gaussians on `V` deformed meshes `vertices (+ residual)` [V,Nv,3] -- or
+    ([P,3], [P,4]) for a single mesh [Nv,3] -- in one fused launch (csb_mesh_transform_forward)."""
+    single = vertices.dim() == 2
+    if single:
+        vertices = vertices.unsqueeze(0)
+        residual = None if residual is None else residual.unsqueeze(0)
+    xyz, rot = _MeshTransform.apply(rest_vertices, vertices, residual, face, face_ids, face_bary, rotation)
+    return (xyz[0], rot[0]) if single else (xyz, rot)
 
 
 def mesh_rotation(rest_vertices, vertices, face, face_ids, rotation):
@@ -289,6 +361,13 @@ class MultiGaussianMesh(torch.nn.Module):
             assert deformed_vertices.shape[0] == self.mesh.pos.shape[0]
         verts = self.mesh.pos if deformed_vertices is None else deformed_vertices
         return barycentric_xyz(verts, self.mesh.face, self.face_ids, self.face_bary)
+
+    def get_xyz_rotation(self, deformed_vertices, residual=None):
+        """get_xyz(v) and get_rotation(v) together (gaussian_mesh.py:151-188) through the fused transform kernel: one forward
+        launch and two backward launches for any number of deformed meshes ([Nv,3] or [V,Nv,3]; `residual` is added to the
+        vertices inside the kernel).  Same arithmetic as the two accessors."""
+        return mesh_transform(self.mesh.pos, deformed_vertices, self.mesh.face, self.face_ids, self.face_bary,
+                              self._rotation, residual)
 
     # ---- densification / pruning bookkeeping (SURVEY.md 8(f) #3; gaussian_model.py:266-430, gaussian_mesh.py:336-431) ----
     # Host-side tensor surgery on the parameters and on the Adam state (csb_optim.Adam keeps torch's state keys, so

@@ -269,6 +269,26 @@ int csb_mesh_rotation_backward(int P, int Nv, int F, const float* rest_vertices,
                                const int64_t* face, const int64_t* face_ids, const float* rotation,
                                const float* dL_dout, float* dL_dvertices, float* dL_drotation, void* stream);
 
+/* The fused mesh -> Gaussian transform of a refinement step: get_xyz AND get_rotation
+ * (scene_reconstruction/gaussian_mesh.py:151-188) for `num_views` deformed meshes in one forward launch.  The deformed
+ * vertices of view v are vertices[v] + residual[v] (meshnet/meshnet_network.py:361-373: mesh prediction + the residual
+ * simulator's output, consumed in place); residual may be NULL.  vertices / residual f32[V,Nv,3]; rest_vertices
+ * f32[Nv,3]; face i64[3,F]; face_ids i64[P]; face_bary f32[P,3]; rotation f32[P,4] (raw parameter).
+ * Outputs xyz f32[V,P,3], rot f32[V,P,4] (XYZW as the reference composes them); one of them may be NULL.
+ * Backward: dL_dxyz f32[V,P,3] and / or dL_drot f32[V,P,4] in; dL_dvertices f32[V,Nv,3] (zeroed inside; it is the
+ * gradient of `vertices` and of `residual` alike), dL_dface_bary f32[P,3] and dL_drotation f32[P,4] (both summed over the
+ * views in view order); any output may be NULL.  workspace: csb_mesh_transform_workspace_bytes(num_views, F) bytes
+ * (per-face gradients of the relative rotation).  Same arithmetic as csb_mesh_xyz_* / csb_mesh_rotation_*. */
+size_t csb_mesh_transform_workspace_bytes(int num_views, int F);
+int csb_mesh_transform_forward(int num_views, int P, int Nv, int F, const float* rest_vertices, const float* vertices,
+                               const float* residual, const int64_t* face, const int64_t* face_ids,
+                               const float* face_bary, const float* rotation, float* xyz, float* rot, void* stream);
+int csb_mesh_transform_backward(int num_views, int P, int Nv, int F, const float* rest_vertices, const float* vertices,
+                                const float* residual, const int64_t* face, const int64_t* face_ids,
+                                const float* face_bary, const float* rotation, const float* dL_dxyz,
+                                const float* dL_drot, float* dL_dvertices, float* dL_dface_bary, float* dL_drotation,
+                                void* workspace, size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------- *
  * Photometric loss
  * ------------------------------------------------------------------------- */

@@ -42,6 +42,7 @@ def build(seed=3, masks=False):
     from scene_reconstruction.gaussian_mesh import MultiGaussianMesh
 
     class CpuMesh(MultiGaussianMesh):  # get_xyz of the reference in torch (gaussian_mesh.py:151-169): no GPU here
+        get_xyz_rotation = None  # no fused CUDA transform on the CPU: render() then calls the two accessors
         def get_xyz(self, deformed_vertices=None):
             verts = self.mesh.pos if deformed_vertices is None else deformed_vertices
             vid = self.mesh.face[:, self.face_ids].transpose(0, 1)
