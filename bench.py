@@ -555,9 +555,12 @@ def raster_leg(workload, rank, world, dev, steps, warmup, fp32, peaks, with_e2e=
     alg = {  # algorithmic bytes per launch of the HBM-bound stages
         "preprocess": 311.0 * P * Vb,
         "emit": 20.0 * P * Vb + 12.0 * R_launch,
+        "sort_depth": 16.0 * P * Vb,          # per pass: (depth key, entry) pairs of the V x P entries, read + written
+        "sort_tile": 16.0 * R_launch,         # per pass: (tile id, entry) pairs of the instances, read + written
         "sort_onesweep": 16.0 * R_launch,
         "sort_histogram": 4.0 * R_launch,
-        "tile_ranges": 16.0 * R_launch + 8.0 * tiles * Vb,
+        # the split keys make this stage read ONE 4-byte tile id per instance (the reference reads two 8-byte keys: 16 B)
+        "tile_ranges": 4.0 * R_launch + 8.0 * tiles * Vb,
         "bin_ranges": 8.0 * tiles * Vb,
         "bin_fill": 20.0 * P * Vb + 8.0 * R_launch,
         "bin_sort": 16.0 * R_launch,
@@ -685,7 +688,7 @@ def run_b200(args, rank, world, dev):
                           "instances_per_step": c3["R_step"], "pairs_per_step": c3.get("pairs_per_step"),
                           "gpu_launches": c3["launches"], "kernels": c3["kernels"]}
             k3 = c3["kernels"]
-            mine = sum(k3[k]["ms_per_step"] for k in ("sort_onesweep", "sort_histogram", "emit", "tile_ranges") if k in k3)
+            mine = sum(k3[k]["ms_per_step"] for k in ("sort_onesweep", "sort_depth", "sort_tile", "sort_histogram", "emit", "tile_ranges") if k in k3)
             line["sort"] = {"instances": c3["R_step"],
                             "b200_ms": mine,
                             "b200_stages": "depth sort (4 onesweep passes over V*P u32 keys) + emit (scan + duplicate) + "

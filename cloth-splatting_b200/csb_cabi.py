@@ -82,6 +82,8 @@ _OPTIONAL = [
     ("csb_dist_cuda2", c_int, [c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     ("csb_launch_count", ctypes.c_ulonglong, []),
     ("csb_debug_render_variant", c_int, [c_int]),
+    ("csb_debug_gnn_small", c_int, [c_int]),
+    ("csb_debug_gnn_trace", c_int, [c_void_p, c_int]),
     ("csb_measure_fp32_peaks", c_int, [c_void_p, c_size_t, POINTER(ctypes.c_double), POINTER(ctypes.c_double),
                                        POINTER(ctypes.c_double), c_void_p]),
     ("csb_profile_enable", None, [c_int]),

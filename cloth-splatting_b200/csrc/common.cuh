@@ -205,7 +205,7 @@ int fill_view_batch(struct ViewBatch& vb, int num_views, const csb_view* views, 
 int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
                      const uint32_t* n_dev, size_t n_max, int end_bit, uint32_t* hist /*4x256, zeroed*/,
                      uint32_t* tickets /*4, zeroed*/, uint32_t* lookback /*zeroed*/, int* side_out,
-                     cudaStream_t stream, bool hist_ready = false);
+                     cudaStream_t stream, bool hist_ready = false, const char* launch_name = nullptr);
 
 #ifdef __CUDACC__
 // One key per lane -> shared-memory digit histograms of `passes` 8-bit digits (sh[p * 256 + d]).  Neighbouring keys

@@ -20,10 +20,28 @@
 // 0.3).  e_0 is therefore stored once (bf16, in dst-sorted edge order) and the factor 2^m is folded into
 // the edge block of the first edge Linear when the weights are packed (exact in bf16).
 
+#include <type_traits>
+
 #include "gnn_common.cuh"
 
 namespace csb {
 namespace gnn {
+
+// Debugging aid (csb_debug_gnn_trace): thread 0 of ONE chosen CTA stamps %globaltimer at the stations of its tile walk
+// into a device buffer: word 0 = count, then (time_ns << 8 | station).  A null buffer (the default) costs one load per station.
+__device__ unsigned long long* g_trace_buf = nullptr;
+__device__ int g_trace_block = 0;
+__device__ __forceinline__ void trace_pt(int station) {
+    if (threadIdx.x == 0 && (int)blockIdx.x == g_trace_block) {
+        unsigned long long* p = g_trace_buf;
+        if (p) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+            const unsigned long long n = atomicAdd(p, 1ull);
+            if (n < 8000) p[1 + n] = (t << 8) | (unsigned long long)station;
+        }
+    }
+}
 
 // W [128, K] row-major fp32 -> chunks of [128 rows x 64 k] bf16, swizzle-128B K-major
 __device__ void pack_linear(const float* __restrict__ W, int K, int col_scale_from, float scale, uint8_t* dst) {
@@ -111,80 +129,114 @@ static size_t smem_bytes(int mode, int kin, int nout) {
     return b;
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1) gnn_mlp_kernel(const __grid_constant__ Args a) {
+// What a CTA carries from one role / tile walk to the next: the weight barrier's phase (the unit image is bulk-copied once
+// per walk), the MMA barrier's parity.  Identical in all threads.
+struct WalkState {
+    uint32_t w_phase = 0, mma_parity = 0;
+    bool weights_ready = true;
+};
+
+template <int MODE> struct Carve {
     using C = Cfg<MODE>;
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint8_t* sW = smem;                                        // weight chunks
-    uint8_t* sA = sW + (size_t)C::W_CHUNKS * CHUNK_BYTES;     // A operand chunks (also scatter staging)
-    float* sF = reinterpret_cast<float*>(sA + (size_t)C::A_SLOTS * CHUNK_BYTES);  // fp32 parameters
-    const int nf32 = unit_f32(MODE, a.kin, a.nout);
-    float* sRed = sF + ((nf32 + 31) & ~31);                    // SCRATCH_FLOATS
-    int* sDst = reinterpret_cast<int*>(sRed + SCRATCH_FLOATS);  // [128]
-    int* sSrc = sDst + TILE_M;                                 // [128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sSrc + TILE_M);  // [0] weights, [1] mma
-    uint32_t* sTmem = reinterpret_cast<uint32_t*>(bars + 2);
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int row = (warp & 3) * 32 + lane;  // TMEM lane == tile row owned in the epilogues
-    const int half = warp >> 2;              // columns [64*half, 64*half + 64)
-    const uint32_t bar_w = smem_u32(&bars[0]), bar_mma = smem_u32(&bars[1]);
-
-    if (tid == 0) {
-        mbar_init(bar_w, 1);
-        mbar_init(bar_mma, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    uint8_t *sW, *sA;
+    float *sF, *sRed;
+    int *sDst, *sSrc;
+    __device__ Carve(uint8_t* smem, int nf32) {
+        sW = smem;                                               // weight chunks
+        sA = sW + (size_t)C::W_CHUNKS * CHUNK_BYTES;            // A operand chunks (also scatter staging)
+        sF = reinterpret_cast<float*>(sA + (size_t)C::A_SLOTS * CHUNK_BYTES);  // fp32 parameters
+        sRed = sF + ((nf32 + 31) & ~31);                         // SCRATCH_FLOATS
+        sDst = reinterpret_cast<int*>(sRed + SCRATCH_FLOATS);    // [128]
+        sSrc = sDst + TILE_M;                                    // [128]
     }
-    if (warp == 0) tmem_alloc(smem_u32(sTmem), TMEM_COLS);
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *sTmem;
+};
 
-    // resident weights: one bulk copy per 16 KB chunk + the fp32 block
-    if (tid == 0) {
+// Loads that see what OTHER CTAs of the same (persistent) kernel wrote after a grid barrier: L2 only, no L1 line that an
+// earlier phase may have left behind.  Between kernel launches (COH = false) plain loads are coherent.
+template <bool COH> __device__ __forceinline__ uint4 ld_act(const uint4* p) { return COH ? __ldcg(p) : *p; }
+template <bool COH> __device__ __forceinline__ float4 ld_act(const float4* p) { return COH ? __ldcg(p) : *p; }
+
+// the role's resident weights: one bulk copy per 16 KB chunk + the fp32 block (one thread)
+template <int MODE>
+__device__ __forceinline__ void issue_weights(const Args& a, uint8_t* smem, uint32_t bar_w, WalkState& ws) {
+    using C = Cfg<MODE>;
+    const int nf32 = unit_f32(MODE, a.kin, a.nout);
+    Carve<MODE> cv(smem, nf32);
+    if (threadIdx.x == 0) {
         const uint32_t wbytes = (uint32_t)C::W_CHUNKS * CHUNK_BYTES;
         const uint32_t fbytes = (uint32_t)nf32 * 4;
         mbar_expect_tx(bar_w, wbytes + fbytes);
         for (int c = 0; c < C::W_CHUNKS; ++c)
-            bulk_g2s(smem_u32(sW + (size_t)c * CHUNK_BYTES), a.unit + (size_t)c * CHUNK_BYTES, CHUNK_BYTES, bar_w);
-        bulk_g2s(smem_u32(sF), a.unit + wbytes, fbytes, bar_w);
+            bulk_g2s(smem_u32(cv.sW + (size_t)c * CHUNK_BYTES), a.unit + (size_t)c * CHUNK_BYTES, CHUNK_BYTES, bar_w);
+        bulk_g2s(smem_u32(cv.sF), a.unit + wbytes, fbytes, bar_w);
     }
-    // Programmatic dependent launch: everything above (barriers, TMEM, the bulk copy of the constant weight image)
-    // overlaps the tail of the previous kernel of the forward; its activations are only touched below.
-    grid_dep_trigger();
-    grid_dep_wait();
-    bool weights_ready = false;
-    uint32_t mma_parity = 0;
+    ws.weights_ready = false;
+}
+
+// The tile walk of a role: tiles tile0, tile0 + tile_step, ... of a.rows rows.
+// Row indices of an EDGE tile, fetched by threads 0..127 BEFORE the walk waits for its predecessor (the graph is constant:
+// the load's latency hides behind the dependency wait instead of heading the tile's chain).
+struct EdgeRows {
+    int d = -1, s = -1;
+    bool valid = false;
+};
+__device__ __forceinline__ EdgeRows load_edge_rows(const Args& a, int tile) {
+    EdgeRows r;
+    if (threadIdx.x < TILE_M) {
+        const int p = tile * TILE_M + threadIdx.x;
+        if (p < a.rows) {
+            r.d = a.dst_sorted[p];
+            r.s = a.src_sorted[p];
+            if ((unsigned)r.d >= (unsigned)a.N || (unsigned)r.s >= (unsigned)a.N) r.d = r.s = -1;
+        }
+    }
+    r.valid = true;
+    return r;
+}
+
+template <int MODE, bool COH>
+__device__ __forceinline__ void mlp_tiles(const Args& a, uint8_t* smem, const uint32_t tmem, const uint32_t bar_w,
+                                          const uint32_t bar_mma, WalkState& ws, const int tile0, const int tile_step,
+                                          const EdgeRows pre = EdgeRows()) {
+    using C = Cfg<MODE>;
+    const int nf32 = unit_f32(MODE, a.kin, a.nout);
+    Carve<MODE> cv(smem, nf32);
+    uint8_t* sW = cv.sW;
+    uint8_t* sA = cv.sA;
+    float* sF = cv.sF;
+    float* sRed = cv.sRed;
+    int* sDst = cv.sDst;
+    int* sSrc = cv.sSrc;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int warp_u = __shfl_sync(0xFFFFFFFFu, warp, 0);  // the same value, known to be warp-uniform
+    const int row = (warp & 3) * 32 + lane;  // TMEM lane == tile row owned in the epilogues
+    const int half = warp >> 2;              // columns [64*half, 64*half + 64)
+    bool weights_ready = ws.weights_ready;
+    uint32_t mma_parity = ws.mma_parity;
     const uint32_t sA_u32 = smem_u32(sA), sW_u32 = smem_u32(sW);
     const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(half * 64);
 
     const int num_tiles = (a.rows + TILE_M - 1) / TILE_M;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
         const int row0 = tile * TILE_M;
         const int grow = row0 + row;  // global row of this thread's epilogue row
         const bool rvalid = grow < a.rows;
+        if (MODE == EDGE || MODE == NODE) trace_pt(1);
 
         // ------------------------------------------------------------------ stage the first A operand
         if (MODE == EDGE) {
+            const EdgeRows er = (pre.valid && tile == tile0) ? pre : load_edge_rows(a, tile);
             if (tid < TILE_M) {
-                const int p = row0 + tid;
-                int d = -1, s = -1;
-                if (p < a.rows) {
-                    d = a.dst_sorted[p];
-                    s = a.src_sorted[p];
-                    if ((unsigned)d >= (unsigned)a.N || (unsigned)s >= (unsigned)a.N) d = s = -1;
-                }
-                sDst[tid] = d;
-                sSrc[tid] = s;
+                sDst[tid] = er.d;
+                sSrc[tid] = er.s;
             }
             __syncthreads();
         }
         int wchunk = 0;  // next weight chunk to multiply with
         if (MODE == ENC) {
             // first Linear on the CUDA cores (fp32), K = kin
-            if (!weights_ready) { mbar_wait(bar_w, 0); weights_ready = true; }
+            if (!weights_ready) { mbar_wait(bar_w, ws.w_phase); ws.w_phase ^= 1; weights_ready = true; }
             const float* W0 = sF + 5 * LAT;
             const float* b0 = sF;
             float xin[16];
@@ -231,8 +283,8 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
                 xb[it] = make_uint4(0, 0, 0, 0);
                 if (n < a.rows) {
                     const float4* p = reinterpret_cast<const float4*>(a.agg + (size_t)n * LAT + kb * 64 + c * 8);
-                    fa[2 * it] = p[0];
-                    fa[2 * it + 1] = p[1];
+                    fa[2 * it] = ld_act<COH>(p);
+                    fa[2 * it + 1] = ld_act<COH>(p + 1);
                     xb[it] = *reinterpret_cast<const uint4*>(a.x_bf16 + (size_t)n * LAT + kb * 64 + c * 8);
                 }
             }
@@ -256,7 +308,7 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
             }
             // pull the next tile of this CTA towards L2 while this one is multiplied
             {
-                const int nt = tile + gridDim.x;
+                const int nt = tile + tile_step;
                 if (nt < num_tiles) {
                     const int r = tid >> 1, n = nt * TILE_M + r;
                     if (n < a.rows) {
@@ -274,7 +326,7 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
         }
         if (MODE == EDGE) {
             // next tile of this CTA: its rows' x[dst], x[src] and e0 lines towards L2
-            const int nt = tile + gridDim.x;
+            const int nt = tile + tile_step;
             if (nt < num_tiles) {
                 const int r = tid >> 1, p = nt * TILE_M + r;
                 if (p < a.rows) {
@@ -290,6 +342,24 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
         }
 
         // ------------------------------------------------------------------ tensor-core layers
+        uint4 gv[MODE == EDGE ? 12 : 1];
+        auto edge_gather = [&](int ph) {
+            if (MODE != EDGE) return;
+#pragma unroll
+            for (int it = 0; it < (MODE == EDGE ? 12 : 1); ++it) {
+                const int idx = it * THREADS + tid;
+                const int c = idx & 7, r = (idx >> 3) & 127, kb = 3 * ph + (idx >> 10);
+                const int d = sDst[r];
+                gv[it] = make_uint4(0, 0, 0, 0);
+                if (d >= 0) {
+                    const __nv_bfloat16* src;
+                    if (kb < 2) src = a.x_bf16 + (size_t)d * LAT + kb * 64;
+                    else if (kb < 4) src = a.x_bf16 + (size_t)sSrc[r] * LAT + (kb - 2) * 64;
+                    else src = a.e0 + (size_t)(row0 + r) * LAT + (kb - 4) * 64;
+                    gv[it] = ld_act<COH>(reinterpret_cast<const uint4*>(src + c * 8));
+                }
+            }
+        };
 #pragma unroll 1
         for (int layer = 0; layer < C::TC_LAYERS; ++layer) {
             const bool first = layer == 0;
@@ -298,51 +368,52 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
             for (int ph = 0; ph < phases; ++ph) {
                 int nchunks = first ? (MODE == EDGE ? 3 : C::K1_CHUNKS) : 2;
                 if (MODE == EDGE && first) {
-                    // gather 3 K blocks of [x[dst] | x[src] | e0] (blocks 3*ph .. 3*ph+2)
-                    uint4 v[12];
-#pragma unroll
-                    for (int it = 0; it < 12; ++it) {
-                        const int idx = it * THREADS + tid;
-                        const int c = idx & 7, r = (idx >> 3) & 127, kb = 3 * ph + (idx >> 10);
-                        const int d = sDst[r];
-                        v[it] = make_uint4(0, 0, 0, 0);
-                        if (d >= 0) {
-                            const __nv_bfloat16* src;
-                            if (kb < 2) src = a.x_bf16 + (size_t)d * LAT + kb * 64;
-                            else if (kb < 4) src = a.x_bf16 + (size_t)sSrc[r] * LAT + (kb - 2) * 64;
-                            else src = a.e0 + (size_t)(row0 + r) * LAT + (kb - 4) * 64;
-                            v[it] = *reinterpret_cast<const uint4*>(src + c * 8);
-                        }
-                    }
+                    // 3 K blocks of [x[dst] | x[src] | e0] (blocks 3*ph .. 3*ph+2): phase 0 is fetched here, phase 1 was
+                    // fetched into gv[] while phase 0's MMAs ran (below)
+                    if (ph == 0) edge_gather(0);
 #pragma unroll
                     for (int it = 0; it < 12; ++it) {
                         const int idx = it * THREADS + tid;
                         const int c = idx & 7, r = (idx >> 3) & 127, kl = idx >> 10;
-                        *reinterpret_cast<uint4*>(sA + (size_t)kl * CHUNK_BYTES + swz_off(r, c)) = v[it];
+                        *reinterpret_cast<uint4*>(sA + (size_t)kl * CHUNK_BYTES + swz_off(r, c)) = gv[it];
                     }
                 }
                 // the resident unit image (bulk copy) must have landed before anybody touches it
-                if (!weights_ready) { mbar_wait(bar_w, 0); weights_ready = true; }
+                if (!weights_ready) { mbar_wait(bar_w, ws.w_phase); ws.w_phase ^= 1; weights_ready = true; }
                 // generic-proxy writes of the A operand -> visible to the tensor core (async proxy)
                 fence_proxy_async();
                 tc_fence_before();
                 __syncthreads();
-                if (tid == 0) {
-                    tc_fence_after();
-                    for (int s = 0; s < nchunks; ++s) {
+                if (MODE == EDGE || MODE == NODE) trace_pt(2);
+                // One elected lane of warp 0 issues the chain (a warp-uniform branch: the descriptor arithmetic stays in the
+                // uniform datapath instead of being moved there value by value behind a divergent `tid == 0`); the chunk loop
+                // is unrolled to its compile-time maximum.  Measured (csb_debug_gnn_trace): 12 MMAs took 1.06 us to issue.
+                if (warp_u == 0) {
+                    if (elect_one()) {
+                        tc_fence_after();
+                        const uint32_t a0 = sA_u32, b0 = sW_u32 + (uint32_t)wchunk * CHUNK_BYTES;
 #pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const uint64_t ad = umma_desc(sA_u32 + (uint32_t)s * CHUNK_BYTES + k * 32);
-                            const uint64_t bd = umma_desc(sW_u32 + (uint32_t)(wchunk + s) * CHUNK_BYTES + k * 32);
-                            umma(tmem, ad, bd, (ph > 0 || s > 0 || k > 0) ? 1u : 0u);
+                        for (int s = 0; s < C::K1_CHUNKS; ++s) {
+                            if (s < nchunks) {
+#pragma unroll
+                                for (int k = 0; k < 4; ++k) {
+                                    const uint64_t ad = umma_desc(a0 + (uint32_t)s * CHUNK_BYTES + k * 32);
+                                    const uint64_t bd = umma_desc(b0 + (uint32_t)s * CHUNK_BYTES + k * 32);
+                                    umma(tmem, ad, bd, (ph > 0 || s > 0 || k > 0) ? 1u : 0u);
+                                }
+                            }
                         }
+                        umma_commit(bar_mma);
                     }
-                    umma_commit(bar_mma);
+                    __syncwarp();
                 }
                 wchunk += nchunks;
+                if (MODE == EDGE || MODE == NODE) trace_pt(3);
+                if (MODE == EDGE && first && ph == 0) edge_gather(1);  // in flight while phase 0 is multiplied
                 mbar_wait(bar_mma, mma_parity);
                 mma_parity ^= 1;
                 tc_fence_after();
+                if (MODE == EDGE || MODE == NODE) trace_pt(4);
             }
             // ---- epilogue of this layer: TMEM -> registers
             float v[64];
@@ -362,6 +433,7 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
                                           pack_bf16(h[6], h[7]));
                     *reinterpret_cast<uint4*>(sA + (size_t)half * CHUNK_BYTES + swz_off(row, c)) = pk;
                 }
+                if (MODE == EDGE || MODE == NODE) trace_pt(5);
                 continue;
             }
             if (MODE == DEC) {
@@ -403,6 +475,7 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
             const float* lb = sF + 4 * LAT + half * 64;
 #pragma unroll
             for (int j = 0; j < 64; ++j) v[j] = (v[j] - mean) * rstd * lg[j] + lb[j];
+            if (MODE == EDGE || MODE == NODE) trace_pt(6);
 
             if (MODE == ENC) {
                 if (rvalid) {
@@ -428,55 +501,239 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
                         make_float4(v[c * 4], v[c * 4 + 1], v[c * 4 + 2], v[c * 4 + 3]);
                 }
                 __syncthreads();
-#pragma unroll 4
+                // the warp's 16 rows of the fp32 master: every load in flight before the first use (v[] is dead here; one
+                // at a time this loop was 4 x a global-load latency = 4.5 us of a 15 us tile, csb_debug_gnn_trace)
+                float4 xo[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const int n = row0 + warp * 16 + i;
+                    xo[i] = n < a.rows ? *(reinterpret_cast<const float4*>(a.x_f32 + (size_t)n * LAT) + lane)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
                 for (int i = 0; i < 16; ++i) {
                     const int r = warp * 16 + i;
                     const int n = row0 + r;
                     if (n >= a.rows) break;  // warp-uniform
                     const float4 u = *reinterpret_cast<const float4*>(stg + r * LAT + ((lane ^ (r & 7)) * 4));
-                    float4* xf = reinterpret_cast<float4*>(a.x_f32 + (size_t)n * LAT) + lane;
-                    float4 o = *xf;
+                    float4 o = xo[i];
                     o.x += u.x; o.y += u.y; o.z += u.z; o.w += u.w;
-                    *xf = o;
+                    *(reinterpret_cast<float4*>(a.x_f32 + (size_t)n * LAT) + lane) = o;
                     *(reinterpret_cast<uint2*>(a.out_bf16 + (size_t)n * LAT) + lane) =
                         make_uint2(pack_bf16(o.x, o.y), pack_bf16(o.z, o.w));
                 }
             } else if (MODE == EDGE) {
                 // segmented sum over the warp's 32 dst-sorted rows, 32 columns per round, staged in the
                 // (now idle) A region; lane j owns one column and adds once per segment.
+                // The segment structure of the warp's 32 rows is one ballot (bit i: row i is the last of its dst run) and
+                // the walk below is straight-line code: 32 independent shared loads, a running sum, a predicated red.add at
+                // the run ends.  (A data-dependent branch per row made this loop 4.3 us of a 20 us tile: every iteration
+                // waited for its own two shared loads, csb_debug_gnn_trace.)  Same summation order as before.
                 float* st = reinterpret_cast<float*>(sA) + warp * (32 * 33);
                 const int* wd = sDst + (warp & 3) * 32;
+                const int my_d = wd[lane];
+                const int nx_d = lane < 31 ? wd[lane + 1] : -2;
+                const uint32_t ends = __ballot_sync(0xFFFFFFFFu, my_d != nx_d);
 #pragma unroll
                 for (int rd = 0; rd < 2; ++rd) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) st[lane * 33 + j] = v[rd * 32 + j];
                     __syncwarp();
-                    const int col = half * 64 + rd * 32 + lane;
-                    int cur = wd[0];
+                    float* out_col = a.agg + (half * 64 + rd * 32 + lane);
+                    float xv[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) xv[i] = st[i * 33 + lane];
                     float acc = 0.f;
-#pragma unroll 4
+#pragma unroll
                     for (int i = 0; i < 32; ++i) {
-                        const int d = wd[i];
-                        if (d != cur) {
-                            if (cur >= 0) atomicAdd(a.agg + (size_t)cur * LAT + col, acc);
-                            cur = d;
+                        acc += xv[i];
+                        if ((ends >> i) & 1u) {  // warp-uniform
+                            const int d = __shfl_sync(0xFFFFFFFFu, my_d, i);
+                            if (d >= 0) atomicAdd(out_col + (size_t)d * LAT, acc);
                             acc = 0.f;
                         }
-                        acc += st[i * 33 + lane];
                     }
-                    if (cur >= 0) atomicAdd(a.agg + (size_t)cur * LAT + col, acc);
                     __syncwarp();
                 }
             }
             // the next tile overwrites sA / TMEM: order this tile's TMEM reads and staging before it
             tc_fence_before();
             __syncthreads();
+            if (MODE == EDGE || MODE == NODE) trace_pt(7);
         }
     }
-    if (!weights_ready && tid == 0) mbar_wait(bar_w, 0);  // never leave a bulk copy in flight
+    ws.weights_ready = weights_ready;
+    ws.mma_parity = mma_parity;
+}
+
+struct CtaSetup {
+    uint8_t* smem;
+    uint32_t tmem, bar_w, bar_mma;
+};
+// mbarriers + TMEM of a CTA of any role; the control words sit behind the largest role's carve-up
+__device__ __forceinline__ CtaSetup cta_setup(uint8_t* smem_raw, size_t ctrl_offset) {
+    CtaSetup cs;
+    cs.smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(cs.smem + ctrl_offset);  // [0] weights, [1] mma
+    uint32_t* sTmem = reinterpret_cast<uint32_t*>(bars + 2);
+    cs.bar_w = smem_u32(&bars[0]);
+    cs.bar_mma = smem_u32(&bars[1]);
+    if (threadIdx.x == 0) {
+        mbar_init(cs.bar_w, 1);
+        mbar_init(cs.bar_mma, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (threadIdx.x < 32) tmem_alloc(smem_u32(sTmem), TMEM_COLS);
     tc_fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, TMEM_COLS);
+    tc_fence_after();
+    cs.tmem = *sTmem;
+    return cs;
+}
+template <int MODE> __device__ __forceinline__ size_t ctrl_offset_of(int kin, int nout) {
+    const int nf32 = unit_f32(MODE, kin, nout);
+    return (size_t)(Cfg<MODE>::W_CHUNKS + Cfg<MODE>::A_SLOTS) * CHUNK_BYTES + (size_t)((nf32 + 31) & ~31) * 4 +
+           SCRATCH_FLOATS * 4 + 2 * TILE_M * 4;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1) gnn_mlp_kernel(const __grid_constant__ Args a) {
+    extern __shared__ uint8_t smem_raw[];
+    const CtaSetup cs = cta_setup(smem_raw, ctrl_offset_of<MODE>(a.kin, a.nout));
+    WalkState ws;
+    issue_weights<MODE>(a, cs.smem, cs.bar_w, ws);
+    // Programmatic dependent launch: everything above (barriers, TMEM, the bulk copy of the constant weight image)
+    // overlaps the tail of the previous kernel of the forward; its activations are only touched below.
+    grid_dep_trigger();
+    EdgeRows pre;
+    if (MODE == EDGE) pre = load_edge_rows(a, blockIdx.x);
+    grid_dep_wait();
+    mlp_tiles<MODE, false>(a, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, blockIdx.x, gridDim.x, pre);
+    if (!ws.weights_ready && threadIdx.x == 0) mbar_wait(cs.bar_w, ws.w_phase);  // never leave a bulk copy in flight
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(cs.tmem, TMEM_COLS);
+}
+
+// ---- small graphs: the whole forward as ONE persistent kernel ----------------------------------------------------
+// A graph whose edge and node tiles all fit on the GPU at once (C1: 20x20 cloth = 18 + 4 tiles on 148 SMs) spends its
+// forward in launch boundaries: 33 launches of ~10 us of work each.  Here every tile gets its own CTA for the whole
+// forward: edge CTA t owns edge tile t through encoder and all message-passing steps, node CTA t owns node tile t through
+// encoder, all steps and the decoder.  The roles meet at two grid-wide counters per step in global memory (edge phase done
+// -> node phase; node phase done -> next edge phase); the weights of the NEXT walk are bulk-copied while the CTA waits for
+// the other role, so no weight load is exposed.  Data other CTAs produce (x for the edge gathers, agg for the node role)
+// is read with L2-only loads (ld_act<true>).  Arithmetic is mlp_tiles' -- the same as the multi-launch path.
+struct SmallArgs {
+    Args enc_node, enc_edge, edge, node, dec;   // edge / node: `unit` is replaced per step
+    const uint8_t* packed;
+    uint32_t edge_unit[32], node_unit[32];      // byte offsets of the steps' unit images
+    int steps, edge_tiles, node_tiles;
+    uint32_t* ctrl;                              // [0] encoders done, [1 + m] edge phase m, [33 + m] node phase m, [65] timeout flag
+    unsigned long long timeout_ns;
+};
+constexpr int SMALL_CTRL_WORDS = 128;
+
+__device__ __forceinline__ unsigned long long gnn_now_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// all threads of the CTA have finished their global writes of the phase -> one release increment
+__device__ __forceinline__ void grid_arrive(uint32_t* ctr) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+    }
+}
+// false: the other role did not get there within the timeout (the kernel then winds down instead of hanging the GPU)
+__device__ __forceinline__ bool grid_wait(uint32_t* ctr, uint32_t target, const SmallArgs& s) {
+    __shared__ int ok_flag;
+    if (threadIdx.x == 0) {
+        int ok = 1;
+        const unsigned long long t0 = gnn_now_ns();
+        uint32_t spins = 0, v;
+        while (true) {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+            if (v >= target) break;
+            if ((++spins & 255u) == 0 && (gnn_now_ns() - t0 > s.timeout_ns || *(volatile uint32_t*)(s.ctrl + 65))) {
+                *(volatile uint32_t*)(s.ctrl + 65) = 1;
+                ok = 0;
+                break;
+            }
+        }
+        ok_flag = ok;
+    }
+    __syncthreads();
+    const bool ok = ok_flag != 0;
+    __syncthreads();
+    return ok;
+}
+
+__global__ void __launch_bounds__(THREADS, 1) gnn_small_kernel(const __grid_constant__ SmallArgs s) {
+    extern __shared__ uint8_t smem_raw[];
+    // control words behind the largest carve-up (EDGE): the same place for every role of this kernel
+    const CtaSetup cs = cta_setup(smem_raw, ctrl_offset_of<EDGE>(0, LAT) > ctrl_offset_of<NODE>(0, LAT)
+                                                ? ctrl_offset_of<EDGE>(0, LAT) : ctrl_offset_of<NODE>(0, LAT));
+    WalkState ws;
+    const bool is_edge = (int)blockIdx.x < s.edge_tiles;
+    const int tile = is_edge ? blockIdx.x : blockIdx.x - s.edge_tiles;
+    const uint32_t everyone = (uint32_t)(s.edge_tiles + s.node_tiles);
+    // generic-proxy accesses of this CTA to shared memory (epilogues, staging) before the next bulk copy lands on it
+    auto next_weights = [&](auto mode_tag, const Args& a) {
+        __syncthreads();
+        fence_proxy_async();
+        issue_weights<decltype(mode_tag)::value>(a, cs.smem, cs.bar_w, ws);
+    };
+    bool ok = true;
+    if (is_edge) {
+        issue_weights<ENC>(s.enc_edge, cs.smem, cs.bar_w, ws);
+        mlp_tiles<ENC, false>(s.enc_edge, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
+        Args e = s.edge;
+        e.unit = s.packed + s.edge_unit[0];
+        const EdgeRows rows = load_edge_rows(e, tile);  // the CTA's tile never changes: its row indices are read once
+        next_weights(std::integral_constant<int, EDGE>{}, e);
+        grid_arrive(s.ctrl + 0);
+        for (int m = 0; m < s.steps && ok; ++m) {
+            ok = m == 0 ? grid_wait(s.ctrl + 0, everyone, s) : grid_wait(s.ctrl + 33 + (m - 1), (uint32_t)s.node_tiles, s);
+            if (!ok) break;
+            trace_pt(8);
+            mlp_tiles<EDGE, true>(e, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30, rows);
+            if (m + 1 < s.steps) {
+                e.unit = s.packed + s.edge_unit[m + 1];
+                next_weights(std::integral_constant<int, EDGE>{}, e);
+            }
+            grid_arrive(s.ctrl + 1 + m);
+            trace_pt(9);
+        }
+    } else {
+        issue_weights<ENC>(s.enc_node, cs.smem, cs.bar_w, ws);
+        mlp_tiles<ENC, false>(s.enc_node, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
+        Args n = s.node;
+        n.unit = s.packed + s.node_unit[0];
+        next_weights(std::integral_constant<int, NODE>{}, n);
+        grid_arrive(s.ctrl + 0);
+        for (int m = 0; m < s.steps && ok; ++m) {
+            ok = grid_wait(s.ctrl + 1 + m, (uint32_t)s.edge_tiles, s);
+            if (!ok) break;
+            trace_pt(8);
+            mlp_tiles<NODE, true>(n, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
+            if (m + 1 < s.steps) {
+                n.unit = s.packed + s.node_unit[m + 1];
+                next_weights(std::integral_constant<int, NODE>{}, n);
+            } else {
+                next_weights(std::integral_constant<int, DEC>{}, s.dec);
+            }
+            grid_arrive(s.ctrl + 33 + m);
+            trace_pt(9);
+        }
+        // the decoder reads the rows this CTA has just written itself
+        if (ok) mlp_tiles<DEC, false>(s.dec, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
+    }
+    if (!ws.weights_ready && threadIdx.x == 0) mbar_wait(cs.bar_w, ws.w_phase);  // never leave a bulk copy in flight
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(cs.tmem, TMEM_COLS);
 }
 
 // ---- graph preparation: dst-sorted edge order ---------------------------------------------------
@@ -503,6 +760,7 @@ struct Workspace {
     __nv_bfloat16* x_bf16;
     float* agg;
     __nv_bfloat16* e0;
+    uint32_t* ctrl;  // grid counters of gnn_small_kernel
     size_t bytes;
     static Workspace carve(void* ws, int N, int E) {
         Workspace w;
@@ -511,6 +769,7 @@ struct Workspace {
         w.x_bf16 = c.take<__nv_bfloat16>((size_t)N * LAT);
         w.agg = c.take<float>((size_t)N * LAT);
         w.e0 = c.take<__nv_bfloat16>((size_t)E * LAT);
+        w.ctrl = c.take<uint32_t>(SMALL_CTRL_WORDS);
         w.bytes = c.total();
         return w;
     }
@@ -816,6 +1075,8 @@ static int launch_edge2(const Args& a, cudaStream_t stream) {
 using namespace csb;
 using namespace csb::gnn;
 
+static int g_small_path = 1;  // csb_debug_gnn_small: 0 = always the multi-launch path
+
 extern "C" {
 
 size_t csb_gnn_param_floats(const csb_gnn_dims* d) {
@@ -841,6 +1102,19 @@ int csb_gnn_pack(const csb_gnn_dims* d, const float* flat_params, void* packed, 
     cudaStream_t stream = (cudaStream_t)stream_;
     CSB_LAUNCH("gnn_pack", stream, gnn_pack_kernel<<<t.n, 256, 0, stream>>>(flat_params, (uint8_t*)packed, t));
     return 0;
+}
+
+int csb_debug_gnn_trace(void* device_buffer, int block) {
+    unsigned long long* p = (unsigned long long*)device_buffer;
+    CSB_CUDA_TRY(cudaMemcpyToSymbol(csb::gnn::g_trace_buf, &p, sizeof(p)));
+    CSB_CUDA_TRY(cudaMemcpyToSymbol(csb::gnn::g_trace_block, &block, sizeof(block)));
+    return 0;
+}
+
+int csb_debug_gnn_small(int on) {
+    const int old = g_small_path;
+    if (on == 0 || on == 1) g_small_path = on;
+    return old;
 }
 
 size_t csb_gnn_graph_workspace_bytes(int E) { return GraphWs::carve(nullptr, E < 0 ? 0 : E).bytes; }
@@ -872,17 +1146,79 @@ size_t csb_gnn_workspace_bytes(const csb_gnn_dims* d, int N, int E) {
     return Workspace::carve(nullptr, N, E).bytes;
 }
 
+
+// The whole forward as one persistent kernel (gnn_small_kernel) when every tile can have its own CTA.  Returns 1 when it
+// ran, 0 when the graph does not qualify, < 0 / cudaError_t on failure.
+static int forward_small(const csb_gnn_dims* d, const PackTable& t, const uint8_t* pk, int N, int E, const float* x,
+                         const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
+                         const int32_t* perm, float* y, float* x_f32, float* agg, __nv_bfloat16* e0,
+                         __nv_bfloat16* x_bf16, uint32_t* ctrl, cudaStream_t stream) {
+    const int steps = d->nmessage_passing_steps;
+    const int te = (E + TILE_M - 1) / TILE_M, tn = (N + TILE_M - 1) / TILE_M;
+    int dev = 0, sms = 148, coop = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (!g_small_path || !coop || !ctrl || E <= 0 || steps < 1 || steps > 32 || te + tn > sms) return 0;
+    static unsigned long long configured = 0;
+    const size_t smem = smem_bytes(EDGE, 0, LAT);
+    CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_small_kernel, 232448 - 1024, &configured));
+    SmallArgs s{};
+    Args a{};
+    a.N = N;
+    a.unit = pk + t.u[0].dst; a.rows = N; a.kin = d->nnode_in; a.nout = LAT;
+    a.in = x; a.perm = nullptr; a.out_bf16 = x_bf16; a.x_f32 = x_f32;
+    s.enc_node = a;
+    a.unit = pk + t.u[1].dst; a.rows = E; a.kin = d->nedge_in;
+    a.in = edge_features; a.perm = perm; a.out_bf16 = e0; a.x_f32 = nullptr;
+    s.enc_edge = a;
+    Args e{};
+    e.N = N; e.kin = 0; e.nout = LAT; e.rows = E;
+    e.dst_sorted = dst_sorted; e.src_sorted = src_sorted; e.x_bf16 = x_bf16; e.e0 = e0; e.agg = agg;
+    s.edge = e;
+    Args n{};
+    n.N = N; n.kin = 0; n.nout = LAT; n.rows = N;
+    n.agg = agg; n.x_bf16 = x_bf16; n.x_f32 = x_f32; n.out_bf16 = x_bf16;
+    s.node = n;
+    Args c{};
+    c.N = N; c.kin = 0; c.nout = d->nnode_out;
+    c.unit = pk + t.u[t.n - 1].dst; c.rows = N; c.x_bf16 = x_bf16; c.y = y;
+    s.dec = c;
+    s.packed = pk;
+    for (int m = 0; m < steps; ++m) {
+        s.edge_unit[m] = (uint32_t)t.u[2 + 2 * m].dst;
+        s.node_unit[m] = (uint32_t)t.u[3 + 2 * m].dst;
+    }
+    s.steps = steps; s.edge_tiles = te; s.node_tiles = tn;
+    s.ctrl = ctrl;
+    s.timeout_ns = 2000000000ull;  // 2 s: a forward takes well under a millisecond
+    CSB_CUDA_TRY(cudaMemsetAsync(ctrl, 0, SMALL_CTRL_WORDS * sizeof(uint32_t), stream));
+    void* kargs[] = {(void*)&s};
+    CSB_LAUNCH("gnn_small", stream, cudaLaunchCooperativeKernel((const void*)gnn_small_kernel, dim3(te + tn), dim3(THREADS), kargs, smem, stream));
+    return 1;
+}
+
 static int forward_impl(const csb_gnn_dims* d, const void* packed, int N, int E, const float* x,
                         const float* edge_features, const int32_t* dst_sorted, const int32_t* src_sorted,
                         const int32_t* perm, float* y, float* x_latent_out, float* x_f32, float* agg,
                         __nv_bfloat16* e0, __nv_bfloat16* x_stack, size_t x_stride, __nv_bfloat16* agg_stack,
-                        cudaStream_t stream) {
+                        uint32_t* small_ctrl, cudaStream_t stream) {
     PackTable t;
     build_table(d, t, nullptr, nullptr);
     const uint8_t* pk = (const uint8_t*)packed;
     int rc;
 
     CSB_CUDA_TRY(cudaMemsetAsync(agg, 0, (size_t)N * LAT * sizeof(float), stream));
+    if (small_ctrl && x_stride == 0 && !agg_stack) {  // inference: small graphs run as one persistent kernel
+        rc = forward_small(d, t, pk, N, E, x, edge_features, dst_sorted, src_sorted, perm, y, x_f32, agg, e0, x_stack,
+                           small_ctrl, stream);
+        if (rc < 0 || rc > 1) return rc;
+        if (rc == 1) {
+            if (x_latent_out)
+                CSB_CUDA_TRY(cudaMemcpyAsync(x_latent_out, x_f32, (size_t)N * LAT * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+            return 0;
+        }
+    }
     Args a{};
     a.N = N;
     // encoders
@@ -935,7 +1271,7 @@ int csb_gnn_forward(const csb_gnn_dims* d, const void* packed, int N, int E, con
     Workspace w = Workspace::carve(ws, N, E);
     if (ws_bytes < w.bytes) return CSB_ERR_WORKSPACE;
     return forward_impl(d, packed, N, E, x, edge_features, dst_sorted, src_sorted, perm, y, x_latent_out, w.x_f32,
-                        w.agg, w.e0, w.x_bf16, 0, nullptr, (cudaStream_t)stream_);
+                        w.agg, w.e0, w.x_bf16, 0, nullptr, w.ctrl, (cudaStream_t)stream_);
 }
 
 size_t csb_gnn_train_state_bytes(const csb_gnn_dims* d, int N, int E) {
@@ -955,7 +1291,7 @@ int csb_gnn_forward_train(const csb_gnn_dims* d, const void* packed, int N, int 
     TrainState w = TrainState::carve(state, N, E, d->nmessage_passing_steps);
     if (state_bytes < w.bytes) return CSB_ERR_WORKSPACE;
     return forward_impl(d, packed, N, E, x, edge_features, dst_sorted, src_sorted, perm, y, nullptr, w.x_f32, w.agg,
-                        w.e0, w.x_stack, (size_t)N * LAT, w.agg_stack, (cudaStream_t)stream_);
+                        w.e0, w.x_stack, (size_t)N * LAT, w.agg_stack, nullptr, (cudaStream_t)stream_);
 }
 
 }  // extern "C"

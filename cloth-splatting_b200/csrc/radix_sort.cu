@@ -217,7 +217,7 @@ sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict_
 
 int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
                      const uint32_t* n_dev, size_t n_max, int end_bit, uint32_t* hist, uint32_t* tickets,
-                     uint32_t* lookback, int* side_out, cudaStream_t stream, bool hist_ready) {
+                     uint32_t* lookback, int* side_out, cudaStream_t stream, bool hist_ready, const char* launch_name) {
     if (end_bit < 1) end_bit = 1;
     if (end_bit > 32) return CSB_ERR_BAD_ARG;
     const int passes = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
@@ -234,7 +234,7 @@ int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint3
         CSB_LAUNCH("sort_histogram", stream, sort_histogram_kernel<<<hist_blocks, SORT_THREADS, 0, stream>>>(keys_a, n_dev, passes, hist));
     uint32_t *kin = keys_a, *kout = keys_b, *vin = vals_a, *vout = vals_b;
     for (int p = 0; p < passes; ++p) {
-        CSB_LAUNCH("sort_onesweep", stream, launch_pdl(kernel, dim3((unsigned)tiles), dim3(SORT_THREADS), 0, stream, 
+        CSB_LAUNCH(launch_name ? launch_name : "sort_onesweep", stream, launch_pdl(kernel, dim3((unsigned)tiles), dim3(SORT_THREADS), 0, stream, 
             kin, kout, vin, vout, n_dev, p * RADIX_BITS, hist + p * RADIX, tickets + p,
             lookback + (size_t)p * (tiles + 1) * RADIX));
         uint32_t* t = kin; kin = kout; kout = t;

@@ -923,7 +923,7 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
         int side = 0;
         rc = radix_sort_pairs(g.depth_keys, g.keys_b, g.order_a, g.order_b, g.control + CTRL_N_ENTRIES, n, 32,
                               g.control + CTRL_HIST_DEPTH, g.control + CTRL_TICKET_DEPTH, depth_lookback, &side,
-                              stream, /*hist_ready=*/true);
+                              stream, /*hist_ready=*/true, "sort_depth");
         if (rc) return rc;
         const uint32_t* order = side ? g.order_b : g.order_a;
         const int tile_passes = (higher_msb((uint32_t)total_tiles) + 7) / 8;
@@ -936,7 +936,7 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             int tside = 0;
             rc = radix_sort_pairs(b.tiles_a, b.tiles_b, b.vals_a, b.vals_b, g.control + CTRL_NUM_RENDERED,
                                   binning_capacity, tile_bits, g.control + CTRL_HIST_TILE,
-                                  g.control + CTRL_TICKET_TILE, b.lookback, &tside, stream, /*hist_ready=*/tile_hist_fused);
+                                  g.control + CTRL_TICKET_TILE, b.lookback, &tside, stream, /*hist_ready=*/tile_hist_fused, "sort_tile");
             if (rc) return rc;
             // the final order always lives in *_a for the consumers: copy back if it ended in *_b
             const uint32_t* st = tside ? b.tiles_b : b.tiles_a;

@@ -226,6 +226,7 @@ class EncodeProcessDecode(nn.Module):
         self._graph_key = None
         self._graph_src = None
         self._graph_copy = None
+        self._param_list = None  # the parameters in csb_gnn_pack order (invalidate_packed_weights() after replacing one)
         self._ws = None
         self._bws = None
         self.last_flat_grad = None  # flat fp32 gradient buffer of the latest backward (csb_gnn_pack order)
@@ -249,12 +250,31 @@ class EncodeProcessDecode(nn.Module):
         ps += mlp(self._decoder.node_fn, None)
         return ps
 
+    def invalidate_packed_weights(self):
+        """Forget the packed bf16 weight image.  Only needed after a Parameter OBJECT of this module was replaced by hand
+        (`m.weight = nn.Parameter(...)`): in-place updates, load_state_dict and .to() are noticed by themselves."""
+        self._packed, self._packed_key, self._param_list = None, None, None
+
     def _packed_weights(self, dev):
         lib = _abi.lib()
-        ps = self._ordered_params()
-        key = (str(dev),) + tuple((id(p), p.data_ptr(), p._version) for p in ps)
+        # Is the packed bf16 image still that of the parameters?  Asked on every forward, so it has to be cheap (the full
+        # (id, data_ptr, version) tuple over the 262 tensors cost ~0.1 ms of Python per call -- a quarter of a one-graph
+        # forward): every in-place update (optimizer step, load_state_dict, csb_optim.Adam) bumps the tensor's version
+        # counter, every re-allocation (.to(), .cuda(), param.data = ...) moves the first and the last tensor.
+        ps = self._param_list
+        if ps is None:
+            ps = self._param_list = self._ordered_params()
+        ver = 0
+        for p_ in ps:
+            ver += p_._version
+        key = (str(dev), ver, id(ps[0]), ps[0].data_ptr(), id(ps[-1]), ps[-1].data_ptr(), len(ps))
         if self._packed is not None and key == self._packed_key:
             return self._packed
+        ps = self._param_list = self._ordered_params()   # a parameter OBJECT may have been replaced: rebuild the list
+        ver = 0
+        for p_ in ps:
+            ver += p_._version
+        key = (str(dev), ver, id(ps[0]), ps[0].data_ptr(), id(ps[-1]), ps[-1].data_ptr(), len(ps))
         nfl = lib.csb_gnn_param_floats(ctypes.byref(self._dims))
         if nfl == 0:
             raise NotImplementedError(

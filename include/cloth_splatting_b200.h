@@ -62,6 +62,13 @@ int csb_profile_names(char* out, size_t out_bytes);
  * register cap, 4 / 5 / 6 = 1 / 3 / 2 with the delayed warp reduction).  All forward kernels produce the same per-pixel
  * bits.  Returns the previous value; a negative or out-of-range value only queries. */
 int csb_debug_render_variant(int variant);
+/* A-B switch of the GNN forward (process-wide): 1 (default) = graphs whose edge and node tiles all fit on the GPU at once
+ * run as ONE persistent kernel (gnn_small_kernel), 0 = always one launch per role and step.  Returns the previous value;
+ * any other argument only queries. */
+int csb_debug_gnn_small(int on);
+/* Debugging aid: thread 0 of CTA `block` of every GNN forward kernel stamps %globaltimer at the stations of its tile walk
+ * into device_buffer (u64 words: [0] = count, then time_ns << 8 | station; room for 8000 stamps).  NULL switches it off. */
+int csb_debug_gnn_trace(void* device_buffer, int block);
 /* Micro-benchmarks of the FP32 FMA pipe (scalar FFMA and packed FFMA2, FMAs per second) and of the SFU (MUFU.EX2 per
  * second) on the current device: the denominators of bench.py's compositing roofline, measured in the same
  * run as the kernels.  `scratch`: at least 8 * 256 * 4 bytes per SM of device memory.  Synchronises the stream. */

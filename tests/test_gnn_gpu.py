@@ -154,3 +154,30 @@ def test_graph_cache_by_identity_content_and_caller_supplied_graph():
         assert m._graph is not g5
     assert torch.equal(y0, y1) and torch.equal(y0, y2) and torch.equal(y0, y3)
     assert float((y4 - y0).abs().max()) < DEEP * float(y0.abs().max())
+
+
+@pytest.mark.parametrize("n", [5, 12, 20, 33])
+def test_persistent_small_graph_kernel_equals_the_multi_launch_path(n):
+    """Graphs whose tiles all fit on the GPU at once run the whole forward as ONE kernel (gnn_small_kernel: a CTA per tile,
+    grid counters between the edge and the node phase of every step).  Same arithmetic as the per-role launches: the only
+    difference is the order of the float atomics of the scatter-add, which both paths leave to the hardware."""
+    import csb_cabi
+
+    lib = csb_cabi.lib()
+    x, ei, ef, _, _ = S.gnn_inputs(n, 4)
+    m = _model()
+    outs = {}
+    for mode in (1, 0, 1):
+        old = lib.csb_debug_gnn_small(mode)
+        try:
+            outs.setdefault(mode, []).append(_run(m, x, ei, ef))
+            lat = _run(m, x, ei, ef, latent=True)
+            assert torch.isfinite(lat).all()
+        finally:
+            lib.csb_debug_gnn_small(old)
+    scale = float(outs[0][0].abs().max())
+    assert float((outs[1][0] - outs[0][0]).abs().max()) <= TIGHT * scale
+    assert float((outs[1][1] - outs[1][0]).abs().max()) <= TIGHT * scale   # and it can be called again (counters re-armed)
+    sd = {k: v.cpu() for k, v in m.state_dict().items()}
+    ref = gnn_oracle.forward(sd, torch.from_numpy(x), torch.from_numpy(ei), torch.from_numpy(ef))   # fp32 restatement
+    assert float((outs[1][0] - ref).abs().max()) <= LOOSE * _scale(ref)
