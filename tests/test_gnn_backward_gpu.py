@@ -62,7 +62,13 @@ def run_case(steps, n, seed, emulate=False):
 def test_gradients_tight_where_forward_is_reproduced(steps, n):
     got, ref, y, yr = run_case(steps, n, 3, emulate=True)
     if float((y - yr).abs().max()) > 1e-6 * max(float(yr.abs().max()), 1e-6):
-        pytest.skip("the emulating oracle did not reproduce this forward bit for bit")
+        # The order of the float atomics of the scatter-add is the hardware's: on some runs a bf16 rounding of `agg` falls the
+        # other way and the emulating oracle no longer reproduces this forward bit for bit (graphs with more than one warp
+        # of edges per node tile).  The tight bound then does not apply -- ReLU masks may differ -- and the case is held
+        # to the bound of the larger graphs instead: within 1.5x the oracle's own bf16-vs-fp32 deviation + 3e-2.
+        _, ref32, _, _ = run_case(steps, n, 3, emulate=False)
+        _assert_within_floor(got, ref32, ref, f"steps {steps}, n {n} (forward not reproduced bit for bit)")
+        return
     bad = {k: _rel(got[k], r) for k, r in ref.items() if r is not None and not _rel(got[k], r) < 2e-2}
     assert not bad, bad
 
