@@ -860,20 +860,42 @@ def dropin_bench(dev, impl, warm=8, steps=40, W=800, H=800):
     else:
         step = _reference_train_step(dev, pc, sim, mesh_opt, cams, opt, bg)
 
-    losses, t = [], []
-    for it in range(1, warm + steps + 1):
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        _, loss, _ = step(it)
-        torch.cuda.synchronize()
-        t.append((time.perf_counter() - t0) * 1e3)
-        losses.append(float(loss))
-    ms = sorted(t[warm:])
-    med = ms[len(ms) // 2]
-    return {"what": "train_step (reference signature), 3 views 800x800, 10108 Gaussians, SH 3, one iteration", "impl": impl,
-            "steps": steps, "warmup": warm, "ms_per_iteration": med, "ms_min": ms[0], "ms_max": ms[-1],
-            "mpix_per_s": 3 * W * H / med / 1e3, "loss_first": losses[0], "loss_last": losses[-1],
-            "timing": "wall clock around the call, device synchronised on both sides"}
+    def timed_loop(first_it):
+        losses, t = [], []
+        for it in range(first_it, first_it + warm + steps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            _, loss, _ = step(it)
+            torch.cuda.synchronize()
+            t.append((time.perf_counter() - t0) * 1e3)
+            losses.append(float(loss))
+        ms = sorted(t[warm:])
+        return ms[len(ms) // 2], ms[0], ms[-1], losses
+
+    out = {"what": "train_step (reference signature), 3 views 800x800, 10108 Gaussians, SH 3, one iteration", "impl": impl,
+           "steps": steps, "warmup": warm, "timing": "wall clock around the call, device synchronised on both sides"}
+    if impl == "b200":
+        # (1) the ground truth crosses PCIe in every iteration, like the reference's `.cuda()` per view (train_utils.py:262);
+        # (2) the product's default: a view's planes stay resident after their first use (train_utils.ResidentPlanes)
+        from scene_reconstruction import train_utils as TU
+
+        budget = TU.resident_planes.budget
+        TU.resident_planes.budget = 0
+        TU.resident_planes.clear()
+        med, lo, hi, losses = timed_loop(1)
+        TU.resident_planes.budget = budget
+        med_r, lo_r, hi_r, _ = timed_loop(1 + warm + steps)
+        out.update({"ms_per_iteration": med, "ms_min": lo, "ms_max": hi, "mpix_per_s": 3 * W * H / med / 1e3,
+                    "ground_truth": "uploaded from pinned host memory in every iteration (3 x 7.68 MB), as the reference does",
+                    "resident_ground_truth": {"ms_per_iteration": med_r, "ms_min": lo_r, "ms_max": hi_r, "mpix_per_s": 3 * W * H / med_r / 1e3,
+                                              "what": "the product's default: a view's ground-truth planes stay in HBM after their first "
+                                                      "use (ResidentPlanes, LRU over CSB_GT_CACHE_MB), so steady-state iterations upload nothing"}})
+    else:
+        med, lo, hi, losses = timed_loop(1)
+        out.update({"ms_per_iteration": med, "ms_min": lo, "ms_max": hi, "mpix_per_s": 3 * W * H / med / 1e3,
+                    "ground_truth": "uploaded from pinned host memory in every iteration (3 x 7.68 MB)"})
+    out.update({"loss_first": losses[0], "loss_last": losses[-1]})
+    return out
 
 
 def _reference_train_step(dev, pc, sim, mesh_opt, cams, opt, bg):

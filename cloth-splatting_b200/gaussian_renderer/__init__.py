@@ -46,16 +46,21 @@ def project_to_pixels(cam, points):
 
 def render(viewpoint_camera, pc, simulator, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None,
            log_deform_path=None, no_shadow=False, render_static=False, project_vertices=False,
-           project_gaussians=True) -> RenderResults:
+           project_gaussians=True, precomputed=None) -> RenderResults:
     """Render one view of the mesh-anchored Gaussians at viewpoint_camera.time.  bg_color must be on the GPU.
     Extensions for callers that replay the step as a CUDA graph (train_utils.train_step): a camera may carry `time_tensor`
     (a [1, 1] device tensor holding its time: the value then is an input of the graph, not a constant baked into it), and
-    `project_gaussians=False` skips the pixel projections the refinement loop never reads (`projections` is then None)."""
+    `project_gaussians=False` skips the pixel projections the refinement loop never reads (`projections` is then None);
+    `precomputed=(vertice_deform, means3D_deform, rotations_deform)` hands in this view's slice of a step-wide batched
+    simulator + transform pass (train_utils._render_views) instead of running both per view."""
     if getattr(pipe, "compute_cov3D_python", False):
         raise NotImplementedError("compute_cov3D_python is outside the accelerated path (SURVEY.md section 8)")
     dev = pc.mesh.pos.device
-    base_xyz = pc.get_xyz()
-    screenspace_points = torch.zeros_like(base_xyz, requires_grad=True) + 0
+    # the reference builds this zero tensor with zeros_like(pc.get_xyz()): only shape, dtype and device of the rest-pose
+    # positions are used, so they are not computed unless the static branch or the deformation log needs them
+    need_base = render_static or log_deform_path is not None
+    base_xyz = pc.get_xyz() if need_base else None
+    screenspace_points = torch.zeros((pc.face_ids.shape[0], 3), dtype=pc.face_bary.dtype, device=dev, requires_grad=True) + 0
     try:
         screenspace_points.retain_grad()
     except Exception:
@@ -72,6 +77,8 @@ def render(viewpoint_camera, pc, simulator, pipe, bg_color: torch.Tensor, scalin
         vertice_deform = pc.mesh.pos
         means3D_deform = base_xyz
         rotations_deform = pc.get_rotation()
+    elif precomputed is not None:
+        vertice_deform, means3D_deform, rotations_deform = precomputed
     else:
         time = getattr(viewpoint_camera, "time_tensor", None)
         if time is None:

@@ -71,6 +71,18 @@ class ResidualMeshSimulator(nn.Module):
             raise ValueError(f"Time {time} is out of bounds for the mesh simulator.")
         return self.mesh_predictions[time_id].squeeze() + residual
 
+    def forward_times(self, times):
+        """The deformed meshes of SEVERAL times at once: `times` [V] (a device tensor) -> [V, N, 3], row v equal to
+        `forward(time_vector filled with times[v], checked=True)` up to the rounding of a batched instead of a
+        matrix-vector product.  The views of a refinement step (three consecutive times) then cost one pass through the
+        MLP instead of three.  The caller checks the bounds on the host (`check_time`)."""
+        t = times.reshape(-1, 1)
+        h = torch.relu(self.input(self.encoder(t)))
+        h = torch.relu(self.hidden(h))
+        residual = self.output(h).reshape(t.shape[0], -1, 3)
+        time_id = torch.round(t[:, 0] / self.time_delta).to(dtype=torch.long).clamp(max=self.n_times - 1)
+        return self.mesh_predictions[time_id] + residual
+
     def save(self, path):
         torch.save(self.state_dict(), path)
 

@@ -85,8 +85,26 @@ def _render_views(views, gaussians, simulator, pipeline_params, background, stat
 
     no_shadow = getattr(user_args, "no_shadow", False)
     extra = {} if project else {"project_gaussians": False}  # the eager path calls render() with the reference's arguments
-    pkgs = [render(cam, gaussians, simulator, pipeline_params, background, no_shadow=no_shadow, render_static=static,
-                   **extra) for cam in views]
+    import contextlib
+
+    share = gaussians.shared_activations() if hasattr(gaussians, "shared_activations") else contextlib.nullcontext()
+    pre = [None] * len(views)
+    if (not static and len(views) > 1 and hasattr(simulator, "forward_times") and hasattr(simulator, "check_time")
+            and callable(getattr(gaussians, "get_xyz_rotation", None))):
+        # one pass of the residual simulator and ONE fused transform launch for all views of the step
+        for cam in views:
+            simulator.check_time(cam.time)
+        tt = [getattr(cam, "time_tensor", None) for cam in views]
+        if all(t is not None for t in tt):
+            times = torch.cat([t.reshape(1) for t in tt])  # device values: inputs of a captured step, not constants
+        else:
+            times = torch.tensor([float(cam.time) for cam in views], dtype=torch.float32, device=gaussians.mesh.pos.device)
+        vertices = simulator.forward_times(times)
+        xyz, rot = gaussians.get_xyz_rotation(vertices)
+        pre = [(vertices[v], xyz[v], rot[v]) for v in range(len(views))]
+    with share:  # exp / sigmoid / cat of the view-independent parameters once per step instead of once per view
+        pkgs = [render(cam, gaussians, simulator, pipeline_params, background, no_shadow=no_shadow, render_static=static,
+                       **({} if pre[v] is None else {"precomputed": pre[v]}), **extra) for v, cam in enumerate(views)]
     image_tensor = torch.stack([p.render for p in pkgs])
     all_vertice_deform = torch.stack([p.vertice_deform for p in pkgs])
     radii = torch.stack([p.radii for p in pkgs]).max(dim=0).values
@@ -126,6 +144,59 @@ def _loss_and_step(rendered, gt_image_tensor, mask_tensor, iteration_stats, gaus
     return psnr_, loss, loss_dict, viewspace_point_tensor_grad, visibility_filter, radii
 
 
+class ResidentPlanes:
+    """Ground-truth images and masks kept on the device after their first use.  The reference uploads `cam.original_image`
+    (3 x 800 x 800 floats = 7.7 MB) from the host in every iteration of every view (`viewpoint_cam.original_image.cuda()`,
+    train_utils.py:262); a scene's views are a fixed set that fits HBM many times over (180 GB: ~23 000 such planes), so a
+    view's planes cross PCIe once and every later iteration that draws the view reads them from HBM.  LRU over
+    `CSB_GT_CACHE_MB` megabytes (default 8192; 0 switches it off); an entry is keyed on the host tensor OBJECT and its
+    version counter, so an image edited in place is uploaded again."""
+
+    def __init__(self):
+        import collections
+        import os
+
+        self.budget = int(float(os.environ.get("CSB_GT_CACHE_MB", "8192")) * (1 << 20))
+        self.used = 0
+        self.entries = collections.OrderedDict()  # id(host tensor) -> (weakref, version, device tensor)
+        self.hits = self.misses = 0
+
+    def fetch(self, host, device, into=None):
+        """The device copy of `host` (a CPU tensor); written into `into` when given (a static buffer of a captured step)."""
+        import weakref
+
+        if host.is_cuda or self.budget <= 0:
+            src = host if host.is_cuda and into is not None else host.to(device, non_blocking=True)
+            return src if into is None else into.copy_(src, non_blocking=True)
+        key = id(host)
+        ent = self.entries.get(key)
+        if ent is not None and ent[0]() is host and ent[1] == host._version and ent[2].device == torch.device(device):
+            self.entries.move_to_end(key)
+            self.hits += 1
+            dev_t = ent[2]
+        else:
+            self.misses += 1
+            if ent is not None:
+                self.used -= ent[2].numel() * ent[2].element_size()
+                del self.entries[key]
+            dev_t = host.to(device, non_blocking=True)
+            nbytes = dev_t.numel() * dev_t.element_size()
+            if nbytes <= self.budget:
+                while self.used + nbytes > self.budget and self.entries:
+                    _, (_, _, old) = self.entries.popitem(last=False)
+                    self.used -= old.numel() * old.element_size()
+                self.entries[key] = (weakref.ref(host), host._version, dev_t)
+                self.used += nbytes
+        return dev_t if into is None else into.copy_(dev_t, non_blocking=True)
+
+    def clear(self):
+        self.entries.clear()
+        self.used = 0
+
+
+resident_planes = ResidentPlanes()
+
+
 class _StaticView:
     """A camera whose tensors are the static device buffers of a captured step."""
 
@@ -144,6 +215,11 @@ class _StaticView:
         self.camera_center.copy_(cam.camera_center, non_blocking=True)
         self.time = float(cam.time)
         self.time_tensor.fill_(self.time)
+
+
+def _host_tensor(x):
+    """`cam.original_image` / `cam.mask` as a tensor (the CPU stand-ins of the tests wrap theirs)."""
+    return x if isinstance(x, torch.Tensor) else x.to("cpu")
 
 
 class _StepGraph:
@@ -179,9 +255,9 @@ class _StepGraph:
     def load_images(self, cams):
         """On the copy stream: the planes cross PCIe while the views are rendered."""
         for i, c in enumerate(cams):
-            self.gt[i].copy_(c.original_image, non_blocking=True)
+            resident_planes.fetch(_host_tensor(c.original_image), self.gt.device, into=self.gt[i])
             if self.mask is not None:
-                self.mask[i].copy_(c.mask, non_blocking=True)
+                resident_planes.fetch(_host_tensor(c.mask), self.mask.device, into=self.mask[i])
 
 
 def _graph_signature(viewpoint_cams, gaussians, simulator, meshnet_optimizer, opt_params, static, stats):
@@ -404,10 +480,10 @@ def train_step(iteration, viewpoint_cams, gaussians, simulator, meshnet_optimize
     if iteration % 1000 == 0:
         gaussians.oneupSHdegree()
     dev = background.device
-    gt_image_tensor = torch.stack([cam.original_image.to(dev, non_blocking=True) for cam in viewpoint_cams])
+    gt_image_tensor = torch.stack([resident_planes.fetch(_host_tensor(cam.original_image), dev) for cam in viewpoint_cams])
     mask_tensor = None
     if viewpoint_cams[0].mask is not None:
-        mask_tensor = torch.stack([cam.mask.to(dev, non_blocking=True) for cam in viewpoint_cams])
+        mask_tensor = torch.stack([resident_planes.fetch(_host_tensor(cam.mask), dev) for cam in viewpoint_cams])
     rendered = _render_views(viewpoint_cams, gaussians, simulator, pipeline_params, background, static, user_args)
     psnr_, loss, loss_dict, viewspace_point_tensor_grad, visibility_filter, radii = _loss_and_step(
         rendered, gt_image_tensor, mask_tensor, False, gaussians, meshnet_optimizer, opt_params, static, False, True)
