@@ -10,6 +10,8 @@
 // One upfront histogram kernel counts every pass' digits; each pass is ONE kernel: a tile of
 // 4096 pairs is ranked with warp match-any + per-warp digit counters, the tile's digit counts are
 // published and the global prefix is obtained by decoupled look-back over earlier tiles.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace csb {
@@ -56,8 +58,8 @@ sort_histogram_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restr
 }
 
 // ---- one onesweep pass -------------------------------------------------------------
-template <int SORT_ITEMS>  // pairs per thread: 16 (4096-pair tiles) or 4 (1024-pair tiles, small inputs)
-__global__ void __launch_bounds__(SORT_THREADS, 3)
+template <int SORT_ITEMS, int MINB>  // pairs per thread: 16 (4096-pair tiles) or 4 (1024-pair tiles, small inputs); resident blocks asked for
+__global__ void __launch_bounds__(SORT_THREADS, MINB)
 sort_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                      const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                      const uint32_t* __restrict__ n_dev, int shift, const uint32_t* __restrict__ hist,
@@ -225,8 +227,14 @@ int radix_sort_pairs(uint32_t* keys_a, uint32_t* keys_b, uint32_t* vals_a, uint3
     if (n_max == 0) { *side_out = 0; return 0; }
     const size_t tile = sort_tile_size(n_max);
     const size_t tiles = (n_max + tile - 1) / tile;
-    auto kernel = tile == CSB_SORT_TILE ? sort_onesweep_kernel<CSB_SORT_TILE / SORT_THREADS>
-                                        : sort_onesweep_kernel<CSB_SORT_TILE_SMALL / SORT_THREADS>;
+    // Big inputs (the tile sort of C3 / C4: tens of millions of pairs) run with four resident blocks per SM (64 registers,
+    // a 32-byte spill) instead of three: 486 -> 456 us for C3's two tile passes, 1745 -> 1642 us at C4; the small depth
+    // sorts (<= a few million keys, latency-bound look-back chains) are faster with three.  CSB_SORT_MINB overrides (A/B).
+    static const int forced = [] { const char* e = getenv("CSB_SORT_MINB"); return e ? atoi(e) : 0; }();
+    const int minb = forced ? forced : (n_max >= ((size_t)8 << 20) ? 4 : 3);
+    auto kernel = tile == CSB_SORT_TILE ? (minb >= 4 ? sort_onesweep_kernel<CSB_SORT_TILE / SORT_THREADS, 4>
+                                                     : sort_onesweep_kernel<CSB_SORT_TILE / SORT_THREADS, 3>)
+                                        : sort_onesweep_kernel<CSB_SORT_TILE_SMALL / SORT_THREADS, 3>;
     int hist_blocks = (int)((n_max + SORT_THREADS * 16 - 1) / (SORT_THREADS * 16));
     if (hist_blocks > 148 * 8) hist_blocks = 148 * 8;
     if (hist_blocks < 1) hist_blocks = 1;

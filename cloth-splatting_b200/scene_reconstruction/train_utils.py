@@ -88,7 +88,7 @@ def _render_views(views, gaussians, simulator, pipeline_params, background, stat
     import contextlib
 
     share = gaussians.shared_activations() if hasattr(gaussians, "shared_activations") else contextlib.nullcontext()
-    pre = [None] * len(views)
+    pre, batched_vertices = [None] * len(views), None
     if (not static and len(views) > 1 and hasattr(simulator, "forward_times") and hasattr(simulator, "check_time")
             and callable(getattr(gaussians, "get_xyz_rotation", None))):
         # one pass of the residual simulator and ONE fused transform launch for all views of the step
@@ -101,12 +101,14 @@ def _render_views(views, gaussians, simulator, pipeline_params, background, stat
             times = torch.tensor([float(cam.time) for cam in views], dtype=torch.float32, device=gaussians.mesh.pos.device)
         vertices = simulator.forward_times(times)
         xyz, rot = gaussians.get_xyz_rotation(vertices)
-        pre = [(vertices[v], xyz[v], rot[v]) for v in range(len(views))]
+        # unbind: ONE stack in the backward pass per tensor instead of a zero-fill + add per view and tensor
+        pre = list(zip(vertices.unbind(0), xyz.unbind(0), rot.unbind(0)))
+        batched_vertices = vertices
     with share:  # exp / sigmoid / cat of the view-independent parameters once per step instead of once per view
         pkgs = [render(cam, gaussians, simulator, pipeline_params, background, no_shadow=no_shadow, render_static=static,
                        **({} if pre[v] is None else {"precomputed": pre[v]}), **extra) for v, cam in enumerate(views)]
     image_tensor = torch.stack([p.render for p in pkgs])
-    all_vertice_deform = torch.stack([p.vertice_deform for p in pkgs])
+    all_vertice_deform = batched_vertices if batched_vertices is not None else torch.stack([p.vertice_deform for p in pkgs])
     radii = torch.stack([p.radii for p in pkgs]).max(dim=0).values
     visibility_filter = torch.stack([p.visibility_filter for p in pkgs]).any(dim=0)
     return pkgs, image_tensor, all_vertice_deform, radii, visibility_filter
