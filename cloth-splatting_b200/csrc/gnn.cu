@@ -194,7 +194,7 @@ __device__ __forceinline__ EdgeRows load_edge_rows(const Args& a, int tile) {
     return r;
 }
 
-template <int MODE, bool COH>
+template <int MODE, bool COH, bool TRACE>
 __device__ __forceinline__ void mlp_tiles(const Args& a, uint8_t* smem, const uint32_t tmem, const uint32_t bar_w,
                                           const uint32_t bar_mma, WalkState& ws, const int tile0, const int tile_step,
                                           const EdgeRows pre = EdgeRows()) {
@@ -222,7 +222,7 @@ __device__ __forceinline__ void mlp_tiles(const Args& a, uint8_t* smem, const ui
         const int row0 = tile * TILE_M;
         const int grow = row0 + row;  // global row of this thread's epilogue row
         const bool rvalid = grow < a.rows;
-        if (MODE == EDGE || MODE == NODE) trace_pt(1);
+        if (TRACE && (MODE == EDGE || MODE == NODE)) trace_pt(1);
 
         // ------------------------------------------------------------------ stage the first A operand
         if (MODE == EDGE) {
@@ -384,7 +384,7 @@ __device__ __forceinline__ void mlp_tiles(const Args& a, uint8_t* smem, const ui
                 fence_proxy_async();
                 tc_fence_before();
                 __syncthreads();
-                if (MODE == EDGE || MODE == NODE) trace_pt(2);
+                if (TRACE && (MODE == EDGE || MODE == NODE)) trace_pt(2);
                 // One elected lane of warp 0 issues the chain (a warp-uniform branch: the descriptor arithmetic stays in the
                 // uniform datapath instead of being moved there value by value behind a divergent `tid == 0`); the chunk loop
                 // is unrolled to its compile-time maximum.  Measured (csb_debug_gnn_trace): 12 MMAs took 1.06 us to issue.
@@ -408,12 +408,12 @@ __device__ __forceinline__ void mlp_tiles(const Args& a, uint8_t* smem, const ui
                     __syncwarp();
                 }
                 wchunk += nchunks;
-                if (MODE == EDGE || MODE == NODE) trace_pt(3);
+                if (TRACE && (MODE == EDGE || MODE == NODE)) trace_pt(3);
                 if (MODE == EDGE && first && ph == 0) edge_gather(1);  // in flight while phase 0 is multiplied
                 mbar_wait(bar_mma, mma_parity);
                 mma_parity ^= 1;
                 tc_fence_after();
-                if (MODE == EDGE || MODE == NODE) trace_pt(4);
+                if (TRACE && (MODE == EDGE || MODE == NODE)) trace_pt(4);
             }
             // ---- epilogue of this layer: TMEM -> registers
             float v[64];
@@ -433,7 +433,7 @@ __device__ __forceinline__ void mlp_tiles(const Args& a, uint8_t* smem, const ui
                                           pack_bf16(h[6], h[7]));
                     *reinterpret_cast<uint4*>(sA + (size_t)half * CHUNK_BYTES + swz_off(row, c)) = pk;
                 }
-                if (MODE == EDGE || MODE == NODE) trace_pt(5);
+                if (TRACE && (MODE == EDGE || MODE == NODE)) trace_pt(5);
                 continue;
             }
             if (MODE == DEC) {
@@ -475,7 +475,7 @@ __device__ __forceinline__ void mlp_tiles(const Args& a, uint8_t* smem, const ui
             const float* lb = sF + 4 * LAT + half * 64;
 #pragma unroll
             for (int j = 0; j < 64; ++j) v[j] = (v[j] - mean) * rstd * lg[j] + lb[j];
-            if (MODE == EDGE || MODE == NODE) trace_pt(6);
+            if (TRACE && (MODE == EDGE || MODE == NODE)) trace_pt(6);
 
             if (MODE == ENC) {
                 if (rvalid) {
@@ -559,7 +559,7 @@ __device__ __forceinline__ void mlp_tiles(const Args& a, uint8_t* smem, const ui
             // the next tile overwrites sA / TMEM: order this tile's TMEM reads and staging before it
             tc_fence_before();
             __syncthreads();
-            if (MODE == EDGE || MODE == NODE) trace_pt(7);
+            if (TRACE && (MODE == EDGE || MODE == NODE)) trace_pt(7);
         }
     }
     ws.weights_ready = weights_ready;
@@ -596,7 +596,7 @@ template <int MODE> __device__ __forceinline__ size_t ctrl_offset_of(int kin, in
            SCRATCH_FLOATS * 4 + 2 * TILE_M * 4;
 }
 
-template <int MODE>
+template <int MODE, bool TRACE = false>
 __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1) gnn_mlp_kernel(const __grid_constant__ Args a) {
     extern __shared__ uint8_t smem_raw[];
     const CtaSetup cs = cta_setup(smem_raw, ctrl_offset_of<MODE>(a.kin, a.nout));
@@ -608,7 +608,7 @@ __global__ void __launch_bounds__(THREADS, (MODE == ENC || MODE == DEC) ? 2 : 1)
     EdgeRows pre;
     if (MODE == EDGE) pre = load_edge_rows(a, blockIdx.x);
     grid_dep_wait();
-    mlp_tiles<MODE, false>(a, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, blockIdx.x, gridDim.x, pre);
+    mlp_tiles<MODE, false, TRACE>(a, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, blockIdx.x, gridDim.x, pre);
     if (!ws.weights_ready && threadIdx.x == 0) mbar_wait(cs.bar_w, ws.w_phase);  // never leave a bulk copy in flight
     tc_fence_before();
     __syncthreads();
@@ -670,6 +670,7 @@ __device__ __forceinline__ bool grid_wait(uint32_t* ctr, uint32_t target, const 
     return ok;
 }
 
+template <bool TRACE>
 __global__ void __launch_bounds__(THREADS, 1) gnn_small_kernel(const __grid_constant__ SmallArgs s) {
     extern __shared__ uint8_t smem_raw[];
     // control words behind the largest carve-up (EDGE): the same place for every role of this kernel
@@ -688,7 +689,7 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_small_kernel(const __grid_cons
     bool ok = true;
     if (is_edge) {
         issue_weights<ENC>(s.enc_edge, cs.smem, cs.bar_w, ws);
-        mlp_tiles<ENC, false>(s.enc_edge, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
+        mlp_tiles<ENC, false, false>(s.enc_edge, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
         Args e = s.edge;
         e.unit = s.packed + s.edge_unit[0];
         const EdgeRows rows = load_edge_rows(e, tile);  // the CTA's tile never changes: its row indices are read once
@@ -697,18 +698,18 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_small_kernel(const __grid_cons
         for (int m = 0; m < s.steps && ok; ++m) {
             ok = m == 0 ? grid_wait(s.ctrl + 0, everyone, s) : grid_wait(s.ctrl + 33 + (m - 1), (uint32_t)s.node_tiles, s);
             if (!ok) break;
-            trace_pt(8);
-            mlp_tiles<EDGE, true>(e, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30, rows);
+            if (TRACE) trace_pt(8);
+            mlp_tiles<EDGE, true, TRACE>(e, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30, rows);
             if (m + 1 < s.steps) {
                 e.unit = s.packed + s.edge_unit[m + 1];
                 next_weights(std::integral_constant<int, EDGE>{}, e);
             }
             grid_arrive(s.ctrl + 1 + m);
-            trace_pt(9);
+            if (TRACE) trace_pt(9);
         }
     } else {
         issue_weights<ENC>(s.enc_node, cs.smem, cs.bar_w, ws);
-        mlp_tiles<ENC, false>(s.enc_node, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
+        mlp_tiles<ENC, false, false>(s.enc_node, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
         Args n = s.node;
         n.unit = s.packed + s.node_unit[0];
         next_weights(std::integral_constant<int, NODE>{}, n);
@@ -716,8 +717,8 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_small_kernel(const __grid_cons
         for (int m = 0; m < s.steps && ok; ++m) {
             ok = grid_wait(s.ctrl + 1 + m, (uint32_t)s.edge_tiles, s);
             if (!ok) break;
-            trace_pt(8);
-            mlp_tiles<NODE, true>(n, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
+            if (TRACE) trace_pt(8);
+            mlp_tiles<NODE, true, TRACE>(n, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
             if (m + 1 < s.steps) {
                 n.unit = s.packed + s.node_unit[m + 1];
                 next_weights(std::integral_constant<int, NODE>{}, n);
@@ -725,10 +726,10 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_small_kernel(const __grid_cons
                 next_weights(std::integral_constant<int, DEC>{}, s.dec);
             }
             grid_arrive(s.ctrl + 33 + m);
-            trace_pt(9);
+            if (TRACE) trace_pt(9);
         }
         // the decoder reads the rows this CTA has just written itself
-        if (ok) mlp_tiles<DEC, false>(s.dec, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
+        if (ok) mlp_tiles<DEC, false, false>(s.dec, cs.smem, cs.tmem, cs.bar_w, cs.bar_mma, ws, tile, 1 << 30);
     }
     if (!ws.weights_ready && threadIdx.x == 0) mbar_wait(cs.bar_w, ws.w_phase);  // never leave a bulk copy in flight
     tc_fence_before();
@@ -792,10 +793,14 @@ struct GraphWs {
     }
 };
 
+static bool g_trace_on = false;  // csb_debug_gnn_trace: the instantiations with %globaltimer stations (EDGE / NODE roles)
+
 template <int MODE>
 static int launch_role(const Args& a, int kin, int nout, cudaStream_t stream, const char* name) {
-    static unsigned long long configured = 0;  // per-device opt-in (common.cuh)
+    static unsigned long long configured = 0, configured_t = 0;  // per-device opt-in (common.cuh)
     const size_t smem = smem_bytes(MODE, kin, nout);
+    const bool traced = g_trace_on && (MODE == EDGE || MODE == NODE);
+    if (traced) CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_mlp_kernel<MODE, true>, 232448 - 1024, &configured_t));
     CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_mlp_kernel<MODE>, 232448 - 1024, &configured));
     if (smem > 232448 - 1024) return CSB_ERR_UNSUPPORTED;
     const int tiles = (a.rows + TILE_M - 1) / TILE_M;
@@ -806,7 +811,8 @@ static int launch_role(const Args& a, int kin, int nout, cudaStream_t stream, co
     // ENC / DEC: ~108 KB of shared memory and 128 registers: two CTAs per SM overlap each other's serial tile chains
     const int per_sm = (MODE == ENC || MODE == DEC) ? 2 : 1;
     const int grid = tiles < sms * per_sm ? tiles : sms * per_sm;
-    CSB_LAUNCH(name, stream, launch_pdl(gnn_mlp_kernel<MODE>, dim3(grid), dim3(THREADS), smem, stream, a));
+    if (traced) CSB_LAUNCH(name, stream, launch_pdl(gnn_mlp_kernel<MODE, true>, dim3(grid), dim3(THREADS), smem, stream, a));
+    else CSB_LAUNCH(name, stream, launch_pdl(gnn_mlp_kernel<MODE>, dim3(grid), dim3(THREADS), smem, stream, a));
     return 0;
 }
 
@@ -1031,13 +1037,22 @@ __global__ void __launch_bounds__(THREADS, 1) gnn_edge2_kernel(const __grid_cons
             __syncwarp();
             const int col = rd * 32 + lane;
             float acc = 0.f;
+            // the column's 32 values are fetched 16 at a time BEFORE the walk that may issue atomics: behind an atomic the
+            // compiler keeps every shared load in place, and each iteration then waits out its own load (csb_debug_gnn_trace:
+            // the scatter was 6.1 us of a 19.5 us tile)
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                acc += st[i * 33 + lane];
-                if ((ends >> i) & 1u) {
-                    const int dd = __shfl_sync(full, d, i);
-                    if (dd >= 0) atomicAdd(a.agg + (size_t)dd * LAT + col, acc);
-                    acc = 0.f;
+            for (int h = 0; h < 2; ++h) {
+                float xv[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) xv[i] = st[(h * 16 + i) * 33 + lane];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    acc += xv[i];
+                    if ((ends >> (h * 16 + i)) & 1u) {
+                        const int dd = __shfl_sync(full, d, h * 16 + i);
+                        if (dd >= 0) atomicAdd(a.agg + (size_t)dd * LAT + col, acc);
+                        acc = 0.f;
+                    }
                 }
             }
             __syncwarp();
@@ -1108,6 +1123,7 @@ int csb_debug_gnn_trace(void* device_buffer, int block) {
     unsigned long long* p = (unsigned long long*)device_buffer;
     CSB_CUDA_TRY(cudaMemcpyToSymbol(csb::gnn::g_trace_buf, &p, sizeof(p)));
     CSB_CUDA_TRY(cudaMemcpyToSymbol(csb::gnn::g_trace_block, &block, sizeof(block)));
+    csb::gnn::g_trace_on = p != nullptr;
     return 0;
 }
 
@@ -1160,9 +1176,10 @@ static int forward_small(const csb_gnn_dims* d, const PackTable& t, const uint8_
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
     if (!g_small_path || !coop || !ctrl || E <= 0 || steps < 1 || steps > 32 || te + tn > sms) return 0;
-    static unsigned long long configured = 0;
+    static unsigned long long configured = 0, configured_t = 0;
     const size_t smem = smem_bytes(EDGE, 0, LAT);
-    CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_small_kernel, 232448 - 1024, &configured));
+    CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_small_kernel<false>, 232448 - 1024, &configured));
+    if (g_trace_on) CSB_CUDA_TRY(opt_in_dynamic_smem(gnn_small_kernel<true>, 232448 - 1024, &configured_t));
     SmallArgs s{};
     Args a{};
     a.N = N;
@@ -1194,7 +1211,8 @@ static int forward_small(const csb_gnn_dims* d, const PackTable& t, const uint8_
     s.timeout_ns = 2000000000ull;  // 2 s: a forward takes well under a millisecond
     CSB_CUDA_TRY(cudaMemsetAsync(ctrl, 0, SMALL_CTRL_WORDS * sizeof(uint32_t), stream));
     void* kargs[] = {(void*)&s};
-    CSB_LAUNCH("gnn_small", stream, cudaLaunchCooperativeKernel((const void*)gnn_small_kernel, dim3(te + tn), dim3(THREADS), kargs, smem, stream));
+    const void* fn = g_trace_on ? (const void*)gnn_small_kernel<true> : (const void*)gnn_small_kernel<false>;
+    CSB_LAUNCH("gnn_small", stream, cudaLaunchCooperativeKernel(fn, dim3(te + tn), dim3(THREADS), kargs, smem, stream));
     return 1;
 }
 

@@ -1,4 +1,4 @@
-"""Station timeline of one CTA of the GNN forward (csb_debug_gnn_trace): python tools/gnn_trace.py [n] [block] [small]"""
+"""Station timeline of one CTA of the GNN forward (csb_debug_gnn_trace): python tools/gnn_trace.py [n] [block] [small] [graphs]"""
 import os
 import sys
 
@@ -13,9 +13,16 @@ from meshnet import EncodeProcessDecode  # noqa: E402
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 block = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 small = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+graphs = int(sys.argv[4]) if len(sys.argv) > 4 else 1
 lib = csb_cabi.lib()
 lib.csb_debug_gnn_small(small)
 x, ei, ef, _, _ = S.gnn_inputs(n, 4)
+if graphs > 1:  # disjoint-union batch of `graphs` copies
+    import numpy as np
+
+    N0 = x.shape[0]
+    x, ef = np.tile(x, (graphs, 1)), np.tile(ef, (graphs, 1))
+    ei = np.ascontiguousarray(np.concatenate([ei + g * N0 for g in range(graphs)], 1))
 torch.manual_seed(0)
 m = EncodeProcessDecode(8, 3, 4, 128, 15, 2, 128).eval().cuda()
 xt, eit, eft = torch.from_numpy(x).cuda(), torch.from_numpy(ei).cuda(), torch.from_numpy(ef).cuda()
