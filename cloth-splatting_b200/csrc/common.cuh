@@ -142,10 +142,13 @@ struct GeomState {
     static GeomState carve(void* ws, int V, int P);
 };
 
+constexpr int TILE_ORDER_HEAD = 513;
 struct ImageState {
     float* final_T;      // [V*H*W]
     uint32_t* n_contrib; // [V*H*W]
     uint2* ranges;       // [V*tiles]
+    uint32_t* tile_order; // [TILE_ORDER_HEAD + V*tiles]: word 0 = 1 when the ids behind the head list the (view, tile) pairs
+                          // longest list first; words 1..256 class histogram, 257..512 class cursors (build_tile_order)
     size_t bytes;
     static ImageState carve(void* ws, int V, int W, int H);
 };

@@ -646,11 +646,14 @@ using namespace csb;
 static int launch_render_backward(cudaStream_t stream, dim3 grid, const ViewBatch& vb, const uint2* ranges,
                                   const uint32_t* point_list, const float2* means2D, const float4* conic_opacity,
                                   const float4* rgb_depth, const float* final_T, const uint32_t* n_contrib,
-                                  const float* dL_dpix, float* grad_acc, int view0) {
+                                  const float* dL_dpix, float* grad_acc, int view0, const uint32_t* tile_order) {
+    // all views of the set in one launch: a 1-D grid over the (view, tile) pairs, composited longest list first when the
+    // forward left an order (render_lanes.cuh: tile_of_block); the per-view launches of the staged backward keep (x, y, 1)
+    const dim3 lgrid = tile_order ? dim3(grid.x * grid.y * grid.z) : grid;
 #define CSB_RB_LANES(NP, MINB, DELAY)                                                                                    \
     CSB_LAUNCH("render_backward", stream,                                                                                \
-               launch_pdl(render_backward_lanes_kernel<NP, MINB, DELAY>, grid, dim3(LaneTiling<NP>::THREADS), 0, stream, \
-                          vb, ranges, point_list, means2D, conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0))
+               launch_pdl(render_backward_lanes_kernel<NP, MINB, DELAY>, lgrid, dim3(LaneTiling<NP>::THREADS), 0, stream, \
+                          vb, ranges, point_list, means2D, conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0, tile_order))
     switch ((g_render_variant >> 4) & 15) {
         case 0:
             CSB_LAUNCH("render_backward", stream, launch_pdl(render_backward_kernel, grid, dim3(CSB_TILE_PIX), 0, stream, vb, ranges, point_list, means2D,
@@ -700,13 +703,13 @@ static int backward_impl(int num_views, const csb_view* views, int P, int D, int
             for (int v = 0; v < num_views; ++v) {
                 if (view_ready[v]) CSB_CUDA_TRY(cudaStreamWaitEvent(stream, (cudaEvent_t)view_ready[v], 0));
                 rc = launch_render_backward(stream, dim3(vb.gx, vb.gy, 1), vb, im.ranges, point_list, g.means2D, g.conic_opacity,
-                                            g.rgb_depth, im.final_T, im.n_contrib, dL_dpix, g.grad_acc, v);
+                                            g.rgb_depth, im.final_T, im.n_contrib, dL_dpix, g.grad_acc, v, nullptr);
                 if (rc) return rc;
             }
         } else {
             dim3 tgrid(vb.gx, vb.gy, num_views);
             rc = launch_render_backward(stream, tgrid, vb, im.ranges, point_list, g.means2D, g.conic_opacity, g.rgb_depth,
-                                        im.final_T, im.n_contrib, dL_dpix, g.grad_acc, 0);
+                                        im.final_T, im.n_contrib, dL_dpix, g.grad_acc, 0, im.tile_order);
             if (rc) return rc;
         }
     }

@@ -42,6 +42,7 @@ ImageState ImageState::carve(void* ws, int V, int W, int H) {
     s.final_T = c.take<float>(npix);
     s.n_contrib = c.take<uint32_t>(npix);
     s.ranges = c.take<uint2>(tiles);
+    s.tile_order = c.take<uint32_t>(tiles + TILE_ORDER_HEAD);
     s.bytes = c.total();
     return s;
 }
@@ -414,13 +415,87 @@ constexpr int CTRL_BIN_TICKET = CTRL_TICKET_DEPTH + 2;  // block ticket of bin_r
 
 // FILL = false: every (view, Gaussian) entry counts itself into the tiles of its rectangle.  FILL = true: the same walk claims a slot per tile and stores
 // (depth bits, entry) there.
+// Longest tile list first.  The compositing kernels give every tile a CTA and the hardware hands CTAs to the SMs in index
+// order, so the order of the indices IS the schedule: in image order the cloth's heavy tiles (lists of 100-220 entries in
+// a quarter of the tiles, the rest empty) arrive in clumps and the kernels end on a tail of half-empty SMs (ncu: achieved
+// occupancy 76-82 % of the theoretical one).  Sorted by descending list length the big tiles start first and the small
+// and empty ones fill the gaps -- the classic longest-processing-time rule, for the price of one indirection per CTA.
+// Counting sort of the tiles by length class (8 entries per class, class 0 = the longest lists): bin_ranges_kernel adds its
+// tiles to the 256-bin class histogram, extra blocks of the fill launch (one per 256 tiles, so they run beside the fill)
+// scan it and place their tiles with one cursor atomic each.
+__device__ __forceinline__ uint32_t tile_len_class(uint32_t len) { return 255u - min((len + 7u) >> 3, 255u); }
+
+__device__ void build_tile_order(const uint2* __restrict__ ranges, uint32_t n_tiles, uint32_t total, uint32_t* __restrict__ order,
+                                 uint32_t chunk, bool closed_ranges = false) {
+    __shared__ uint32_t s_base[256], s_warp[8];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // exclusive scan of the class histogram (256 bins, one per thread)
+    const uint32_t h = __ldcg(&order[1 + tid]);
+    uint32_t inc = h;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+        if (lane >= (uint32_t)o) inc += u;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t off = 0;
+    for (uint32_t w = 0; w < warp; ++w) off += s_warp[w];
+    s_base[tid] = off + inc - h;
+    __syncthreads();
+    const uint32_t t = chunk * 256u + tid;
+    uint32_t cls = 0xFFFFFFFFu;
+    if (t < n_tiles) {
+        // per-tile binning: only the starts are final while the fill runs; global path: finished (start, end) pairs
+        const uint32_t a = __ldcg(&ranges[t].x);
+        const uint32_t b = closed_ranges ? __ldcg(&ranges[t].y) : (t + 1 < n_tiles ? __ldcg(&ranges[t + 1].x) : total);
+        cls = tile_len_class(b - a);
+    }
+    // one cursor atomic per (warp, class): three quarters of a cloth frame's tiles share the class "empty"
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, cls);
+    const uint32_t leader = __ffs(peers) - 1;
+    uint32_t slot0 = 0;
+    if (lane == leader && t < n_tiles) slot0 = atomicAdd(&order[257 + cls], (uint32_t)__popc(peers));
+    slot0 = __shfl_sync(0xFFFFFFFFu, slot0, leader);
+    if (t < n_tiles) order[TILE_ORDER_HEAD + s_base[cls] + slot0 + __popc(peers & ((1u << lane) - 1u))] = t;
+    if (chunk == 0 && tid == 0) order[0] = 1u;  // the consumers start after this whole grid has finished
+}
+
+// The same order for the global sort path, where the ranges come from tile_ranges_kernel: two small launches behind it
+// (class histogram; scan + placement).
+__global__ void __launch_bounds__(256)
+tile_order_hist_kernel(const uint2* __restrict__ ranges, uint32_t n_tiles, uint32_t* __restrict__ order) {
+    grid_dep_wait();
+    grid_dep_launch();
+    const uint32_t t = blockIdx.x * 256u + threadIdx.x, lane = threadIdx.x & 31;
+    uint32_t cls = 0xFFFFFFFFu;
+    if (t < n_tiles) {
+        const uint2 r = ranges[t];
+        cls = tile_len_class(r.y - r.x);
+    }
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, cls);
+    if (lane == (uint32_t)__ffs(peers) - 1u && t < n_tiles) atomicAdd(&order[1 + cls], (uint32_t)__popc(peers));
+}
+__global__ void __launch_bounds__(256)
+tile_order_place_kernel(const uint2* __restrict__ ranges, uint32_t n_tiles, uint32_t* __restrict__ order) {
+    grid_dep_wait();
+    grid_dep_launch();
+    build_tile_order(ranges, n_tiles, 0u, order, blockIdx.x, true);
+}
+
 template <bool FILL>
 __global__ void __launch_bounds__(256)
 bin_entries_kernel(const ViewBatch vb, GeomState g, uint2* __restrict__ ranges, uint32_t* __restrict__ groups,
-                   uint32_t* __restrict__ fill_depth, uint32_t* __restrict__ fill_vals) {
+                   uint32_t* __restrict__ fill_depth, uint32_t* __restrict__ fill_vals, uint32_t* __restrict__ tile_order) {
     grid_dep_wait();
     grid_dep_launch();
     if (FILL && g.control[CTRL_OVERFLOW]) return;
+    const uint32_t entry_blocks = (uint32_t)(((size_t)vb.V * vb.P + 255) / 256);
+    if (FILL && tile_order && blockIdx.x >= entry_blocks) {  // the extra blocks: no entries of their own
+        build_tile_order(ranges, (uint32_t)vb.V * (uint32_t)vb.tiles, g.control[CTRL_NUM_RENDERED], tile_order,
+                         blockIdx.x - entry_blocks);
+        return;
+    }
     const size_t n = (size_t)vb.V * vb.P;
     const size_t j = (size_t)blockIdx.x * 256 + threadIdx.x;
     const uint32_t cnt = j < n ? g.tiles_touched[j] : 0u;
@@ -473,7 +548,7 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
 __global__ void __launch_bounds__(256)
 bin_ranges_kernel(uint2* __restrict__ ranges, uint32_t* __restrict__ status, uint32_t n_tiles, size_t capacity,
                   uint32_t* __restrict__ control, uint32_t* __restrict__ num_rendered_out,
-                  uint32_t* num_rendered_mapped) {
+                  uint32_t* num_rendered_mapped, uint32_t* __restrict__ tile_order) {
     __shared__ uint32_t s_warp[8];
     __shared__ uint32_t s_blk, s_excl;
     grid_dep_wait();
@@ -484,6 +559,11 @@ bin_ranges_kernel(uint2* __restrict__ ranges, uint32_t* __restrict__ status, uin
     const uint32_t blk = s_blk;
     const uint32_t t = blk * 256u + tid;
     const uint32_t c = t < n_tiles ? __ldcg(&ranges[t].y) : 0u;
+    if (tile_order) {  // class histogram of build_tile_order, one atomic per (warp, class)
+        const uint32_t cls = t < n_tiles ? tile_len_class(c) : 0xFFFFFFFFu;
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, cls);
+        if (lane == (uint32_t)__ffs(peers) - 1u && t < n_tiles) atomicAdd(&tile_order[1 + cls], (uint32_t)__popc(peers));
+    }
     uint32_t incl = c, mx = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -799,7 +879,7 @@ using namespace csb;
 static int launch_render_forward(cudaStream_t stream, dim3 tgrid, const ViewBatch& vb, const uint2* ranges,
                                  const uint32_t* point_list, const float2* means2D, const float4* conic_opacity,
                                  const float4* rgb_depth, float* final_T, uint32_t* n_contrib, float* out_color,
-                                 float* out_depth, bool long_lists) {
+                                 float* out_depth, bool long_lists, const uint32_t* tile_order) {
     // 15 = by path (measured on B200, profiles/r2_summary.md): cloth-sized scenes on the per-tile binning path (small
     // footprints, ~30 entries per tile) run fastest with one pixel pair per lane (8x8 pixels per warp: finer culling), the
     // global sort path (C3 / C4: footprints of many tiles, thousands of entries per tile) with two pairs per lane
@@ -811,12 +891,12 @@ static int launch_render_forward(cudaStream_t stream, dim3 tgrid, const ViewBatc
                                                             conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
             break;
         case 3:
-            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_packed_kernel<1>, tgrid, dim3(LaneTiling<1>::THREADS), 0, stream, vb, ranges, point_list,
-                                                            means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_packed_kernel<1>, dim3(tgrid.x * tgrid.y * tgrid.z), dim3(LaneTiling<1>::THREADS), 0, stream, vb, ranges, point_list,
+                                                            means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth, tile_order));
             break;
         case 4:
-            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_packed_kernel<2>, tgrid, dim3(LaneTiling<2>::THREADS), 0, stream, vb, ranges, point_list,
-                                                            means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth));
+            CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_packed_kernel<2>, dim3(tgrid.x * tgrid.y * tgrid.z), dim3(LaneTiling<2>::THREADS), 0, stream, vb, ranges, point_list,
+                                                            means2D, conic_opacity, rgb_depth, final_T, n_contrib, out_color, out_depth, tile_order));
             break;
         case 2:
             CSB_LAUNCH("render_forward", stream, launch_pdl(render_forward_lanes_kernel<2>, tgrid, dim3(LaneTiling<2>::THREADS), 0, stream, vb, ranges, point_list,
@@ -872,6 +952,7 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
     const bool early_count = (flags & 2) && num_rendered_host && n > 0;
     CSB_CUDA_TRY(cudaMemsetAsync(g.control, 0, g.control_words * sizeof(uint32_t), stream));
     CSB_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, total_tiles * sizeof(uint2), stream));
+    CSB_CUDA_TRY(cudaMemsetAsync(im.tile_order, 0, TILE_ORDER_HEAD * sizeof(uint32_t), stream));  // "no order" + histogram + cursors
     // all memsets first: the kernels behind them form one programmatic-dependent-launch chain
     if (n > 0 && binning_capacity > 0) {
         // global path: look-back words of the tile sort; per-tile path (flags bit2): the status words of its scan
@@ -904,13 +985,14 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             uint32_t* groups = b.lookback;  // status words of the chained scan: free in this path; zeroed above
             // (the per-tile counts were made by preprocess_kernel)
             CSB_LAUNCH("bin_ranges", stream, launch_pdl(bin_ranges_kernel, dim3(sblocks_scan), dim3(256), 0, stream, im.ranges, groups,
-                                                         (uint32_t)total_tiles, binning_capacity, g.control, num_rendered_dev, mapped));
-            CSB_LAUNCH("bin_fill", stream, launch_pdl(bin_entries_kernel<true>, dim3(blocks), dim3(256), 0, stream, vb, g, im.ranges, groups, fill_d, fill_v));
+                                                         (uint32_t)total_tiles, binning_capacity, g.control, num_rendered_dev, mapped, im.tile_order));
+            CSB_LAUNCH("bin_fill", stream, launch_pdl(bin_entries_kernel<true>, dim3(blocks + sblocks_scan), dim3(256), 0, stream, vb, g, im.ranges, groups, fill_d, fill_v,
+                                                       im.tile_order));
             const unsigned sblocks = (unsigned)std::min<size_t>(total_tiles, 148 * 8);
             CSB_LAUNCH("bin_sort", stream, launch_pdl(bin_sort_kernel, dim3(sblocks), dim3(256), 0, stream, im.ranges, (const uint32_t*)g.control,
                                                        (uint32_t)total_tiles, (const uint32_t*)fill_d, (const uint32_t*)fill_v, st, sv,
                                                        (flags & 1) ? b.keys : nullptr));
-            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, false);
+            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, false, im.tile_order);
             if (rc) return rc;
             if (num_rendered_host && !early_count)
                 CSB_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, num_rendered_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost,
@@ -946,13 +1028,18 @@ int csb_rasterize_forward(int num_views, const csb_view* views, int P, int D, in
             CSB_LAUNCH("tile_ranges", stream, launch_pdl(tile_ranges_kernel, dim3(rblocks), dim3(256), 0, stream, g.control + CTRL_NUM_RENDERED, st, sv, g.rgb_depth,
                                                             im.ranges, (flags & 1) ? b.keys : nullptr,
                                                             (uint32_t)vb.tiles));
-            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, true);
+            {   // longest list first (build_tile_order): the big tiles of a view set start first, the small ones fill the tail
+                const unsigned oblocks = (unsigned)((total_tiles + 255) / 256);
+                CSB_LAUNCH("tile_order", stream, launch_pdl(tile_order_hist_kernel, dim3(oblocks), dim3(256), 0, stream, (const uint2*)im.ranges, (uint32_t)total_tiles, im.tile_order));
+                CSB_LAUNCH("tile_order", stream, launch_pdl(tile_order_place_kernel, dim3(oblocks), dim3(256), 0, stream, (const uint2*)im.ranges, (uint32_t)total_tiles, im.tile_order));
+            }
+            rc = launch_render_forward(stream, tgrid, vb, im.ranges, sv, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, true, im.tile_order);
             if (rc) return rc;
             if (tside != sorted_side(total_tiles)) return CSB_ERR_UNSUPPORTED;  // consumers recompute the side
         }
     } else {
         CSB_CUDA_TRY(cudaMemsetAsync(num_rendered_dev, 0, sizeof(uint32_t), stream));
-        rc = launch_render_forward(stream, tgrid, vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, true);
+        rc = launch_render_forward(stream, tgrid, vb, im.ranges, b.vals_a, g.means2D, g.conic_opacity, g.rgb_depth, im.final_T, im.n_contrib, out_color, out_depth, true, im.tile_order);
         if (rc) return rc;
     }
     if (num_rendered_host && !early_count)

@@ -66,7 +66,10 @@ def test_variants_agree():
             assert torch.equal(res[v][3], res[0][3]), f"{name}: final_T of variant {v}"
             for k in ("means2D", "means3D", "opacities", "shs", "scales", "rotations", "cov3D"):
                 rel = Hh.rel_err(res[v][4][k].cpu().numpy(), res[0][4][k].cpu().numpy())
-                assert rel < (3e-4 if k == "cov3D" else 1e-4), f"{name}: grad {k} of variant {v}: rel {rel}"
+                # dL/dcov3D collects float atomics in a run-dependent order (two runs of the reference itself differ by ~1e-4
+                # there); dL/dscales and dL/drotations are linear images of it and inherit that spread (measured between two
+                # variants, run to run: 0.3 .. 1.13e-4)
+                assert rel < (3e-4 if k in ("cov3D", "scales", "rotations") else 1e-4), f"{name}: grad {k} of variant {v}: rel {rel}"
 
 
 @pytest.mark.parametrize("v", [0x00, 0x22, 0x43, 0x64])  # the default variant is what every other test runs
