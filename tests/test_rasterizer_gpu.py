@@ -132,8 +132,9 @@ def _compare_with_reference(g, cam, sh_degree=3, bg=(1.0, 1.0, 1.0)):
     # gradients
     dl = torch.from_numpy(S.pixel_grad(1, H, W)).cuda()
     g_ref = {k: (v.clone() if v is not None else None) for k, v in ref.backward(dl[0]).items()}
-    # the reference accumulates with float atomics: its own run-to-run spread is part of the budget
-    g_ref2 = ref.backward(dl[0])
+    # the reference accumulates with float atomics: its own run-to-run spread is part of the budget.  One extra run is a
+    # noisy estimate of that spread (it made this test fail about once in 35 runs): the largest of three is used.
+    g_refs = [{k: (v.clone() if v is not None else None) for k, v in ref.backward(dl[0]).items()} for _ in range(3)]
     got = Hh.product_backward(gc, cam, views, fwd, dl, sh_degree)
     for k in ("means2D", "opacities", "means3D", "cov3D", "shs", "scales", "rotations", "colors"):
         if g_ref.get(k) is None or got[k].numel() == 0:
@@ -144,7 +145,7 @@ def _compare_with_reference(g, cam, sh_degree=3, bg=(1.0, 1.0, 1.0)):
             continue
         a = got[k][0] if k == "means2D" else got[k]
         rel = Hh.rel_err(a.cpu().numpy(), g_ref[k].cpu().numpy())
-        spread = Hh.rel_err(g_ref2[k].cpu().numpy(), g_ref[k].cpu().numpy())
+        spread = max(Hh.rel_err(r[k].cpu().numpy(), g_ref[k].cpu().numpy()) for r in g_refs)
         # two runs of the reference differ by up to ~5e-4 on the intermediate dL/dcov3D (float atomics over heavily
         # cancelling terms; measured 1.0e-4 .. 4.8e-4 over repeated runs): the spread is budget, capped so that a
         # broken reference build cannot hide a real error

@@ -1,1 +1,1 @@
-for i in 1 2 3 4 5 6 7 8; do timeout 600 python -m pytest tests/test_rasterizer_gpu.py tests/test_render_variants_gpu.py -q --timeout 600 -x 2>&1 | grep -E "^E  |passed|failed" | cut -c1-400 | head -12; done
+for i in $(seq 1 14); do timeout 600 python -m pytest tests/test_rasterizer_gpu.py -q --timeout 600 -x 2>&1 | grep -E "^E  |passed|failed|Error" | cut -c1-400 | head -12; done
