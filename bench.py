@@ -643,6 +643,8 @@ def run_b200(args, rank, world, dev):
     except Exception:
         pass
     roofline["traffic"] = traffic
+    if traffic is not None:
+        roofline["traffic_source"] = "profiles/r2_traffic.json: dram bytes read + written per launch in the committed ncu --set full capture of this command"
     roofline["fp32_peaks"] = fp32
 
     line = {

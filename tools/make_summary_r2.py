@@ -196,4 +196,22 @@ for src, dst in (("r2z_bench.json", "r2_bench_1gpu.json"), ("r2z_ref.json", "r2_
                  ("r2z_fwd_mix.txt", "r2_mix_render_forward.txt"), ("r2z_bwd_mix.txt", "r2_mix_render_backward.txt"),
                  ("r2k_sanitizer_memcheck.log", "r2_sanitizer_unavailable.log"), ("r2z_tests.log", "r2_gpu_tests.log"), ("r2r_bench_2gpu.json", "r2_bench_2gpu.json")):
     keep(src, dst)
+# DRAM traffic per launch (dram__bytes_read.sum + dram__bytes_write.sum of the ncu --set full captures) for bench.py's roofline.traffic
+NAMES = {"preprocess_kernel": "preprocess", "bin_ranges_kernel": "bin_ranges", "bin_entries_kernel<1>": "bin_fill", "bin_sort_kernel": "bin_sort",
+         "render_forward": "render_forward", "render_backward": "render_backward", "gaussian_backward": "gaussian_backward", "emit_kernel": "emit",
+         "tile_ranges_kernel": "tile_ranges"}
+traffic = {}
+for wl, f in (("c2", "r2z_ncu_c2_table.json"), ("c3", "r2z_ncu_c3_table.json")):
+    path = os.path.join(G, f)
+    if not os.path.exists(path):
+        continue
+    acc = {}
+    for row in json.load(open(path)):
+        for pre, name in NAMES.items():
+            if row["kernel"].startswith(pre) and row.get("rd MB") is not None:
+                acc.setdefault(name, []).append((row["rd MB"] + row["wr MB"]) * 1e6)
+    traffic[wl] = {k: max(v) for k, v in acc.items()}  # the launch of the timed step (warm-up launches of a kernel may be smaller)
+if traffic:
+    traffic["how"] = "ncu --set full --clock-control none of `bench.py --steps 2 --warmup 1` (tools/gpu_run19.sh): dram__bytes_read.sum + dram__bytes_write.sum per launch"
+    json.dump(traffic, open(os.path.join(P, "r2_traffic.json"), "w"), indent=1)
 print(open(os.path.join(P, "r2_summary.md")).read()[:3000])
