@@ -84,6 +84,9 @@ def var(v, wl, key):
 for i in range(5):
     f, bk = rows_f[i], rows_b[i]
     A(f"| {f[0]} | {var(f[1], 'c2', 'render_forward')} | {var(f[1], 'c3', 'render_forward')} | | {bk[0]} | {var(bk[1], 'c2', 'render_backward')} | {var(bk[1], 'c3', 'render_backward')} |")
+A("\n(The A/B above was taken before the tiles were scheduled longest list first; with that order the defaults are forward "
+  f"{b['kernels']['render_forward']['ms_per_step'] * 1e3:.1f} / backward {b['kernels']['render_backward']['ms_per_step'] * 1e3:.1f} us per C2 step, "
+  "and a repeat of the backward A/B still picks variant 4: 133.1 us against 137.4 (1), 142.0 (3), 141.9 (5), 147.7 (6).)")
 A("\nAll forward generations produce bit-identical images, depth, `final_T` and `n_contrib` (`tests/test_render_variants_gpu.py`); ncu: the "
   "branchy multi-pixel kernels execute the SAME number of warp instructions as the one-pixel kernel (67-68 M per C2 step: each pixel's "
   "branch is walked separately), the branch-free packed kernel 55.2 M.\n")
