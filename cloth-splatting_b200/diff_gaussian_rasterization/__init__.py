@@ -38,6 +38,8 @@ _RING = 64
 _COUNT_REFUSED = 0xFFFFFFFD  # per-tile binning refused: a tile list exceeds the per-tile sort's shared memory
 _small_bins = {}
 _ring_next = {}
+_ring_owner = {}         # (device, slot) -> weakref of the PendingCount that still has to read the slot's word
+_ring_slot_of_word = {}  # data_ptr of a ring word -> (device, slot)
 
 
 _reserved_words = []  # pinned words handed out next (set by reserve_count_words for a CUDA-graph capture)
@@ -63,6 +65,13 @@ def _pinned_word(device):
         _pinned_counter[device] = t
     i = _ring_next.get(device, 0)
     _ring_next[device] = (i + 1) % _RING
+    owner = _ring_owner.get((device, i))
+    owner = owner() if owner is not None else None
+    if owner is not None and owner.value is None:
+        # more than _RING deferred counts in flight: the slot's previous forward has not been read yet -- it keeps its word,
+        # this call gets a fresh one (pinned allocation: slow, but correct)
+        return torch.full((1,), -1, dtype=torch.int32).pin_memory()
+    _ring_slot_of_word[t[i:i + 1].data_ptr()] = (device, i)
     return t[i:i + 1]
 
 
@@ -96,6 +105,11 @@ class PendingCount:
     def __init__(self, word, stream, capacity, key, small, n_tiles):
         self.word, self.stream, self.capacity, self.key, self.small, self.n_tiles = word, stream, capacity, key, small, n_tiles
         self.value = None
+        slot = _ring_slot_of_word.get(word.data_ptr())
+        if slot is not None:
+            import weakref
+
+            _ring_owner[slot] = weakref.ref(self)
 
     def wait(self):
         if self.value is None:
@@ -156,8 +170,25 @@ def _views_array(views):
     return arr, keep
 
 
-def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
-                   image_height, image_width, sh, degree, prefiltered, flags=0, defer_count=False):
+def _on_device_of(t, fn, *args, **kwargs):
+    """Runs `fn` with the CUDA device of tensor `t` current (the C-ABI launches on the current device's stream and sets
+    per-device kernel attributes): a process that renders on cuda:1 while cuda:0 is current must not launch there."""
+    if t.is_cuda and t.device.index is not None and torch.cuda.current_device() != t.device.index:
+        with torch.cuda.device(t.device):
+            return fn(*args, **kwargs)
+    return fn(*args, **kwargs)
+
+
+def _forward_views(views, means3D, *args, **kwargs):
+    return _on_device_of(means3D, _forward_views_impl, views, means3D, *args, **kwargs)
+
+
+def _backward_views(views, means3D, *args, **kwargs):
+    return _on_device_of(means3D, _backward_views_impl, views, means3D, *args, **kwargs)
+
+
+def _forward_views_impl(views, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        image_height, image_width, sh, degree, prefiltered, flags=0, defer_count=False):
     """Shared implementation: returns (rendered, color[V,3,H,W], depth[V,1,H,W], radii[V,P], geom, binning, img).
     `defer_count=True` returns a `PendingCount` instead of the int and does not touch the host word: the caller goes
     on enqueueing (the backward pass does not need the count) and calls `.wait()` when convenient; an overflow of the
@@ -244,8 +275,8 @@ def _forward_views(views, means3D, colors, opacity, scales, rotations, scale_mod
     return rendered, out_color, out_depth, radii, geom, binning, img
 
 
-def _backward_views(views, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, image_height,
-                    image_width, dL_dout_color, sh, degree, geom, binning, img, out=None, view_events=None):
+def _backward_views_impl(views, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, image_height,
+                         image_width, dL_dout_color, sh, degree, geom, binning, img, out=None, view_events=None):
     """`out`: optional dict of preallocated contiguous fp32 CUDA tensors ("means3D" [P,3], "scales" [P,3], "rotations"
     [P,4], "opacities" [P,1], "shs" [P,M,3]) the kernels write these gradients into -- e.g. views of the flat
     all-reduce bucket (csb_dist.FlatGradBucket), which saves the pack copies.
