@@ -242,18 +242,33 @@ __device__ __forceinline__ void stage_records_in(const float* __restrict__ src, 
                                                  int tid, int nthr) {
     const int rec = REC > 0 ? REC : rec_rt, pitch = rec + 1, total = count * rec;
     const bool vec = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
-    for (int i = tid * 4; i < total; i += nthr * 4) {
-        float v[4] = {0.f, 0.f, 0.f, 0.f};
-        if (vec && i + 3 < total) {
-            const float4 q = *reinterpret_cast<const float4*>(src + i);
-            v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
-        } else {
-            for (int j = 0; j < 4 && i + j < total; ++j) v[j] = src[i + j];
+    // Six 16-byte loads of a thread are in flight before the first of their words is stored: one iteration at a time
+    // (load, four dependent stores, next load) this copy was twelve serial memory round trips -- a fifth of the stall
+    // samples of preprocess_kernel at cloth size (ncu source page: 206 of 923 on the STS).
+    constexpr int U = 6;
+    for (int base = tid * 4; base < total; base += nthr * 4 * U) {
+        float v[U][4];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * nthr * 4;
+            v[u][0] = v[u][1] = v[u][2] = v[u][3] = 0.f;
+            if (i < total) {
+                if (vec && i + 3 < total) {
+                    const float4 q = *reinterpret_cast<const float4*>(src + i);
+                    v[u][0] = q.x; v[u][1] = q.y; v[u][2] = q.z; v[u][3] = q.w;
+                } else {
+                    for (int j = 0; j < 4 && i + j < total; ++j) v[u][j] = src[i + j];
+                }
+            }
         }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int f = i + j;
-            if (f < total) s_rows[(f / rec) * pitch + (f % rec)] = v[j];
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * nthr * 4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int f = i + j;
+                if (f < total) s_rows[(f / rec) * pitch + (f % rec)] = v[u][j];
+            }
         }
     }
 }
