@@ -63,6 +63,7 @@ const char* csb_error_string(int code) {
         case CSB_ERR_BAD_ARG: return "bad argument";
         case CSB_ERR_WORKSPACE: return "workspace too small";
         case CSB_ERR_UNSUPPORTED: return "unsupported configuration";
+        case CSB_ERR_STATIC_LIMIT: return "problem exceeds the fixed scratch array of this no-allocation entry point (use the workspace variant)";
         default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
     }
 }

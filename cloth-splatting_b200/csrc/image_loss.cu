@@ -481,6 +481,64 @@ int csb_image_loss_forward(int n_img, int C, int H, int W, const float* img, con
     return 0;
 }
 
+// ---- csb_image_loss_forward_static: the same two kernels, partial sums in a library-owned array ----------------
+// For callers that cannot allocate (stream capture, serving loops): no cudaMalloc / cudaFree / allocating routine
+// anywhere below.  Every device that loads the library holds CSB_IMAGE_LOSS_STATIC_BYTES of it until exit.
+}  // extern "C"
+
+static __device__ __align__(256) unsigned char g_loss_static_partials[CSB_IMAGE_LOSS_STATIC_BYTES];
+
+// In host code the array's name is a host-side stand-in, not a device address; the device address is looked up
+// once per device (with that device current) and kept.
+static int loss_static_scratch(float** out) {
+    constexpr int MAX_DEV = 64;
+    static float* cached[MAX_DEV] = {};
+    int dev = 0;
+    CSB_CUDA_TRY(cudaGetDevice(&dev));
+    float* p = (dev >= 0 && dev < MAX_DEV) ? __atomic_load_n(&cached[dev], __ATOMIC_ACQUIRE) : nullptr;
+    if (!p) {
+        void* sym = nullptr;
+        CSB_CUDA_TRY(cudaGetSymbolAddress(&sym, g_loss_static_partials));
+        if (!sym) return CSB_ERR_UNSUPPORTED;
+        p = (float*)sym;
+        if (dev >= 0 && dev < MAX_DEV) __atomic_store_n(&cached[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return 0;
+}
+
+extern "C" {
+
+size_t csb_image_loss_static_max_bytes(void) { return CSB_IMAGE_LOSS_STATIC_BYTES; }
+
+int csb_image_loss_forward_static(int n_img, int C, int H, int W, const float* img, const float* gt,
+                                  const float* mask, int mask_channels, float lambda_dssim, float* ssim_map,
+                                  float* dmaps, float* losses, void* stream_) {
+    LossShape s;
+    if (!make_shape(s, n_img, C, H, W, mask_channels, mask != nullptr)) return CSB_ERR_BAD_ARG;
+    if (n_img == 0) return CSB_ERR_BAD_ARG;
+    if (!img || !gt || !losses) return CSB_ERR_BAD_ARG;
+    if (s.planes > 65535) return CSB_ERR_UNSUPPORTED;
+    const size_t blocks = (size_t)s.tiles_x * s.tiles_y * s.planes;
+    if (blocks * 2 * sizeof(float) > CSB_IMAGE_LOSS_STATIC_BYTES) return CSB_ERR_STATIC_LIMIT;
+    float* partials = nullptr;
+    const int rc = loss_static_scratch(&partials);
+    if (rc) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const dim3 grid(s.tiles_x * s.tiles_y, s.planes);
+    const LossWindow win = make_window();
+    // every block of the forward kernel overwrites its own two partials and the fold reads exactly `blocks` of them:
+    // nothing of the previous call's contents is read, so the shared array needs no clearing between calls
+    auto kernel = ssim_map ? (dmaps ? image_loss_forward_kernel<true, true> : image_loss_forward_kernel<true, false>)
+                           : (dmaps ? image_loss_forward_kernel<false, true> : image_loss_forward_kernel<false, false>);
+    CSB_LAUNCH("image_loss_forward", stream, kernel<<<grid, 256, 0, stream>>>(
+        s, win, img, gt, mask, ssim_map, dmaps, partials));
+    const double inv_count = 1.0 / ((double)s.planes * H * W);
+    CSB_LAUNCH("image_loss_finalize", stream, image_loss_finalize_kernel<<<1, 256, 0, stream>>>(
+        blocks, inv_count, lambda_dssim, (const float*)partials, losses));
+    return 0;
+}
+
 int csb_image_loss_backward(int n_img, int C, int H, int W, const float* img, const float* gt, const float* mask,
                             int mask_channels, const float* dmaps, const float* grad_map, const float* grad_scale,
                             float w_ssim, float w_l1, float* dL_dimg, void* stream_) {

@@ -38,6 +38,7 @@ extern "C" {
 #define CSB_ERR_BAD_ARG (-1)
 #define CSB_ERR_WORKSPACE (-2) /* a caller-provided workspace is too small */
 #define CSB_ERR_UNSUPPORTED (-3)
+#define CSB_ERR_STATIC_LIMIT (-4) /* the problem needs more scratch than a no-allocation entry point's fixed array */
 
 #define CSB_MAX_VIEWS 16 /* views rendered by one launch set */
 
@@ -315,6 +316,22 @@ size_t csb_image_loss_workspace_bytes(int n_img, int C, int H, int W);
 int csb_image_loss_forward(int n_img, int C, int H, int W, const float* img, const float* gt, const float* mask,
                            int mask_channels, float lambda_dssim, float* ssim_map, float* dmaps, float* losses,
                            void* workspace, size_t workspace_bytes, void* stream);
+/* csb_image_loss_forward without a caller workspace and without any allocation.  No counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, kernels and results as csb_image_loss_forward (bitwise:
+ * the per-tile partial sums are folded in the same fixed order); the partial sums live in a file-scope
+ * `static __device__` array of CSB_IMAGE_LOSS_STATIC_BYTES that every GPU loading the library holds until exit.
+ * Limit: n_img * C * ceil(W/32) * ceil(H/32) <= CSB_IMAGE_LOSS_STATIC_BYTES / 8 = 131072 tiles (e.g. 16 RGB images of
+ * 1664x1664, or the 4 x 3 x 800 x 800 batch of the refinement step 17 times over); beyond it the call launches
+ * nothing and returns CSB_ERR_STATIC_LIMIT.  The device that owns `stream` must be current.  All calls (on one
+ * device) share the array: it keeps the last call's partial sums, nothing in it has to start at zero (every tile of
+ * a call overwrites its own slot before the fold reads it), and two calls that overlap on the GPU (different streams,
+ * no ordering between them) race on it -- serialise them or use csb_image_loss_forward with separate workspaces. */
+#define CSB_IMAGE_LOSS_STATIC_BYTES (1u << 20)
+size_t csb_image_loss_static_max_bytes(void);
+int csb_image_loss_forward_static(int n_img, int C, int H, int W, const float* img, const float* gt,
+                                  const float* mask, int mask_channels, float lambda_dssim, float* ssim_map,
+                                  float* dmaps, float* losses, void* stream);
 /* dL/dimg f32[n_img, C, H, W] of  L = scale * (w_l1 * sum |(img - gt) mask| + sum_q g(q) S(q)),
  *   g(q) = grad_map[q] if grad_map != NULL (autograd through a returned ssim_map) else w_ssim * mask(q);
  * scale = *grad_scale, a DEVICE scalar (the upstream gradient of the loss; NULL = 1) so that no host
