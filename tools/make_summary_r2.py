@@ -73,12 +73,17 @@ rows_b = [("0: one pixel per lane (round 1)", "0x00"), ("1: pixel pair per lane"
           ("4: pixel pair, delayed reduction (default)", "0x40"), ("6: two pairs, delayed reduction", "0x60")]
 
 
+AB_PATH = os.path.join(P, "r2_variants_ab.json")   # the A/B runs' outputs are scratch; their numbers are kept here
+AB = json.load(open(AB_PATH))["us_per_step"] if os.path.exists(AB_PATH) else {}
+
+
 def var(v, wl, key):
     for pre in ("r2j", "r2i"):
         d = load(f"{pre}_{wl}_v{v}.json")
         if d:
             return f"{d['kernels'][key]['ms_per_step'] * 1e3:.1f}"
-    return "-"
+    kept = AB.get(("fwd" + v[3]) if key == "render_forward" else ("bwd" + v[2]))
+    return kept[wl] if kept else "-"
 
 
 for i in range(5):
@@ -150,6 +155,10 @@ if d and rd:
 
 scal = {n: load(f"r2s_scale_n{n}.json") for n in (1, 2, 4, 8)}
 scal = {n: v for n, v in scal.items() if v}
+SCAL_PATH = os.path.join(P, "r2_scaling.json")
+scal_fresh = bool(scal)
+if not scal and os.path.exists(SCAL_PATH):     # the 8-GPU run's outputs are scratch; its reduced lines are kept in profiles/
+    scal = {int(n): dict(v, gnn={"train_c5": v.get("gnn_train_c5")}) for n, v in json.load(open(SCAL_PATH)).items()}
 if len(scal) > 1 and 1 in scal:
     A("## 1 -> 8 GPUs on one box (default `bench.py` command at every N)\n")
     A("| GPUs | C2 weak (4 views/GPU) Mpix/s | ms/step | efficiency | e2e Mpix/s | all-reduce: wait for peers / reduce+push / depart (us) | C4 strong (64 views total) ms/step | speed-up / efficiency | C5 training graphs/s (128 graphs/GPU) |\n|---|---|---|---|---|---|---|---|---|")
@@ -162,8 +171,11 @@ if len(scal) > 1 and 1 in scal:
         gt = f"{tr['graphs_per_s']:.0f} ({100 * tr['graphs_per_s'] / (n * tr1['graphs_per_s']):.0f} %)" if tr and tr1 else "-"
         A(f"| {n} | {v['value']:.0f} | {v['ms_per_step']:.4f} | {100 * v['value'] / (n * scal[1]['value']):.1f} % | {v['e2e']['value']:.0f} | {ph} | {c4s} | {gt} |")
     A("")
+    if not scal_fresh:
+        A("(Scaling run of commit 2d6163a, before the SH staging change that took C3 from 1.96 to 1.89 ms; C2 is unaffected.)\n")
+if scal_fresh:
     json.dump({str(n): {kk: v.get(kk) for kk in ("value", "ms_per_step", "n_gpus", "e2e", "allreduce", "step_ms_spread", "config", "clocks", "c4")} |
-               {"gnn_train_c5": (v.get("gnn") or {}).get("train_c5")} for n, v in scal.items()}, open(os.path.join(P, "r2_scaling.json"), "w"), indent=1)
+               {"gnn_train_c5": (v.get("gnn") or {}).get("train_c5")} for n, v in scal.items()}, open(SCAL_PATH, "w"), indent=1)
 g2 = load("r2r_bench_2gpu.json")
 if g2 and 2 not in scal:
     A(f"2-GPU check (`tools/gpu_run18.sh`): C2 {g2['value']:.0f} Mpix/s ({g2['ms_per_step']:.4f} ms/step), C4 strong {g2['c4']['ms_per_step']:.2f} ms/step "
