@@ -60,3 +60,23 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(root, f), errors="ignore").read()
                 assert not re.search(r"^\s*(import|from)\s+oracle\b", src, flags=re.M), f
                 assert "liboracle" not in src and "libref_cuda" not in src, f
+
+
+def test_static_scratch_entry_point_refuses_oversize_without_touching_the_gpu():
+    """csb_image_loss_forward_static checks its fixed 1 MiB array before any CUDA call: an oversize request is refused on
+    a machine without a GPU too (the GPU parity test is tests/test_zz_no_alloc.py)."""
+    import csb_cabi
+
+    lib = csb_cabi.lib()
+    c_int, c_void_p, c_float = ctypes.c_int, ctypes.c_void_p, ctypes.c_float
+    lib.csb_image_loss_forward_static.restype = c_int
+    lib.csb_image_loss_forward_static.argtypes = [c_int] * 4 + [c_void_p] * 3 + [c_int, c_float] + [c_void_p] * 3 + [c_void_p]
+    lib.csb_image_loss_static_max_bytes.restype = ctypes.c_size_t
+    assert lib.csb_image_loss_static_max_bytes() == 1 << 20
+    dummy = ctypes.create_string_buffer(16)                      # never dereferenced: the size check comes first
+    p = ctypes.addressof(dummy)
+    # 16 x 91 x 91 tiles of 32 x 32 = 132 496 > 131 072
+    assert lib.csb_image_loss_forward_static(16, 1, 2900, 2900, p, p, None, 0, 0.2, None, None, p, None) == -4
+    assert b"no-allocation" in lib.csb_error_string(-4)
+    assert lib.csb_image_loss_forward_static(1, 3, 64, 64, None, p, None, 0, 0.2, None, None, p, None) == -1   # NULL image
+    assert lib.csb_image_loss_forward_static(1, 3, 0, 64, p, p, None, 0, 0.2, None, None, p, None) == -1      # empty plane
