@@ -620,6 +620,8 @@ def run_b200(args, rank, world, dev):
     lib = csb_cabi.lib()
     if args.render_variant >= 0:
         lib.csb_debug_render_variant(args.render_variant)
+    if args.cull_exact >= 0:
+        lib.csb_debug_cull_exact(args.cull_exact)
     peaks = load_peaks()
     fp32 = fp32_peaks(dev)
     flush = l2_flusher(dev)
@@ -661,7 +663,7 @@ def run_b200(args, rank, world, dev):
                 "api": "diff_gaussian_rasterization.rasterize_views + autograd backward"
                        + " (dL/dpixel uploaded and consumed view by view: StagedPixelGrads / backward_staged)"},
         "gpu_launches": main["launches"], "clocks": clocks, "roofline": roofline, "kernels": kernels,
-        "impl": "b200", "render_variant": int(lib.csb_debug_render_variant(-1)),
+        "impl": "b200", "render_variant": int(lib.csb_debug_render_variant(-1)), "cull_exact": int(lib.csb_debug_cull_exact(-1)),
         # spread of the timed steps on rank 0 (device time): what a synchronous all-reduce turns into rank skew
         "step_ms_spread": {"min": min(ms_all), "median": statistics.median(ms_all), "max": max(ms_all),
                            "std": statistics.pstdev(ms_all)},
@@ -1206,6 +1208,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gnn", action="store_true")
     ap.add_argument("--no-loss", action="store_true", help="skip the image-loss / Adam leg")
+    ap.add_argument("--cull-exact", type=int, default=-1,
+                    help="A/B timing: csb_debug_cull_exact (0 = bounding-box visit culling only, 1 = exact ellipse-vs-quad test, the default)")
     ap.add_argument("--render-variant", type=lambda v: int(v, 0), default=-1,
                     help="A/B timing: csb_debug_render_variant (low nibble forward kernel, high nibble backward kernel)")
     ap.add_argument("--no-sub", action="store_true", help="skip the C3 / C4 / kNN / sort sub-records")

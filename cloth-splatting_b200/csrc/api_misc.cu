@@ -35,6 +35,7 @@ cudaEvent_t take_event() {
 
 namespace csb {
 int g_render_variant = 0x4F;  // forward: packed kernels chosen by path (15); backward: one pixel pair per lane, delayed reduction (measured best on B200)
+int g_cull_exact = 1;
 LaunchScope::LaunchScope(const char* name_, cudaStream_t stream_) : name(name_), stream(stream_), slot(-1) {
     g_launches.fetch_add(1, std::memory_order_relaxed);
     if (g_profile.load(std::memory_order_relaxed)) {
@@ -73,6 +74,12 @@ unsigned long long csb_launch_count(void) { return g_launches.load(); }
 int csb_debug_render_variant(int variant) {
     const int old = csb::g_render_variant;
     if (variant >= 0 && ((variant & 15) <= 4 || (variant & 15) == 15) && (variant >> 4) <= 6) csb::g_render_variant = variant;
+    return old;
+}
+
+int csb_debug_cull_exact(int on) {
+    const int old = csb::g_cull_exact;
+    if (on == 0 || on == 1) csb::g_cull_exact = on;
     return old;
 }
 

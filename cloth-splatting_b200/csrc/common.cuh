@@ -106,6 +106,7 @@ struct Carver {
 // Per-launch constants of up to CSB_MAX_VIEWS views, passed by value as a kernel parameter.
 struct ViewBatch {
     int V, P, W, H, gx, gy, tiles;
+    int cull_exact;  // compositing kernels: exact ellipse-vs-quad visit culling (render_lanes.cuh quad_mask); csb_debug_cull_exact
     float focal_x[CSB_MAX_VIEWS], focal_y[CSB_MAX_VIEWS];
     float tan_fovx[CSB_MAX_VIEWS], tan_fovy[CSB_MAX_VIEWS];
     const float* viewmatrix[CSB_MAX_VIEWS];

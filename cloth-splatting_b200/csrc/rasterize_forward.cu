@@ -871,6 +871,7 @@ int fill_view_batch(ViewBatch& vb, int num_views, const csb_view* views, int P, 
     vb.gx = (width + CSB_TILE_X - 1) / CSB_TILE_X;
     vb.gy = (height + CSB_TILE_Y - 1) / CSB_TILE_Y;
     vb.tiles = vb.gx * vb.gy;
+    vb.cull_exact = g_cull_exact;
     for (int v = 0; v < num_views; ++v) {
         // rasterizer_impl.cu:226-227
         vb.focal_y[v] = height / (2.0f * views[v].tan_fovy);

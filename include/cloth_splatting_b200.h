@@ -63,6 +63,10 @@ int csb_profile_names(char* out, size_t out_bytes);
  * register cap, 4 / 5 / 6 = 1 / 3 / 2 with the delayed warp reduction).  All forward kernels produce the same per-pixel
  * bits.  Returns the previous value; a negative or out-of-range value only queries. */
 int csb_debug_render_variant(int variant);
+/* Debugging knob: 0 switches off the exact ellipse-vs-quad test that lets the compositing kernels skip the
+ * (Gaussian, 8x8 pixel quad) visits in which no pixel can reach alpha >= 1/255 (bounding-box test only, the state
+ * before it); results are identical either way.  Returns the previous value; any other argument only reads it. */
+int csb_debug_cull_exact(int on);
 /* A-B switch of the GNN forward (process-wide): 1 (default) = graphs whose edge and node tiles all fit on the GPU at once
  * run as ONE persistent kernel (gnn_small_kernel), 0 = always one launch per role and step.  Returns the previous value;
  * any other argument only queries. */

@@ -7,6 +7,7 @@ CUDA (renderCUDA forward.cu:261-379, backward.cu:399-557).
 Forward: every per-pixel output bit for bit across the variants (same operand order, same FMA contraction, expf kept).
 Backward: the warp-reduced sums differ in association only -> 1e-4 relative, the north_star's gradient tolerance."""
 import contextlib
+import ctypes
 
 import numpy as np
 import pytest
@@ -85,3 +86,61 @@ def test_variant_vs_reference_cuda(v):
         T._compare_with_reference(g, cam)
         g, cams = S.config_c2(4, 800)
         T._compare_with_reference({k: g[k] for k in ("means3D", "scales", "rotations", "opacities", "shs")}, cams[2])
+
+
+@contextlib.contextmanager
+def cull_exact(on):
+    import csb_cabi
+
+    lib = csb_cabi.lib()
+    lib.csb_debug_cull_exact.restype = ctypes.c_int
+    lib.csb_debug_cull_exact.argtypes = [ctypes.c_int]
+    old = lib.csb_debug_cull_exact(on)
+    try:
+        yield
+    finally:
+        lib.csb_debug_cull_exact(old)
+
+
+def _needles():
+    """Needle-shaped footprints (axis ratios up to 1 : 200, every orientation, opacities up to 1) in front of the C3 camera:
+    the conics whose terms cancel most in q = a dx^2 + 2 b dx dy + c dy^2, i.e. the hardest case for a culling test that
+    must never drop a quad in which a pixel blends."""
+    g = S.random_gaussians(60_000, seed=77, log_scale=(0.001, 0.2))
+    g["opacities"] = np.random.default_rng(78).uniform(0.004, 1.0, g["opacities"].shape).astype(np.float32)  # some below 1/255
+    return g, [S.front_camera(640, 360, 1.2)]
+
+
+def test_exact_quad_culling_changes_nothing():
+    """csb_debug_cull_exact: the exact ellipse-vs-quad test only removes visits in which no pixel blends, so every
+    per-pixel output is bit-identical with it on and off (and the gradients agree to the atomics' association)."""
+    scenes = list(_scenes())
+    g, cams = _needles()
+    scenes.append(("needles", g, cams))
+    for name, g, cams in scenes:
+        gc = Hh.to_cuda(g)
+        V, P = len(cams), g["means3D"].shape[0]
+        H, W = cams[0].image_height, cams[0].image_width
+        dl = torch.from_numpy(S.pixel_grad(V, H, W)).cuda()
+        def run(on, v):
+            with cull_exact(on), variant(v):
+                views, fwd = Hh.product_forward(gc, cams, 3)
+                grads = Hh.product_backward(gc, cams, views, fwd, dl, 3)
+                nc = Hh.product_state("n_contrib", torch.int32, (V, H, W), V, P, W, H, fwd)
+                fT = Hh.product_state("final_T", torch.float32, (V, H, W), V, P, W, H, fwd)
+                return (fwd[1].clone(), fwd[2].clone(), nc, fT, {k: t.clone() for k, t in grads.items()})
+
+        ref = run(0, 0x43)
+        again = run(0, 0x43)   # the same launch twice: how far the float atomics of the backward move a gradient by themselves
+        GRADS = ("means2D", "means3D", "opacities", "shs", "scales", "rotations", "cov3D")
+        floor = {k: Hh.rel_err(again[4][k].cpu().numpy(), ref[4][k].cpu().numpy()) for k in GRADS}
+        for key in ((0, 0x44), (1, 0x43), (1, 0x44)):       # one / two pixel pairs per lane: both quad layouts
+            r = run(*key)
+            for i, what in enumerate(("colour", "depth", "n_contrib", "final_T")):
+                assert torch.equal(r[i], ref[i]), f"{name}: {what} with (cull, variant) = {key}"
+            for k in GRADS:
+                rel = Hh.rel_err(r[4][k].cpu().numpy(), ref[4][k].cpu().numpy())
+                # the needles' dL/dscales cancels to ~1e-3 of its terms (two identical launches: 5.5e-4 apart on a B200): ten times
+                # the usual bound there, and never less than four times the spread measured in this run
+                bound = max((3e-4 if k in ("cov3D", "scales", "rotations") else 1e-4) * (10 if name == "needles" else 1), 4 * floor[k])
+                assert rel < bound, f"{name}: grad {k} with {key}: rel {rel} (run-to-run {floor[k]})"
