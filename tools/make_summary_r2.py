@@ -172,7 +172,7 @@ if len(scal) > 1 and 1 in scal:
         A(f"| {n} | {v['value']:.0f} | {v['ms_per_step']:.4f} | {100 * v['value'] / (n * scal[1]['value']):.1f} % | {v['e2e']['value']:.0f} | {ph} | {c4s} | {gt} |")
     A("")
     if not scal_fresh:
-        A("(Scaling run of commit 2d6163a, before the SH staging change that took C3 from 1.96 to 1.89 ms; C2 is unaffected.)\n")
+        A("(Scaling run of commit 2d6163a: before the SH staging change and the exact visit culling, which together took the single-GPU C4 step from 23.6 to 23.4 ms and C3 from 1.96 to 1.85 ms; C2 moved by 1.5 %.)\n")
 if scal_fresh:
     json.dump({str(n): {kk: v.get(kk) for kk in ("value", "ms_per_step", "n_gpus", "e2e", "allreduce", "step_ms_spread", "config", "clocks", "c4")} |
                {"gnn_train_c5": (v.get("gnn") or {}).get("train_c5")} for n, v in scal.items()}, open(SCAL_PATH, "w"), indent=1)
