@@ -73,7 +73,7 @@ unsigned long long csb_launch_count(void) { return g_launches.load(); }
 
 int csb_debug_render_variant(int variant) {
     const int old = csb::g_render_variant;
-    if (variant >= 0 && ((variant & 15) <= 4 || (variant & 15) == 15) && (variant >> 4) <= 6) csb::g_render_variant = variant;
+    if (variant >= 0 && ((variant & 15) <= 4 || (variant & 15) == 15) && (variant >> 4) <= 7) csb::g_render_variant = variant;
     return old;
 }
 

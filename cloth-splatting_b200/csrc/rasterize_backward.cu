@@ -650,9 +650,9 @@ static int launch_render_backward(cudaStream_t stream, dim3 grid, const ViewBatc
     // all views of the set in one launch: a 1-D grid over the (view, tile) pairs, composited longest list first when the
     // forward left an order (render_lanes.cuh: tile_of_block); the per-view launches of the staged backward keep (x, y, 1)
     const dim3 lgrid = tile_order ? dim3(grid.x * grid.y * grid.z) : grid;
-#define CSB_RB_LANES(NP, MINB, DELAY)                                                                                    \
-    CSB_LAUNCH("render_backward", stream,                                                                                \
-               launch_pdl(render_backward_lanes_kernel<NP, MINB, DELAY>, lgrid, dim3(LaneTiling<NP>::THREADS), 0, stream, \
+#define CSB_RB_LANES(NP, MINB, ...)                                                                                            \
+    CSB_LAUNCH("render_backward", stream,                                                                                      \
+               launch_pdl(render_backward_lanes_kernel<NP, MINB, __VA_ARGS__>, lgrid, dim3(LaneTiling<NP>::THREADS), 0, stream, \
                           vb, ranges, point_list, means2D, conic_opacity, rgb_depth, final_T, n_contrib, dL_dpix, grad_acc, view0, tile_order))
     switch ((g_render_variant >> 4) & 15) {
         case 0:
@@ -664,6 +664,7 @@ static int launch_render_backward(cudaStream_t stream, dim3 grid, const ViewBatc
         case 4: CSB_RB_LANES(1, 1, true); break;
         case 5: CSB_RB_LANES(1, 6, true); break;
         case 6: CSB_RB_LANES(2, 1, true); break;
+        case 7: CSB_RB_LANES(1, 5, true, true); break;
         default: CSB_RB_LANES(1, 1, false);
     }
 #undef CSB_RB_LANES

@@ -60,7 +60,7 @@ int csb_profile_names(char* out, size_t out_bytes);
  * points launch.  Low nibble = forward kernel (0 = one pixel per lane, 1 = one vertical pixel pair per lane, 2 = two
  * pairs, 3 / 4 = one / two pairs without per-pixel branches, 15 = 3 on the per-tile binning path and 4 on the global
  * sort path: the default), high nibble = backward kernel (0 = one pixel per lane, 1 / 2 = one / two pairs per lane, 3 = one pair under a
- * register cap, 4 / 5 / 6 = 1 / 3 / 2 with the delayed warp reduction).  All forward kernels produce the same per-pixel
+ * register cap, 4 / 5 / 6 = 1 / 3 / 2 with the delayed warp reduction, 7 = 4 with the warp sums taken through shared memory).  All forward kernels produce the same per-pixel
  * bits.  Returns the previous value; a negative or out-of-range value only queries. */
 int csb_debug_render_variant(int variant);
 /* Debugging knob: 0 switches off the exact ellipse-vs-quad test that lets the compositing kernels skip the

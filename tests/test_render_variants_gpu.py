@@ -1,7 +1,7 @@
 """The generations of compositing kernels (csb_debug_render_variant: low nibble = forward kernel, high nibble = backward
 kernel; 0 = one pixel per lane, 1 = one vertical pixel pair per lane on packed fp32x2, 2 = two pairs per lane, forward 3 / 4 =
 one / two pairs per lane without per-pixel branches (packed expf with libdevice's bits), backward 3..6
-= register-capped / delayed-reduction builds; csrc/render_lanes.cuh) against each other and against the reference's own
+= register-capped / delayed-reduction builds, 7 = warp sums through shared memory; csrc/render_lanes.cuh) against each other and against the reference's own
 CUDA (renderCUDA forward.cu:261-379, backward.cu:399-557).
 
 Forward: every per-pixel output bit for bit across the variants (same operand order, same FMA contraction, expf kept).
@@ -32,7 +32,7 @@ def variant(v):
         lib.csb_debug_render_variant(old)
 
 
-VARIANTS = (0x00, 0x11, 0x22, 0x30, 0x43, 0x54, 0x60)
+VARIANTS = (0x00, 0x11, 0x22, 0x30, 0x43, 0x54, 0x60, 0x74)
 
 
 def _scenes():
