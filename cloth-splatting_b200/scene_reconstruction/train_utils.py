@@ -79,6 +79,22 @@ def get_expon_lr_func(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, ma
     return helper
 
 
+_side_streams = {}
+
+
+def _view_streams(like, n):
+    """n side streams on the device of `like` (kept for the life of the process: a captured step must find the same
+    streams at every capture); none on the CPU or when CSB_VIEW_STREAMS=0."""
+    import os
+
+    if n <= 0 or not like.is_cuda or os.environ.get("CSB_VIEW_STREAMS", "1") == "0":
+        return []
+    have = _side_streams.setdefault(like.device, [])
+    while len(have) < n:
+        have.append(torch.cuda.Stream(device=like.device))
+    return have[:n]
+
+
 def _render_views(views, gaussians, simulator, pipeline_params, background, static, user_args, project=True):
     """First half of an iteration (train_utils.py:256-272): every view rendered at its time."""
     from gaussian_renderer import render
@@ -104,9 +120,32 @@ def _render_views(views, gaussians, simulator, pipeline_params, background, stat
         # unbind: ONE stack in the backward pass per tensor instead of a zero-fill + add per view and tensor
         pre = list(zip(vertices.unbind(0), xyz.unbind(0), rot.unbind(0)))
         batched_vertices = vertices
+    def one(v, cam):
+        return render(cam, gaussians, simulator, pipeline_params, background, no_shadow=no_shadow, render_static=static,
+                      **({} if pre[v] is None else {"precomputed": pre[v]}), **extra)
+
     with share:  # exp / sigmoid / cat of the view-independent parameters once per step instead of once per view
-        pkgs = [render(cam, gaussians, simulator, pipeline_params, background, no_shadow=no_shadow, render_static=static,
-                       **({} if pre[v] is None else {"precomputed": pre[v]}), **extra) for v, cam in enumerate(views)]
+        side = _view_streams(background, len(views) - 1) if batched_vertices is not None else []
+        if side:
+            # Every view has its own time, hence its own Gaussian positions and rotations: its rasterization is its own
+            # launch set, a chain of short kernels (preprocess, scan, fill, sort, forward -- and their mirror image in the
+            # backward pass) that each leave most of the GPU idle.  The chains of the views share nothing but their
+            # inputs, so views 1.. run on side streams beside view 0 (fork after everything they share has been enqueued,
+            # join before the images are stacked); autograd runs each view's backward on the stream of its forward.
+            # Inside the captured step the fork and the join become graph branches.
+            gaussians.get_opacity, gaussians.get_scaling, gaussians.get_features
+            main = torch.cuda.current_stream(background.device)
+            for st in side:
+                st.wait_stream(main)
+            pkgs = [None] * len(views)
+            for v in range(1, len(views)):
+                with torch.cuda.stream(side[v - 1]):
+                    pkgs[v] = one(v, views[v])
+            pkgs[0] = one(0, views[0])
+            for st in side:
+                main.wait_stream(st)
+        else:
+            pkgs = [one(v, cam) for v, cam in enumerate(views)]
     image_tensor = torch.stack([p.render for p in pkgs])
     all_vertice_deform = batched_vertices if batched_vertices is not None else torch.stack([p.vertice_deform for p in pkgs])
     radii = torch.stack([p.radii for p in pkgs]).max(dim=0).values
