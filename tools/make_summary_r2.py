@@ -153,6 +153,20 @@ if d and rd:
       f"`torch.optim.Adam` -- {rd['ms_per_iteration'] / d['ms_per_iteration']:.1f}x; same loss trajectory ({d['loss_first']:.4f} -> {d['loss_last']:.4f} vs "
       f"{rd['loss_first']:.4f} -> {rd['loss_last']:.4f}).  Kernel list of one iteration: `profiles/r2_dropin_kernel_profile.json`.\n")
 
+vs_path = os.path.join(P, "r2_view_streams_ab.json")
+if os.path.exists(vs_path):
+    vs = json.load(open(vs_path))
+    a0, a1 = vs["CSB_VIEW_STREAMS=0"], vs["CSB_VIEW_STREAMS=1"]
+    A(f"After the run above `train_step` got its views onto side streams (each view of an iteration is its own launch set); same-box A/B "
+      f"(`tools/gpu_run38.sh`, `profiles/r2_view_streams_ab.json`): {a0['ms_per_iteration']:.3f} -> **{a1['ms_per_iteration']:.3f} ms** per iteration with the "
+      f"ground-truth upload, {a0['resident_ground_truth']['ms_per_iteration']:.3f} -> **{a1['resident_ground_truth']['ms_per_iteration']:.3f} ms** with resident planes; "
+      f"losses {a0['loss_first']:.4f} -> {a0['loss_last']:.4f} and {a1['loss_first']:.4f} -> {a1['loss_last']:.4f}.\n")
+cu_path = os.path.join(P, "r2_cull_exact_ab.json")
+if os.path.exists(cu_path):
+    cu = json.load(open(cu_path))
+    A("Exact ellipse-vs-quad visit culling, same-box A/B (`bench.py --cull-exact 0|1`, `profiles/r2_cull_exact_ab.json`; the tables above are with it on): "
+      + "; ".join(f"{wl.upper()} {cu[wl + '_cull0']['ms_per_step']:.4f} -> {cu[wl + '_cull1']['ms_per_step']:.4f} ms/step" for wl in ("c2", "c3", "c4")) + ".\n")
+
 scal = {n: load(f"r2s_scale_n{n}.json") for n in (1, 2, 4, 8)}
 scal = {n: v for n, v in scal.items() if v}
 SCAL_PATH = os.path.join(P, "r2_scaling.json")
